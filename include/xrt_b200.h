@@ -1,0 +1,208 @@
+/*
+ * xrt_b200.h — C ABI of the B200-native XRTailor Swift-mode cloth hot path.
+ *
+ * Drop-in boundary for the reference's solver component
+ *   ClothSolverBase (xrtailor/include/xrtailor/pipeline/base/ClothSolverBase.hpp:55-189)
+ * Every entry point names the reference interface it replaces.  Plain pointers
+ * and sizes only; the caller owns every host array, the library copies.
+ * Every call returns 0 on success, else a TAILOR_EXIT-compatible code
+ * (xrtailor/include/xrtailor/core/ErrorDefs.hpp:3-35).  Nothing here calls
+ * exit() or throws across the boundary.  There is NO CPU fallback: when no
+ * CUDA device is usable xrt_create fails with XRT_ERR_CUDA.
+ */
+#ifndef XRT_B200_H_
+#define XRT_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define XRT_OK 0
+#define XRT_ERR_CUDA 8000          /* TAILOR_EXIT CUDA error                */
+#define XRT_ERR_NODE_POOL 8001     /* node pool exhausted                   */
+#define XRT_ERR_EDGE_POOL 8002
+#define XRT_ERR_FACE_POOL 8003
+#define XRT_ERR_INVALID 8100       /* bad argument / wrong call order       */
+#define XRT_ERR_FRAME_RANGE 9000
+
+typedef struct xrt_solver xrt_solver;
+
+/* Mirrors the fields of SimParams the Swift path reads
+ * (xrtailor/include/xrtailor/core/Common.hpp:31-116) plus the Swift config
+ * keys of SimulationConfigParser (hash_cell_size, inter_leaved_hash). */
+typedef struct xrt_params {
+  int32_t num_substeps;          /* SimParams::num_substeps            */
+  int32_t num_iterations;        /* SimParams::num_iterations          */
+  int32_t num_collision_passes;  /* SimParams::num_collision_passes    */
+  int32_t max_num_neighbors;     /* SimParams::max_num_neighbors (64)  */
+  float gravity[3];              /* SimParams::gravity                 */
+  float damping;                 /* SimParams::damping                 */
+  float relaxation_factor;       /* SimParams::relaxation_factor       */
+  float long_range_stretchiness; /* SimParams::long_range_stretchiness */
+  float sdf_friction;            /* SimParams::sdf_friction            */
+  float bvh_tolerance;           /* SimParams::bvh_tolerance           */
+  float stretch_compliance;      /* per-cloth in ref, AddCloth arg      */
+  float bend_compliance;
+  float particle_diameter;       /* SimParams::particle_diameter       */
+  float hash_cell_size;          /* swift.collision.self_contact       */
+  int32_t inter_leaved_hash;     /* swift.collision.self_contact       */
+  int32_t enable_self_collision; /* SimParams::enable_self_collision   */
+  int32_t solve_bending;         /* SimParams::solve_bending           */
+  int32_t geodesic_lra;          /* SimParams::geodesic_LRA            */
+  float frame_dt;                /* Timer::FixedDeltaTime(), 1/60      */
+  /* 0: IEEE division in the Morton quantiser (matches the CPU oracle bit
+   * for bit); 1: div.approx like the reference's --use_fast_math build
+   * (CMakeLists.txt:217), for bit parity against the reference's CUDA. */
+  int32_t morton_fast_div;
+  /* 0: one launch per colour (CUDA-graph replayed); 1: fused cooperative
+   * kernels with grid barriers between colours. */
+  int32_t fused_iterations;
+  int32_t device;                /* CUDA device ordinal                */
+} xrt_params;
+
+/* Fills *p with the reference's Swift defaults
+ * (examples/smpl/simulation_conf_smpl.json + Common.hpp HOST_INITs). */
+int xrt_default_params(xrt_params* p);
+
+/* Mesh as the reference's AddCloth/AddObstacle receive it
+ * (pipeline/impl/universal/ClothSolver.cpp:189-350): world-space positions,
+ * triangle indices, unique edges.  inv_mass may be NULL (cloth: 1, obstacle:
+ * 1e-3, PhysicsMeshHelper.cu:139). */
+typedef struct xrt_mesh_desc {
+  const float* positions;   /* 3*n_verts  */
+  const uint32_t* indices;  /* 3*n_faces  */
+  const uint32_t* edges;    /* 2*n_edges (unique, undirected) */
+  const float* inv_mass;    /* n_verts or NULL */
+  uint32_t n_verts, n_faces, n_edges;
+} xrt_mesh_desc;
+
+/* ClothSolverBase lifetime: constructor / OnDestroy. */
+int xrt_create(const xrt_params* p, xrt_solver** out);
+void xrt_destroy(xrt_solver* s);
+const char* xrt_last_error(const xrt_solver* s);
+
+/* ClothSolverUniversal::AddCloth / AddObstacle
+ * (impl/universal/ClothSolver.cpp:189,247).  One cloth mesh and one obstacle
+ * mesh per handle (merge meshes on the caller side; the reference merges
+ * them into one PhysicsMesh too).  *index_offset receives the first vertex
+ * index of the mesh, like the reference's return value. */
+int xrt_add_cloth(xrt_solver* s, const xrt_mesh_desc* m, int32_t* index_offset);
+int xrt_add_obstacle(xrt_solver* s, const xrt_mesh_desc* m, int32_t* index_offset);
+
+/* StretchSolver::AddCloth / BendSolver::AddCloth
+ * (physics/dynamics/BasicSolver.cu:36-62,101-117).  Constraints as produced by
+ * PrepareBasicStretchData / GenerateBendingElements
+ * (physics/ClothSolverHelper.cpp:4-109). */
+int xrt_set_stretch(xrt_solver* s, const uint32_t* idx01, const float* rest, size_t n);
+int xrt_set_bend(xrt_solver* s, const uint32_t* idx0123, const float* theta, size_t n);
+
+/* ClothSolverBase::AddGeodesic (pipeline/base/ClothSolverBase.cpp:527-532). */
+int xrt_add_geodesic(xrt_solver* s, const uint32_t* src, const uint32_t* tgt,
+                     const float* rest, size_t n);
+
+/* Parity injection of the reference's GraphColoring::colors
+ * (physics/graph_coloring/Base.cuh:36).  kind 0 = stretch, 1 = bend.
+ * Without it xrt_finalize_setup colours deterministically (greedy). */
+int xrt_set_colors(xrt_solver* s, int kind, const uint32_t* colors, size_t n);
+
+/* ClothSolverUniversal::Start (impl/universal/ClothSolver.cpp:46-93): builds
+ * the obstacle BVH, RTriangle masks, spatial hash, colour-compacted
+ * constraint lists; allocates every device buffer the step path needs. */
+int xrt_finalize_setup(xrt_solver* s);
+
+/* UpdateObstaclePredicted (physics/ClothSolverHelper.cu:81-97): target
+ * obstacle vertex positions of the coming frame (host pointer, 3*n floats). */
+int xrt_set_obstacle_target(xrt_solver* s, const float* xyz, size_t n_verts);
+
+/* ClothSolverBase::SimulateSwift (pipeline/base/ClothSolverBase.cpp:171-261).
+ * solver_ms (may be NULL) receives the CUDA-event time of the frame, the
+ * reference's "Solver_Total". */
+int xrt_step_frame(xrt_solver* s, float* solver_ms);
+/* Same, but enqueue only (no sync, no timing); pair with xrt_sync. */
+int xrt_step_frame_async(xrt_solver* s);
+int xrt_sync(xrt_solver* s);
+
+/* SaveCache (impl/universal/ClothSolver.cpp:107-144): which 0 = cloth,
+ * 1 = obstacle.  xyz / nrm: 3*n_verts floats each, either may be NULL. */
+int xrt_get_positions(xrt_solver* s, int which, float* xyz, float* nrm);
+/* Overwrite cloth state (x0 and v), for tests and batch seeding. */
+int xrt_set_cloth_state(xrt_solver* s, const float* xyz, const float* vel);
+
+/* Building blocks exposed for parity tests; each one is the same device
+ * code xrt_step_frame runs. */
+int xrt_bvh_build_obstacle(xrt_solver* s);                 /* BVH::UpdateData+Construct, BVH.cu:565,618 */
+int xrt_bvh_refit_obstacle(xrt_solver* s, int step);       /* Interpolate+midstep normals+RefitMidstep  */
+int xrt_generate_contacts(xrt_solver* s);                  /* PBDCollision.cu:17,100,236                */
+int xrt_hash_particles(xrt_solver* s);                     /* SpatialHashGPU::Hash                      */
+int xrt_predict(xrt_solver* s);                            /* PredictPositions                          */
+int xrt_solve_iteration(xrt_solver* s, int iteration);     /* one pass of the inner loop, no generate   */
+int xrt_finalize(xrt_solver* s);                           /* Finalize                                  */
+
+/* Debug getters (the reference's BVH::*Host / PhysicsMesh::Host* accessors,
+ * BVH.cu:579-602).  *bytes in: capacity of dst, out: bytes written/needed.
+ * dst == NULL only queries the size. */
+enum xrt_debug_what {
+  XRT_DBG_MORTON = 0,        /* uint32[F]  sorted Morton codes                 */
+  XRT_DBG_SORTED_OBJECT = 1, /* uint32[F]  object index of leaf i              */
+  XRT_DBG_NODES = 2,         /* uint32[4*(2F-1)] parent,left,right,object      */
+  XRT_DBG_AABBS = 3,         /* float[6*(2F-1)]  lower xyz, upper xyz          */
+  XRT_DBG_ESCAPE_INT = 4,    /* int32[F-1]                                     */
+  XRT_DBG_ESCAPE_EXT = 5,    /* int32[F]                                       */
+  XRT_DBG_VF_CONTACTS = 6,   /* {int32 index; float qs[3]}[V]                  */
+  XRT_DBG_RT_CONTACTS = 7,   /* {int32 index; float qc[3]}[V]                  */
+  XRT_DBG_EE_CONTACTS = 8,   /* {float dist,p2[3],q2[3],s,t,fn[3]}[E]          */
+  XRT_DBG_PREDICTED = 9,     /* float[3V] cloth x                              */
+  XRT_DBG_VELOCITY = 10,     /* float[3V] cloth v                              */
+  XRT_DBG_COLORS_STRETCH = 11,
+  XRT_DBG_COLORS_BEND = 12,
+  XRT_DBG_NEIGHBORS = 13,    /* uint32[max_nb*V] strided by V like the ref     */
+  XRT_DBG_RTRI = 14,         /* uint32[Fo] representative-triangle masks       */
+  XRT_DBG_OBSTACLE_PRED = 15,/* float[9*Fo] primitive pred1..3                 */
+  XRT_DBG_STATS = 16,        /* xrt_stats                                      */
+  XRT_DBG_PARTICLE_HASH = 17,/* uint32[V] sorted hash; then uint32[V] index    */
+  XRT_DBG_VF_CAND_COUNT = 18,/* uint32[V] #leaf hits of the VF point query     */
+  XRT_DBG_RT_CAND_COUNT = 19,/* uint32[V] #leaf hits of the vertex-ray query   */
+  XRT_DBG_EE_CAND_COUNT = 20 /* uint32[E] #leaf hits of the edge query         */
+};
+int xrt_debug_get(xrt_solver* s, int what, void* dst, size_t* bytes);
+
+/* Per-vertex / per-edge candidate sets of the three broad-phase queries in
+ * traversal order (the content of the reference's per-thread buffer[256],
+ * BVH.cu:957-1055).  kind 0 = VF point, 1 = vertex ray, 2 = edge segment.
+ * offsets: uint32[n+1] (CSR), items: uint32[offsets[n]].  Two-call protocol:
+ * call with items == NULL to get *n_items. */
+int xrt_debug_candidates(xrt_solver* s, int kind, uint32_t* offsets,
+                         uint32_t* items, size_t* n_items);
+
+/* Constraint-residual and penetration statistics (north_star's third gate). */
+typedef struct xrt_stats {
+  double stretch_rms;       /* RMS of (|xi-xj|-rest)/rest over stretch constraints */
+  double stretch_max;
+  double bend_rms;          /* RMS of (angle-theta0)                               */
+  uint32_t vf_penetrations; /* vertices with n.(x-qs) < 0 on their VF contact      */
+  uint32_t n_stretch_colors, n_bend_colors;
+  uint32_t launches_per_frame; /* kernels enqueued by one xrt_step_frame         */
+  double bytes_per_frame;      /* algorithmic bytes of one frame     */
+} xrt_stats;
+
+/* Deterministic greedy colouring (replaces GraphColoring::Paint's random
+ * palette, graph_coloring/Base.cu:163-317, in O(n)).  arity 2 or 4. */
+int xrt_greedy_color(const uint32_t* idx, size_t n, int arity, uint32_t n_verts,
+                     uint32_t* colors, uint32_t* n_colors);
+
+/* Standalone LBVH build over triangles (BVH::UpdateData(ccd=false)+Construct)
+ * for parity tests and the 200k-face scaling config.  Outputs as above. */
+int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts,
+                             const uint32_t* indices, uint32_t n_faces,
+                             int morton_fast_div, int device,
+                             uint32_t* morton, uint32_t* sorted_object,
+                             uint32_t* nodes, float* aabbs,
+                             int32_t* esc_int, int32_t* esc_ext, float* build_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* XRT_B200_H_ */
