@@ -1,0 +1,336 @@
+// LBVH for sm_100a: fused leaf-box + scene-box kernel, Morton quantiser,
+// cub radix sort of (key,index) only, Karras hierarchy on (morton,object)
+// pairs, single-pass bottom-up boxes with arrival counters, O(1) escape links
+// from the Karras ranges, nodes packed to one 32-byte sector for traversal.
+// Behaviour follows xrtailor/src/physics/broad_phase/lbvh/BVH.cu:22-46
+// (morton), :57-210 (determine_range / find_split), :212-264 (escape tables),
+// :423-462 (leaf boxes), :618-722 (Construct), :770-818 (RefitMidstep).
+#include "xrt_bvh.cuh"
+#include <cub/device/device_radix_sort.cuh>
+
+namespace {
+
+// order-preserving float <-> int map so atomicMin/Max work on floats
+__device__ __forceinline__ int f2ord(float f) {
+  int i = __float_as_int(f);
+  return i >= 0 ? i : i ^ 0x7FFFFFFF;
+}
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
+
+__global__ void scene_init_kernel(int* scene) {
+  if (threadIdx.x < 3) scene[threadIdx.x] = f2ord(INFINITY);
+  else if (threadIdx.x < 6) scene[threadIdx.x] = f2ord(-INFINITY);
+}
+
+// UpdateObjects_Kernel + InitAABBs_Kernel + thrust::reduce (BVH.cu:382-462,642)
+// in one pass over the faces.
+__global__ void leaf_box_kernel(const float4* __restrict__ x, const uint32_t* __restrict__ tri,
+                                float4* __restrict__ pred, float* __restrict__ leaf_box,
+                                int* __restrict__ scene, uint32_t F) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  if (i < F) {
+    float4 a = x[tri[3 * i]], b = x[tri[3 * i + 1]], c = x[tri[3 * i + 2]];
+    pred[3 * i] = a;
+    pred[3 * i + 1] = b;
+    pred[3 * i + 2] = c;
+    lo[0] = fminf(a.x, fminf(b.x, c.x));
+    lo[1] = fminf(a.y, fminf(b.y, c.y));
+    lo[2] = fminf(a.z, fminf(b.z, c.z));
+    hi[0] = fmaxf(a.x, fmaxf(b.x, c.x));
+    hi[1] = fmaxf(a.y, fmaxf(b.y, c.y));
+    hi[2] = fmaxf(a.z, fmaxf(b.z, c.z));
+    float* o = leaf_box + 6 * (size_t)i;
+    o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2];
+    o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
+  }
+  // warp shuffle reduce, then one atomic per warp per component
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    float l = lo[k], h = hi[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l = fminf(l, __shfl_xor_sync(0xFFFFFFFFu, l, o));
+      h = fmaxf(h, __shfl_xor_sync(0xFFFFFFFFu, h, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(scene + k, f2ord(l));
+      atomicMax(scene + 3 + k, f2ord(h));
+    }
+  }
+}
+
+__device__ __forceinline__ uint32_t expand_bits10(uint32_t v) {  // BVH.cu:18-24
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+__device__ __forceinline__ uint32_t quant10(float t) {
+  t = t * 1024.0f;
+  t = t > 0.0f ? t : 0.0f;        // MathFunctions::max(a,b) = a > b ? a : b  (NaN -> 0)
+  t = t < 1023.0f ? t : 1023.0f;  // MathFunctions::min
+  return (uint32_t)t;
+}
+
+// ComputeMortons_Kernel + InitObjectIndices_Kernel (BVH.cu:464-487)
+template <bool FAST_DIV>
+__global__ void morton_kernel(const float* __restrict__ leaf_box, const int* __restrict__ scene,
+                              uint32_t* __restrict__ key, uint32_t* __restrict__ val, uint32_t F) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F) return;
+  const float* b = leaf_box + 6 * (size_t)i;
+  float wl[3] = {ord2f(scene[0]), ord2f(scene[1]), ord2f(scene[2])};
+  float wu[3] = {ord2f(scene[3]), ord2f(scene[4]), ord2f(scene[5])};
+  uint32_t q[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    float p = 0.5f * (b[k] + b[3 + k]);
+    p = __fsub_rn(p, wl[k]);
+    float d = __fsub_rn(wu[k], wl[k]);
+    p = FAST_DIV ? __fdividef(p, d) : __fdiv_rn(p, d);
+    q[k] = quant10(p);
+  }
+  key[i] = expand_bits10(q[0]) * 4 + expand_bits10(q[1]) * 2 + expand_bits10(q[2]);
+  val[i] = i;
+}
+
+// common_upper_bits on the reference's 64-bit key (morton << 32 | object),
+// evaluated from the two halves.  For distinct Morton codes it equals the
+// 32-bit __clz the reference uses when all codes are unique (BVH.cu:47-55), so
+// one code path gives the reference's tree in both of its modes.
+__device__ __forceinline__ int delta_pair(uint32_t m0, uint32_t o0, uint32_t m1, uint32_t o1) {
+  return m0 != m1 ? __clz(m0 ^ m1) : 32 + __clz(o0 ^ o1);
+}
+
+// ConstructLeafNodes_Kernel + ConstructInternalNodes64Bits_Kernel (BVH.cu:297-318,489-500)
+__global__ void karras_kernel(const uint32_t* __restrict__ morton, const uint32_t* __restrict__ obj,
+                              BVNode* __restrict__ nodes, int2* __restrict__ ranges, uint32_t F) {
+  uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (tid >= F) return;
+  const int n = (int)F;
+  // leaf tid
+  nodes[F - 1 + tid].left = 0xFFFFFFFFu;
+  nodes[F - 1 + tid].right = 0xFFFFFFFFu;
+  nodes[F - 1 + tid].object = obj[tid];
+  if (F == 1) nodes[0].parent = 0xFFFFFFFFu;
+  if (tid >= F - 1) return;
+  const int idx = (int)tid;
+  const uint32_t mc = morton[idx], oc = obj[idx];
+  auto delta = [&](int j) -> int {
+    return (j < 0 || j >= n) ? -1 : delta_pair(mc, oc, morton[j], obj[j]);
+  };
+  int first, last;
+  if (idx == 0) {
+    first = 0;
+    last = n - 1;
+    nodes[0].parent = 0xFFFFFFFFu;
+  } else {
+    const int dl = delta(idx - 1), dr = delta(idx + 1);
+    const int d = dr > dl ? 1 : -1;
+    const int dmin = min(dl, dr);
+    int lmax = 2;
+    while (delta(idx + d * lmax) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t > 0; t >>= 1)
+      if (delta(idx + (l + t) * d) > dmin) l += t;
+    int j = idx + l * d;
+    first = min(idx, j);
+    last = max(idx, j);
+  }
+  // find_split (keys are unique by construction, so no equal-code shortcut)
+  const uint32_t mf = morton[first], of = obj[first];
+  const int dnode = delta_pair(mf, of, morton[last], obj[last]);
+  int split = first, stride = last - first;
+  do {
+    stride = (stride + 1) >> 1;
+    const int mid = split + stride;
+    if (mid < last && delta_pair(mf, of, morton[mid], obj[mid]) > dnode) split = mid;
+  } while (stride > 1);
+  uint32_t L = split, R = split + 1;
+  if (first == split) L += F - 1;
+  if (last == split + 1) R += F - 1;
+  nodes[idx].left = L;
+  nodes[idx].right = R;
+  nodes[idx].object = 0xFFFFFFFFu;
+  nodes[L].parent = idx;
+  nodes[R].parent = idx;
+  ranges[idx] = make_int2(first, last);
+}
+
+__device__ __forceinline__ void tnode_store_box(TNode* t, const float lo[3], const float hi[3]) {
+  // box lives in the first 24 bytes: one float4 + one float2 store
+  reinterpret_cast<float4*>(t)[0] = make_float4(lo[0], lo[1], lo[2], hi[0]);
+  reinterpret_cast<float2*>(t)[2] = make_float2(hi[1], hi[2]);
+}
+__device__ __forceinline__ void tnode_load_box(const TNode* t, float lo[3], float hi[3]) {
+  // L2 loads: sibling boxes written by other SMs must not come from a stale L1 line
+  float4 a = __ldcg(reinterpret_cast<const float4*>(t));
+  float2 b = __ldcg(reinterpret_cast<const float2*>(t) + 2);
+  lo[0] = a.x; lo[1] = a.y; lo[2] = a.z;
+  hi[0] = a.w; hi[1] = b.x; hi[2] = b.y;
+}
+
+// Bottom-up boxes in one pass (replaces AssignAABBAtomic_Kernel's
+// O(F log F) CAS walk, BVH.cu:540-556; min/max are exact so boxes are
+// identical).  The second thread to arrive at a parent merges its children.
+__device__ __forceinline__ void walk_up(TNode* tn, const BVNode* nodes, int* flags, uint32_t leaf_node) {
+  uint32_t parent = nodes[leaf_node].parent;
+  while (parent != 0xFFFFFFFFu) {
+    __threadfence();
+    if (atomicAdd(flags + parent, 1) == 0) return;
+    float la[3], ha[3], lb[3], hb[3];
+    tnode_load_box(tn + nodes[parent].left, la, ha);
+    tnode_load_box(tn + nodes[parent].right, lb, hb);
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      la[k] = fminf(la[k], lb[k]);
+      ha[k] = fmaxf(ha[k], hb[k]);
+    }
+    tnode_store_box(tn + parent, la, ha);
+    parent = nodes[parent].parent;
+  }
+}
+
+__global__ void build_boxes_kernel(TNode* tn, const BVNode* __restrict__ nodes,
+                                   const float* __restrict__ leaf_box,
+                                   const uint32_t* __restrict__ obj, int* flags, uint32_t F) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F) return;
+  const float* b = leaf_box + 6 * (size_t)obj[i];
+  float lo[3] = {b[0], b[1], b[2]}, hi[3] = {b[3], b[4], b[5]};
+  tnode_store_box(tn + F - 1 + i, lo, hi);
+  walk_up(tn, nodes, flags, F - 1 + i);
+}
+
+// Escape links in O(1) from the Karras ranges: the subtree that follows a
+// range ending at leaf `last` is rooted at internal node last+1 when that node
+// starts at last+1, else at leaf last+1.  Equals the parent walk of
+// Build{Internal,External}EscapeIndexTable_Kernel (BVH.cu:212-264).
+__device__ __forceinline__ int escape_after(int last, const int2* ranges, int n) {
+  if (last >= n - 1) return -1;
+  const int k = last + 1;
+  if (k <= n - 2 && ranges[k].x == k) return k;
+  return n - 1 + k;
+}
+
+__global__ void link_kernel(TNode* tn, const BVNode* __restrict__ nodes, const int2* __restrict__ ranges,
+                            int32_t* __restrict__ esc_int, int32_t* __restrict__ esc_ext, uint32_t F) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = (int)F;
+  if (i >= 2 * F - 1) return;
+  if (i < F - 1) {
+    int e = escape_after(ranges[i].y, ranges, n);
+    esc_int[i] = e;
+    tn[i].link_hit = (int)nodes[i].left;
+    tn[i].link_miss = e;
+  } else {
+    int leaf = (int)(i - (F - 1));
+    int e = escape_after(leaf, ranges, n);
+    esc_ext[leaf] = e;
+    tn[i].link_hit = ~(int)nodes[i].object;
+    tn[i].link_miss = e;
+  }
+}
+
+// Interpolated obstacle -> primitive pred + grow-only leaf boxes + exact
+// internal merge (RefitExternalNodeMidstep_Kernel + AssignAABBCAS_Kernel,
+// BVH.cu:770-793,515-538), one kernel.
+__global__ void refit_kernel(TNode* tn, const BVNode* __restrict__ nodes, float4* __restrict__ pred,
+                             const float4* __restrict__ x1, const float4* __restrict__ n1,
+                             const uint32_t* __restrict__ tri, float tol, int* flags, uint32_t F) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F) return;
+  const uint32_t node = F - 1 + i;
+  const uint32_t o = nodes[node].object;
+  float lo[3], hi[3];
+  tnode_load_box(tn + node, lo, hi);
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const uint32_t v = tri[3 * o + k];
+    const float4 p = x1[v], nn = n1[v];
+    const float4 q = make_float4(p.x + tol * nn.x, p.y + tol * nn.y, p.z + tol * nn.z, 0.f);
+    pred[3 * o + k] = q;
+    lo[0] = fminf(lo[0], q.x); lo[1] = fminf(lo[1], q.y); lo[2] = fminf(lo[2], q.z);
+    hi[0] = fmaxf(hi[0], q.x); hi[1] = fmaxf(hi[1], q.y); hi[2] = fmaxf(hi[2], q.z);
+  }
+  tnode_store_box(tn + node, lo, hi);
+  walk_up(tn, nodes, flags, node);
+}
+
+}  // namespace
+
+int bvh_alloc(DevBVH* b, BvhWork* w, uint32_t F) {
+  if (F == 0) return 0;
+  const size_t nn = 2 * (size_t)F - 1;
+  b->n_obj = F;
+  cudaError_t e = cudaSuccess;
+  auto A = [&](void** p, size_t bytes) {
+    if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16);
+  };
+  A((void**)&b->tnodes, nn * sizeof(TNode));
+  A((void**)&b->nodes, nn * sizeof(BVNode));
+  A((void**)&b->esc_int, F * sizeof(int32_t));
+  A((void**)&b->esc_ext, F * sizeof(int32_t));
+  A((void**)&b->pred, 3 * (size_t)F * sizeof(float4));
+  A((void**)&w->key_a, F * 4); A((void**)&w->key_b, F * 4);
+  A((void**)&w->val_a, F * 4); A((void**)&w->val_b, F * 4);
+  A((void**)&w->flags, F * sizeof(int));
+  A((void**)&w->leaf_box, 6 * (size_t)F * sizeof(float));
+  A((void**)&w->scene, 8 * sizeof(int));
+  A((void**)&w->ranges, F * sizeof(int2));
+  if (e != cudaSuccess) return (int)e;
+  cub::DoubleBuffer<uint32_t> k(w->key_a, w->key_b), v(w->val_a, w->val_b);
+  w->cub_bytes = 0;
+  e = cub::DeviceRadixSort::SortPairs(nullptr, w->cub_bytes, k, v, (int)F, 0, 30);
+  A(&w->cub_tmp, w->cub_bytes);
+  w->cap = F;
+  b->morton = nullptr;
+  b->sorted_obj = nullptr;
+  b->aabbs = nullptr;
+  return (int)e;
+}
+
+void bvh_free(DevBVH* b, BvhWork* w) {
+  cudaFree(b->tnodes); cudaFree(b->nodes); cudaFree(b->esc_int); cudaFree(b->esc_ext); cudaFree(b->pred);
+  cudaFree(w->key_a); cudaFree(w->key_b); cudaFree(w->val_a); cudaFree(w->val_b);
+  cudaFree(w->flags); cudaFree(w->leaf_box); cudaFree(w->scene); cudaFree(w->ranges); cudaFree(w->cub_tmp);
+  *b = DevBVH{};
+  *w = BvhWork{};
+}
+
+int bvh_build_launches() { return 7; }   // scene_init, leaf_box, morton, sort(~2: histogram+onesweep counted as 2), karras, boxes, link  (memset excluded)
+int bvh_refit_launches() { return 1; }
+
+void bvh_build(const DevBVH& b_, const BvhWork& w, const float4* x, const uint32_t* tri, uint32_t F,
+               int fast_div, cudaStream_t st) {
+  DevBVH& b = const_cast<DevBVH&>(b_);
+  if (F == 0) return;
+  const unsigned g = xrt_grid(F);
+  scene_init_kernel<<<1, 32, 0, st>>>(w.scene);
+  leaf_box_kernel<<<g, XRT_BLOCK, 0, st>>>(x, tri, b.pred, w.leaf_box, w.scene, F);
+  if (fast_div)
+    morton_kernel<true><<<g, XRT_BLOCK, 0, st>>>(w.leaf_box, w.scene, w.key_a, w.val_a, F);
+  else
+    morton_kernel<false><<<g, XRT_BLOCK, 0, st>>>(w.leaf_box, w.scene, w.key_a, w.val_a, F);
+  // stable LSD radix sort over the 30 key bits == thrust::stable_sort_by_key (BVH.cu:666)
+  cub::DoubleBuffer<uint32_t> k(w.key_a, w.key_b), v(w.val_a, w.val_b);
+  size_t bytes = w.cub_bytes;
+  cub::DeviceRadixSort::SortPairs(w.cub_tmp, bytes, k, v, (int)F, 0, 30, st);
+  b.morton = k.Current();
+  b.sorted_obj = v.Current();
+  cudaMemsetAsync(w.flags, 0, F * sizeof(int), st);
+  karras_kernel<<<g, XRT_BLOCK, 0, st>>>(b.morton, b.sorted_obj, b.nodes, w.ranges, F);
+  build_boxes_kernel<<<g, XRT_BLOCK, 0, st>>>(b.tnodes, b.nodes, w.leaf_box, b.sorted_obj, w.flags, F);
+  link_kernel<<<xrt_grid(2 * (size_t)F - 1), XRT_BLOCK, 0, st>>>(b.tnodes, b.nodes, w.ranges, b.esc_int,
+                                                                  b.esc_ext, F);
+}
+
+void bvh_refit_midstep(const DevBVH& b, const BvhWork& w, const float4* x1, const float4* n1,
+                       const uint32_t* tri, float tol, cudaStream_t st) {
+  const uint32_t F = b.n_obj;
+  if (F == 0) return;
+  cudaMemsetAsync(w.flags, 0, F * sizeof(int), st);
+  refit_kernel<<<xrt_grid(F), XRT_BLOCK, 0, st>>>(b.tnodes, b.nodes, b.pred, x1, n1, tri, tol, w.flags, F);
+}

@@ -1,0 +1,32 @@
+// LBVH build / refit for the B200 path.  Interface only; see xrt_bvh.cu.
+#pragma once
+#include "xrt_common.cuh"
+
+struct BvhWork {
+  uint32_t cap = 0;  // faces this scratch was sized for
+  uint32_t *key_a = nullptr, *key_b = nullptr, *val_a = nullptr, *val_b = nullptr;
+  void* cub_tmp = nullptr;
+  size_t cub_bytes = 0;
+  int* flags = nullptr;     // [F-1] arrival counters of the bottom-up pass
+  float* leaf_box = nullptr;  // [6F] leaf boxes in object order (not carried through the sort)
+  int* scene = nullptr;     // [6] scene box as order-preserving ints
+  int2* ranges = nullptr;   // [F-1] Karras range of each internal node
+};
+
+int bvh_alloc(DevBVH* b, BvhWork* w, uint32_t n_faces);
+void bvh_free(DevBVH* b, BvhWork* w);
+
+// BVH::UpdateData(tol=0, ccd=false) + BVH::Construct(scr=0)
+// (xrtailor/src/physics/broad_phase/lbvh/BVH.cu:565-573,618-722).
+// x: vertex positions (float4, w ignored); tri: uint32[3F].
+void bvh_build(const DevBVH& b, const BvhWork& w, const float4* x, const uint32_t* tri,
+               uint32_t n_faces, int fast_div, cudaStream_t st);
+
+// BVH::RefitMidstep (BVH.cu:795-818): pred = x1 + tol*n1, leaf boxes grow,
+// internal boxes = exact merge of children.
+void bvh_refit_midstep(const DevBVH& b, const BvhWork& w, const float4* x1, const float4* n1,
+                       const uint32_t* tri, float tol, cudaStream_t st);
+
+// number of kernels one call enqueues (for the launch count the bench reports)
+int bvh_build_launches();
+int bvh_refit_launches();
