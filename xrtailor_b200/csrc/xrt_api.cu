@@ -205,3 +205,272 @@ extern "C" int xrt_set_colors(xrt_solver* s, int kind, const uint32_t* colors, s
   }
   return XRT_OK;
 }
+
+// ---------------------------------------------------------------------------
+// setup-time host work
+// ---------------------------------------------------------------------------
+
+// Deterministic greedy colouring in O(n): a 128-bit mask per vertex holds the
+// colours already used by constraints on that vertex.  Replaces the random
+// palette colouring + O(n^2) adjacency build of graph_coloring/Base.cu:163-317
+// and impl/StretchColoring.cu:6-24; any proper colouring is a valid
+// Gauss-Seidel order, and the reference's own order is random per run (F9).
+extern "C" int xrt_greedy_color(const uint32_t* idx, size_t n, int arity, uint32_t n_verts, uint32_t* colors,
+                                uint32_t* n_colors) {
+  if ((n && (!idx || !colors)) || (arity != 2 && arity != 4)) return XRT_ERR_INVALID;
+  std::vector<uint64_t> lo(n_verts, 0), hi(n_verts, 0);
+  uint32_t used = 0;
+  for (size_t c = 0; c < n; c++) {
+    uint64_t ml = 0, mh = 0;
+    for (int a = 0; a < arity; a++) {
+      const uint32_t v = idx[c * arity + a];
+      if (v >= n_verts) return XRT_ERR_INVALID;
+      ml |= lo[v];
+      mh |= hi[v];
+    }
+    uint32_t col;
+    if (~ml) col = (uint32_t)__builtin_ctzll(~ml);
+    else if (~mh) col = 64u + (uint32_t)__builtin_ctzll(~mh);
+    else return XRT_ERR_INVALID;  // > 128 colours: vertex degree beyond anything a triangle mesh produces
+    for (int a = 0; a < arity; a++) {
+      const uint32_t v = idx[c * arity + a];
+      if (col < 64) lo[v] |= 1ull << col;
+      else hi[v] |= 1ull << (col - 64);
+    }
+    colors[c] = col;
+    used = std::max(used, col + 1);
+  }
+  if (n_colors) *n_colors = used;
+  return XRT_OK;
+}
+
+// stable counting sort of constraints by colour; returns offsets[n_colors+1]
+// and whether any colour touches a vertex twice (then the kernels use atomics
+// like the reference does unconditionally)
+static void color_ranges(const std::vector<uint32_t>& idx, int arity, const std::vector<uint32_t>& color,
+                         uint32_t n_verts, std::vector<uint32_t>& perm, std::vector<uint32_t>& off, bool& improper) {
+  const size_t n = color.size();
+  uint32_t nc = 0;
+  for (uint32_t c : color) nc = std::max(nc, c + 1);
+  off.assign(nc + 1, 0);
+  for (uint32_t c : color) off[c + 1]++;
+  for (uint32_t c = 0; c < nc; c++) off[c + 1] += off[c];
+  perm.resize(n);
+  std::vector<uint32_t> cur(off.begin(), off.end() - 1);
+  for (size_t i = 0; i < n; i++) perm[cur[color[i]]++] = (uint32_t)i;
+  improper = false;
+  std::vector<uint32_t> stamp(n_verts, 0xFFFFFFFFu);
+  for (uint32_t c = 0; c < nc && !improper; c++)
+    for (uint32_t s = off[c]; s < off[c + 1] && !improper; s++)
+      for (int a = 0; a < arity; a++) {
+        const uint32_t v = idx[(size_t)perm[s] * arity + a];
+        if (stamp[v] == c) improper = true;
+        stamp[v] = c;
+      }
+}
+
+// vertex -> (face << 2 | corner) CSR, faces ascending per vertex
+// (BuildVFAdjacency, physics/ClothSolverHelper.cu:377-401 uses std::set<uint>)
+static void build_vf(const std::vector<uint32_t>& tri, uint32_t V, std::vector<uint32_t>& off,
+                     std::vector<uint32_t>& idx) {
+  const size_t F = tri.size() / 3;
+  off.assign(V + 1, 0);
+  for (size_t i = 0; i < 3 * F; i++) off[tri[i] + 1]++;
+  for (uint32_t v = 0; v < V; v++) off[v + 1] += off[v];
+  idx.resize(3 * F);
+  std::vector<uint32_t> cur(off.begin(), off.end() - 1);
+  for (size_t f = 0; f < F; f++)
+    for (uint32_t j = 0; j < 3; j++) idx[cur[tri[3 * f + j]]++] = (uint32_t)(f << 2) | j;
+}
+
+// RTriBuild_Kernel (physics/representative_triangle/RTriangle.cu:19-74) on the
+// host: bit i   = this face is the lowest-index face on its vertex i,
+//       bit 3+i = this face owns edge (i, i+1): no other face shares it, or
+//                 the lowest-index other face sharing it has a larger index.
+static void build_rtri(const std::vector<uint32_t>& tri, const std::vector<uint32_t>& vf_off,
+                       const std::vector<uint32_t>& vf_idx, std::vector<uint32_t>& rtri) {
+  const size_t F = tri.size() / 3;
+  rtri.assign(F, 0);
+  for (size_t f = 0; f < F; f++) {
+    uint32_t info = 0;
+    for (uint32_t i = 0; i < 3; i++) {
+      const uint32_t vi = tri[3 * f + i], vj = tri[3 * f + (i + 1) % 3];
+      if (vf_off[vi] < vf_off[vi + 1] && (vf_idx[vf_off[vi]] >> 2) == f) info |= 1u << i;
+      uint32_t of = 0xFFFFFFFFu;
+      for (uint32_t a = vf_off[vi]; a < vf_off[vi + 1] && of == 0xFFFFFFFFu; a++) {
+        const uint32_t g = vf_idx[a] >> 2;
+        if (g == f) continue;
+        for (uint32_t b = vf_off[vj]; b < vf_off[vj + 1]; b++)
+          if ((vf_idx[b] >> 2) == g) { of = g; break; }
+      }
+      if (f < of) info |= 1u << (i + 3u);
+    }
+    rtri[f] = info;
+  }
+}
+
+static std::vector<float4> to_float4(const std::vector<float>& pos, const std::vector<float>& w) {
+  std::vector<float4> out(w.size());
+  for (size_t i = 0; i < w.size(); i++) out[i] = make_float4(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], w[i]);
+  return out;
+}
+
+static void fill_step_const(xrt_solver* s) {
+  const xrt_params& p = s->p;
+  StepConst& k = s->k;
+  k.dt = p.frame_dt / (float)p.num_substeps;
+  k.gx = p.gravity[0]; k.gy = p.gravity[1]; k.gz = p.gravity[2];
+  k.damping = p.damping;
+  k.relaxation = p.relaxation_factor;
+  k.lra_stretchiness = p.long_range_stretchiness;
+  k.friction = p.sdf_friction;
+  k.stretch_compliance = p.stretch_compliance;
+  k.bend_compliance = p.bend_compliance;
+  k.particle_diameter = p.particle_diameter;
+  k.cell_spacing = p.particle_diameter * p.hash_cell_size;  // SpatialHashGPU ctor, SpatialHashGPU.cu:161-167
+  k.table_size = 2 * (int)s->c.V;
+  k.max_neighbors = p.max_num_neighbors;
+}
+
+extern "C" int xrt_finalize_setup(xrt_solver* s) {
+  if (!s) return XRT_ERR_INVALID;
+  XRT_REQUIRE(!s->finalized, "finalize_setup called twice");
+  XRT_REQUIRE(!s->c_pos.empty(), "finalize_setup: no cloth");
+  XRT_REQUIRE(s->p.num_substeps > 0 && s->p.num_iterations > 0 && s->p.num_collision_passes > 0,
+              "finalize_setup: substeps, iterations and collision passes must be positive");
+  XRT_CUDA_OK(cudaSetDevice(s->p.device));
+  ClothDev& c = s->c;
+  ObstacleDev& o = s->o;
+  c.V = (uint32_t)s->c_invm.size();
+  c.F = (uint32_t)(s->c_tri.size() / 3);
+  c.E = (uint32_t)(s->c_edge.size() / 2);
+  for (uint32_t v : s->s_idx) XRT_REQUIRE(v < c.V, "stretch index out of range");
+  for (uint32_t v : s->b_idx) XRT_REQUIRE(v < c.V, "bend index out of range");
+  for (uint32_t v : s->l_src) XRT_REQUIRE(v < c.V, "geodesic src out of range");
+  for (uint32_t v : s->l_tgt) XRT_REQUIRE(v < c.V, "geodesic tgt out of range");
+  // particle diameter like ClothObjectUniversal::Start (impl/universal/ClothObject.hpp:36-37):
+  // |p[idx0]-p[idx1]| of the first triangle; PARTICLE_DIAMETER scaling is the caller's
+  if (s->p.particle_diameter <= 0.f && c.F) {
+    const float* a = &s->c_pos[3 * s->c_tri[0]];
+    const float* b = &s->c_pos[3 * s->c_tri[1]];
+    s->p.particle_diameter = sqrtf((a[0] - b[0]) * (a[0] - b[0]) + (a[1] - b[1]) * (a[1] - b[1]) + (a[2] - b[2]) * (a[2] - b[2]));
+  }
+  // --- colours ---
+  const uint32_t ns = (uint32_t)s->s_rest.size(), nb = (uint32_t)s->b_theta.size();
+  if (!s->s_color_set) {
+    s->s_color.resize(ns);
+    if (xrt_greedy_color(s->s_idx.data(), ns, 2, c.V, s->s_color.data(), nullptr)) {
+      xrt_set_error(s, "stretch colouring failed");
+      return XRT_ERR_INVALID;
+    }
+  }
+  if (!s->b_color_set) {
+    s->b_color.resize(nb);
+    if (xrt_greedy_color(s->b_idx.data(), nb, 4, c.V, s->b_color.data(), nullptr)) {
+      xrt_set_error(s, "bend colouring failed");
+      return XRT_ERR_INVALID;
+    }
+  }
+  std::vector<uint32_t> s_perm, b_perm;
+  color_ranges(s->s_idx, 2, s->s_color, c.V, s_perm, s->s_off, s->atomic_s);
+  color_ranges(s->b_idx, 4, s->b_color, c.V, b_perm, s->b_off, s->atomic_b);
+  c.n_stretch = ns; c.n_sc = (uint32_t)s->s_off.size() - 1;
+  c.n_bend = nb;    c.n_bc = (uint32_t)s->b_off.size() - 1;
+  std::vector<uint2> hs(ns);
+  std::vector<float> hr(ns), hl(ns, 0.f);
+  for (uint32_t i = 0; i < ns; i++) {
+    hs[i] = make_uint2(s->s_idx[2 * s_perm[i]], s->s_idx[2 * s_perm[i] + 1]);
+    hr[i] = s->s_rest[s_perm[i]];
+  }
+  std::vector<uint4> hb(nb);
+  std::vector<float> ht(nb);
+  for (uint32_t i = 0; i < nb; i++) {
+    const uint32_t* q = &s->b_idx[4 * (size_t)b_perm[i]];
+    hb[i] = make_uint4(q[0], q[1], q[2], q[3]);
+    ht[i] = s->b_theta[b_perm[i]];
+  }
+  // --- cloth device state ---
+  std::vector<float4> cx = to_float4(s->c_pos, s->c_invm);
+  XRT_CUDA_OK(dev_upload(&c.x0, cx));
+  XRT_CUDA_OK(dev_upload(&c.x, cx));
+  XRT_CUDA_OK(dev_upload(&c.rest, cx));
+  XRT_CUDA_OK(dev_alloc(&c.v, c.V));
+  XRT_CUDA_OK(cudaMemset(c.v, 0, c.V * sizeof(float4)));
+  XRT_CUDA_OK(dev_alloc(&c.n, c.V));
+  XRT_CUDA_OK(dev_alloc(&c.delta, c.V));
+  XRT_CUDA_OK(cudaMemset(c.delta, 0, c.V * sizeof(float4)));
+  XRT_CUDA_OK(dev_upload(&c.tri, s->c_tri));
+  std::vector<uint2> he(c.E);
+  for (uint32_t i = 0; i < c.E; i++) he[i] = make_uint2(s->c_edge[2 * i], s->c_edge[2 * i + 1]);
+  XRT_CUDA_OK(dev_upload(&c.edge, he));
+  std::vector<uint32_t> vfo, vfi;
+  build_vf(s->c_tri, c.V, vfo, vfi);
+  XRT_CUDA_OK(dev_upload(&c.vf_off, vfo));
+  XRT_CUDA_OK(dev_upload(&c.vf_idx, vfi));
+  XRT_CUDA_OK(dev_upload(&c.s_idx, hs));
+  XRT_CUDA_OK(dev_upload(&c.s_rest, hr));
+  XRT_CUDA_OK(dev_upload(&c.s_lambda, hl));
+  XRT_CUDA_OK(dev_upload(&c.s_perm, s_perm));
+  XRT_CUDA_OK(dev_upload(&c.b_idx, hb));
+  XRT_CUDA_OK(dev_upload(&c.b_theta, ht));
+  XRT_CUDA_OK(dev_upload(&s->d_s_off, s->s_off));
+  XRT_CUDA_OK(dev_upload(&s->d_b_off, s->b_off));
+  c.n_lra = (uint32_t)s->l_rest.size();
+  XRT_CUDA_OK(dev_upload(&c.l_src, s->l_src));
+  XRT_CUDA_OK(dev_upload(&c.l_tgt, s->l_tgt));
+  XRT_CUDA_OK(dev_upload(&c.l_rest, s->l_rest));
+  XRT_CUDA_OK(dev_alloc(&c.vf, c.V));
+  XRT_CUDA_OK(dev_alloc(&c.rt, c.V));
+  XRT_CUDA_OK(dev_alloc(&c.ee, c.E));
+  XRT_CUDA_OK(cudaMemset(c.vf, 0xFF, c.V * sizeof(VFContact)));  // index = -1: no contact
+  XRT_CUDA_OK(cudaMemset(c.rt, 0xFF, c.V * sizeof(VFContact)));
+  {
+    std::vector<EEContact> e0(c.E);
+    for (auto& e : e0) { memset(&e, 0, sizeof(e)); e.dist = XRT_SCALAR_MAX; }
+    if (c.E) XRT_CUDA_OK(cudaMemcpy(c.ee, e0.data(), c.E * sizeof(EEContact), cudaMemcpyHostToDevice));
+  }
+  XRT_CUDA_OK(dev_alloc(&c.cnt_vf, c.V));
+  XRT_CUDA_OK(dev_alloc(&c.cnt_rt, c.V));
+  XRT_CUDA_OK(dev_alloc(&c.cnt_ee, c.E));
+  fill_step_const(s);
+  if (hash_alloc(&c, s->k) != 0) {
+    xrt_set_error(s, "spatial hash allocation failed");
+    return XRT_ERR_CUDA;
+  }
+  // --- obstacle ---
+  o.V = (uint32_t)s->o_invm.size();
+  o.F = (uint32_t)(s->o_tri.size() / 3);
+  if (o.V) {
+    std::vector<float4> ox = to_float4(s->o_pos, s->o_invm);
+    XRT_CUDA_OK(dev_upload(&o.x0, ox));
+    XRT_CUDA_OK(dev_upload(&o.x, ox));
+    XRT_CUDA_OK(dev_upload(&o.x1, ox));
+    XRT_CUDA_OK(dev_alloc(&o.n, o.V));
+    XRT_CUDA_OK(dev_alloc(&o.n1, o.V));
+    XRT_CUDA_OK(dev_upload(&o.tri, s->o_tri));
+    std::vector<uint32_t> ovo, ovi, rt;
+    build_vf(s->o_tri, o.V, ovo, ovi);
+    build_rtri(s->o_tri, ovo, ovi, rt);  // ClothSolverBase::SetupRTriangle
+    XRT_CUDA_OK(dev_upload(&o.vf_off, ovo));
+    XRT_CUDA_OK(dev_upload(&o.vf_idx, ovi));
+    XRT_CUDA_OK(dev_upload(&o.rtri, rt));
+    if (bvh_alloc(&s->bvh, &s->bw, o.F) != 0) {
+      xrt_set_error(s, "BVH allocation failed");
+      return XRT_ERR_CUDA;
+    }
+  }
+  const size_t stage = std::max<size_t>(std::max(c.V, o.V), 1);
+  XRT_CUDA_OK(cudaMallocHost((void**)&s->stage, stage * sizeof(float4)));
+  XRT_CUDA_OK(dev_alloc(&s->d_stage, stage));
+  s->stage_elems = stage;
+  // ClothSolverUniversal::Start: obstacle normals, BVH UpdateData(0, false) + Construct
+  if (o.F) {
+    launch_normals(o.x0, o.n, o.tri, o.vf_off, o.vf_idx, o.V, s->st);
+    bvh_build(s->bvh, s->bw, o.x0, o.tri, o.F, s->p.morton_fast_div, s->st);
+  }
+  launch_normals(c.x0, c.n, c.tri, c.vf_off, c.vf_idx, c.V, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  XRT_CUDA_OK(cudaGetLastError());
+  s->finalized = true;
+  return XRT_OK;
+}
