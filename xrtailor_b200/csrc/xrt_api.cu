@@ -474,3 +474,202 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
   s->finalized = true;
   return XRT_OK;
 }
+
+// ---------------------------------------------------------------------------
+// the step path
+// ---------------------------------------------------------------------------
+
+// one pass of the inner loop after contact generation
+// (ClothSolverBase.cpp:215-237; binding->Solve is a no-op without bindings)
+static void enqueue_iteration(xrt_solver* s, int iteration, uint32_t* launches) {
+  const ClothDev& c = s->c;
+  cudaStream_t st = s->st;
+  for (uint32_t col = 0; col < c.n_sc; col++) {
+    launch_stretch_color(c, s->k, s->s_off[col], s->s_off[col + 1], iteration, s->atomic_s, st);
+    (*launches)++;
+  }
+  if (s->p.solve_bending)
+    for (uint32_t col = 0; col < c.n_bc; col++) {
+      launch_bend_color(c, s->k, s->b_off[col], s->b_off[col + 1], s->atomic_b, st);
+      (*launches)++;
+    }
+  if (s->p.geodesic_lra && c.n_lra) {
+    launch_lra(c, s->k, st);
+    (*launches)++;
+  }
+  if (s->o.F) {
+    launch_solve_contacts(c, s->bvh, s->k, st);  // RT solve, VF solve, EE solve
+    (*launches) += c.E ? 2 : 1;
+    launch_apply_deltas(c, s->k, st);
+    (*launches)++;
+  }
+}
+
+static void enqueue_collision_pass(xrt_solver* s, bool moved, int cnt, uint32_t* launches) {
+  if (!s->o.F) return;
+  cudaStream_t st = s->st;
+  if (moved) {
+    launch_interpolate(s->o, cnt, s->p.num_collision_passes, st);
+    launch_normals(s->o.x1, s->o.n1, s->o.tri, s->o.vf_off, s->o.vf_idx, s->o.V, st);
+    bvh_refit_midstep(s->bvh, s->bw, s->o.x1, s->o.n1, s->o.tri, s->p.bvh_tolerance, st);
+    (*launches) += 2 + bvh_refit_launches();
+  }
+  launch_generate_contacts(s->c, s->bvh, s->o.rtri, st);
+  (*launches) += s->c.E ? 2 : 1;
+}
+
+// SimulateSwift, ClothSolverBase.cpp:171-247
+static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
+  const xrt_params& p = s->p;
+  const ClothDev& c = s->c;
+  cudaStream_t st = s->st;
+  uint32_t launches = 0;
+  if (moved && s->o.F) {
+    // UpdateObstacleAnimationFrame: BVH UpdateData(0, ccd=false) + Construct on the
+    // frame-start positions (impl/smpl/ClothSolver.cpp:257-261)
+    bvh_build(s->bvh, s->bw, s->o.x0, s->o.tri, s->o.F, p.morton_fast_div, st);
+    launches += bvh_build_launches();
+  }
+  uint32_t frequency = (uint32_t)(p.num_substeps * p.num_iterations) / (uint32_t)p.num_collision_passes;
+  if (frequency == 0) frequency = 1;  // the reference divides by zero here
+  int cnt = 0;
+  for (int substep = 0; substep < p.num_substeps; substep++) {
+    launch_predict(c, s->k, st);
+    launches++;
+    if (p.enable_self_collision && substep % std::max(1, p.inter_leaved_hash) == 0) {
+      launch_hash(c, s->k, st);
+      launches += 5;
+    }
+    for (int it = 0; it < p.num_iterations; it++) {
+      if (p.enable_self_collision) {
+        launch_collide_particles(c, s->k, st);
+        launches += 2;
+      }
+      const uint32_t step = (uint32_t)(substep * p.num_iterations + it);
+      if (step % frequency == 0) {
+        enqueue_collision_pass(s, moved, cnt, &launches);
+        cnt++;
+      }
+      enqueue_iteration(s, it, &launches);
+    }
+    launch_finalize(c, s->k, st);
+    launches++;
+  }
+  // obstacle_->PredictedToPositions(); cloth_/obstacle_->UpdateNormals()
+  if (s->o.V) {
+    if (moved) cudaMemcpyAsync(s->o.x0, s->o.x, s->o.V * sizeof(float4), cudaMemcpyDeviceToDevice, st);
+    launch_normals(s->o.x0, s->o.n, s->o.tri, s->o.vf_off, s->o.vf_idx, s->o.V, st);
+    launches++;
+  }
+  launch_normals(c.x0, c.n, c.tri, c.vf_off, c.vf_idx, c.V, st);
+  launches++;
+  return launches;
+}
+
+static int ensure_graph(xrt_solver* s, int moved) {
+  if (s->graph[moved]) return XRT_OK;
+  cudaGraph_t g = nullptr;
+  XRT_CUDA_OK(cudaStreamBeginCapture(s->st, cudaStreamCaptureModeThreadLocal));
+  s->launches[moved] = enqueue_frame(s, moved != 0);
+  XRT_CUDA_OK(cudaStreamEndCapture(s->st, &g));
+  XRT_CUDA_OK(cudaGraphInstantiate(&s->graph[moved], g, 0));
+  cudaGraphDestroy(g);
+  return XRT_OK;
+}
+
+#define XRT_READY()                                            \
+  if (!s) return XRT_ERR_INVALID;                              \
+  XRT_REQUIRE(s->finalized, "call xrt_finalize_setup first");  \
+  XRT_CUDA_OK(cudaSetDevice(s->p.device))
+
+extern "C" int xrt_set_obstacle_target(xrt_solver* s, const float* xyz, size_t n_verts) {
+  XRT_READY();
+  XRT_REQUIRE(xyz && n_verts == s->o.V, "set_obstacle_target: vertex count differs from the obstacle");
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));  // staging buffer reuse
+  for (size_t i = 0; i < n_verts; i++)
+    s->stage[i] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], s->o_invm[i]);
+  XRT_CUDA_OK(cudaMemcpyAsync(s->o.x, s->stage, n_verts * sizeof(float4), cudaMemcpyHostToDevice, s->st));
+  s->target_pending = true;
+  return XRT_OK;
+}
+
+extern "C" int xrt_step_frame_async(xrt_solver* s) {
+  XRT_READY();
+  const int moved = s->target_pending ? 1 : 0;
+  int rc = ensure_graph(s, moved);
+  if (rc) return rc;
+  XRT_CUDA_OK(cudaGraphLaunch(s->graph[moved], s->st));
+  s->target_pending = false;
+  return XRT_OK;
+}
+
+extern "C" int xrt_sync(xrt_solver* s) {
+  XRT_READY();
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+
+extern "C" int xrt_step_frame(xrt_solver* s, float* solver_ms) {
+  XRT_READY();
+  const int moved = s->target_pending ? 1 : 0;
+  int rc = ensure_graph(s, moved);
+  if (rc) return rc;
+  XRT_CUDA_OK(cudaEventRecord(s->ev0, s->st));  // Timer::StartTimerGPU("Solver_Total")
+  XRT_CUDA_OK(cudaGraphLaunch(s->graph[moved], s->st));
+  XRT_CUDA_OK(cudaEventRecord(s->ev1, s->st));
+  s->target_pending = false;
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  if (solver_ms) XRT_CUDA_OK(cudaEventElapsedTime(solver_ms, s->ev0, s->ev1));
+  return XRT_OK;
+}
+
+// building blocks for the parity tests (eager launches of the same kernels)
+extern "C" int xrt_bvh_build_obstacle(xrt_solver* s) {
+  XRT_READY();
+  XRT_REQUIRE(s->o.F, "no obstacle");
+  bvh_build(s->bvh, s->bw, s->o.x0, s->o.tri, s->o.F, s->p.morton_fast_div, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+extern "C" int xrt_bvh_refit_obstacle(xrt_solver* s, int step) {
+  XRT_READY();
+  XRT_REQUIRE(s->o.F, "no obstacle");
+  launch_interpolate(s->o, step, s->p.num_collision_passes, s->st);
+  launch_normals(s->o.x1, s->o.n1, s->o.tri, s->o.vf_off, s->o.vf_idx, s->o.V, s->st);
+  bvh_refit_midstep(s->bvh, s->bw, s->o.x1, s->o.n1, s->o.tri, s->p.bvh_tolerance, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+extern "C" int xrt_generate_contacts(xrt_solver* s) {
+  XRT_READY();
+  XRT_REQUIRE(s->o.F, "no obstacle");
+  launch_generate_contacts(s->c, s->bvh, s->o.rtri, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+extern "C" int xrt_hash_particles(xrt_solver* s) {
+  XRT_READY();
+  launch_hash(s->c, s->k, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+extern "C" int xrt_predict(xrt_solver* s) {
+  XRT_READY();
+  launch_predict(s->c, s->k, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+extern "C" int xrt_solve_iteration(xrt_solver* s, int iteration) {
+  XRT_READY();
+  uint32_t l = 0;
+  if (s->p.enable_self_collision) launch_collide_particles(s->c, s->k, s->st);
+  enqueue_iteration(s, iteration, &l);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+extern "C" int xrt_finalize(xrt_solver* s) {
+  XRT_READY();
+  launch_finalize(s->c, s->k, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
