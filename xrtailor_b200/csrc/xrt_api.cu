@@ -673,3 +673,296 @@ extern "C" int xrt_finalize(xrt_solver* s) {
   XRT_CUDA_OK(cudaStreamSynchronize(s->st));
   return XRT_OK;
 }
+
+// ---------------------------------------------------------------------------
+// read-back, debug, teardown
+// ---------------------------------------------------------------------------
+
+static int download_xyz(xrt_solver* s, const float4* d, size_t n, float* out) {
+  if (!out || !n) return XRT_OK;
+  XRT_CUDA_OK(cudaMemcpyAsync(s->stage, d, n * sizeof(float4), cudaMemcpyDeviceToHost, s->st));
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  for (size_t i = 0; i < n; i++) {
+    out[3 * i] = s->stage[i].x;
+    out[3 * i + 1] = s->stage[i].y;
+    out[3 * i + 2] = s->stage[i].z;
+  }
+  return XRT_OK;
+}
+
+extern "C" int xrt_get_positions(xrt_solver* s, int which, float* xyz, float* nrm) {
+  XRT_READY();
+  XRT_REQUIRE(which == 0 || which == 1, "get_positions: which must be 0 (cloth) or 1 (obstacle)");
+  int rc;
+  if (which == 0) {
+    if ((rc = download_xyz(s, s->c.x0, s->c.V, xyz))) return rc;
+    return download_xyz(s, s->c.n, s->c.V, nrm);
+  }
+  if ((rc = download_xyz(s, s->o.x0, s->o.V, xyz))) return rc;
+  return download_xyz(s, s->o.n, s->o.V, nrm);
+}
+
+extern "C" int xrt_set_cloth_state(xrt_solver* s, const float* xyz, const float* vel) {
+  XRT_READY();
+  const size_t V = s->c.V;
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  if (xyz) {
+    for (size_t i = 0; i < V; i++) s->stage[i] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], s->c_invm[i]);
+    XRT_CUDA_OK(cudaMemcpyAsync(s->c.x0, s->stage, V * sizeof(float4), cudaMemcpyHostToDevice, s->st));
+    XRT_CUDA_OK(cudaMemcpyAsync(s->c.x, s->stage, V * sizeof(float4), cudaMemcpyHostToDevice, s->st));
+    XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  }
+  if (vel) {
+    for (size_t i = 0; i < V; i++) s->stage[i] = make_float4(vel[3 * i], vel[3 * i + 1], vel[3 * i + 2], 0.f);
+    XRT_CUDA_OK(cudaMemcpyAsync(s->c.v, s->stage, V * sizeof(float4), cudaMemcpyHostToDevice, s->st));
+    XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  }
+  return XRT_OK;
+}
+
+// algorithmic bytes of one frame, SoA-ideal, SURVEY.md section 8(d) with the
+// exact counts of this scene (see DESIGN.md "Roofline accounting")
+static double frame_bytes(const xrt_solver* s, bool moved) {
+  const xrt_params& p = s->p;
+  const double V = s->c.V, E = s->c.E, Fo = s->o.F, Vo = s->o.V;
+  const double ns = s->c.n_stretch, nb = p.solve_bending ? s->c.n_bend : 0, nl = p.geodesic_lra ? s->c.n_lra : 0;
+  const double S = p.num_substeps, N = p.num_iterations, C = p.num_collision_passes;
+  double per_iter = 84.0 * ns + 160.0 * nb + 60.0 * nl;
+  if (Fo) per_iter += 96.0 * V + 96.0 * V + 120.0 * E + 52.0 * V;  // VF-CCD, VF-DCD, EE solves, apply deltas
+  double b = S * N * per_iter + S * (64.0 + 64.0) * V;              // + predict + finalize
+  if (Fo) b += C * (48.0 * V + 48.0 * V + 88.0 * E);                // contact generation, compulsory traffic only
+  if (moved && Fo) {
+    b += 84.0 * Fo + 24.0 * Fo + 8.0 * Fo * 8.0 + 40.0 * (2 * Fo - 1) + 8.0 * Fo;  // BVH build
+    b += C * (36.0 * Fo + 24.0 * (2 * Fo - 1) + 32.0 * Vo);                          // refit + interpolate
+  }
+  if (p.enable_self_collision) {
+    const double K = 8.0;  // mean neighbour count assumed by SURVEY.md 8(d)
+    b += S * N * ((4.0 * K + 16.0 * K + 36.0) * V + 52.0 * V);
+  }
+  return b;
+}
+
+extern "C" int xrt_debug_get(xrt_solver* s, int what, void* dst, size_t* bytes) {
+  XRT_READY();
+  XRT_REQUIRE(bytes, "debug_get: bytes is null");
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  const size_t F = s->bvh.n_obj, V = s->c.V, E = s->c.E;
+  const void* src = nullptr;
+  size_t need = 0;
+  std::vector<float> tmp;
+  std::vector<uint32_t> tmpu;
+  xrt_stats stats;
+  switch (what) {
+    case XRT_DBG_MORTON: src = s->bvh.morton; need = F * 4; break;
+    case XRT_DBG_SORTED_OBJECT: src = s->bvh.sorted_obj; need = F * 4; break;
+    case XRT_DBG_NODES: src = s->bvh.nodes; need = F ? (2 * F - 1) * sizeof(BVNode) : 0; break;
+    case XRT_DBG_ESCAPE_INT: src = s->bvh.esc_int; need = F ? (F - 1) * 4 : 0; break;
+    case XRT_DBG_ESCAPE_EXT: src = s->bvh.esc_ext; need = F * 4; break;
+    case XRT_DBG_VF_CONTACTS: src = s->c.vf; need = V * sizeof(VFContact); break;
+    case XRT_DBG_RT_CONTACTS: src = s->c.rt; need = V * sizeof(VFContact); break;
+    case XRT_DBG_EE_CONTACTS: src = s->c.ee; need = E * sizeof(EEContact); break;
+    case XRT_DBG_NEIGHBORS: src = s->c.neighbors; need = V * (size_t)s->p.max_num_neighbors * 4; break;
+    case XRT_DBG_RTRI: src = s->o.rtri; need = (size_t)s->o.F * 4; break;
+    case XRT_DBG_VF_CAND_COUNT: src = s->c.cnt_vf; need = V * 4; break;
+    case XRT_DBG_RT_CAND_COUNT: src = s->c.cnt_rt; need = V * 4; break;
+    case XRT_DBG_EE_CAND_COUNT: src = s->c.cnt_ee; need = E * 4; break;
+    case XRT_DBG_COLORS_STRETCH: need = s->s_color.size() * 4; break;
+    case XRT_DBG_COLORS_BEND: need = s->b_color.size() * 4; break;
+    case XRT_DBG_AABBS: need = F ? (2 * F - 1) * 6 * sizeof(float) : 0; break;
+    case XRT_DBG_PREDICTED: case XRT_DBG_VELOCITY: need = V * 3 * sizeof(float); break;
+    case XRT_DBG_OBSTACLE_PRED: need = (size_t)s->o.F * 9 * sizeof(float); break;
+    case XRT_DBG_PARTICLE_HASH: need = V * 8; break;
+    case XRT_DBG_STATS: need = sizeof(xrt_stats); break;
+    default: xrt_set_error(s, "debug_get: unknown item %d", what); return XRT_ERR_INVALID;
+  }
+  const size_t cap = *bytes;
+  *bytes = need;
+  if (!dst) return XRT_OK;
+  XRT_REQUIRE(cap >= need, "debug_get: destination too small");
+  if (src) {
+    if (need) XRT_CUDA_OK(cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
+    return XRT_OK;
+  }
+  switch (what) {
+    case XRT_DBG_COLORS_STRETCH: memcpy(dst, s->s_color.data(), need); break;
+    case XRT_DBG_COLORS_BEND: memcpy(dst, s->b_color.data(), need); break;
+    case XRT_DBG_AABBS: {
+      std::vector<TNode> t(2 * F - 1);
+      XRT_CUDA_OK(cudaMemcpy(t.data(), s->bvh.tnodes, t.size() * sizeof(TNode), cudaMemcpyDeviceToHost));
+      float* o = (float*)dst;
+      for (size_t i = 0; i < t.size(); i++) {
+        o[6 * i] = t[i].lx; o[6 * i + 1] = t[i].ly; o[6 * i + 2] = t[i].lz;
+        o[6 * i + 3] = t[i].ux; o[6 * i + 4] = t[i].uy; o[6 * i + 5] = t[i].uz;
+      }
+      break;
+    }
+    case XRT_DBG_PREDICTED: return download_xyz(s, s->c.x, V, (float*)dst);
+    case XRT_DBG_VELOCITY: return download_xyz(s, s->c.v, V, (float*)dst);
+    case XRT_DBG_OBSTACLE_PRED: {
+      std::vector<float4> t(3 * (size_t)s->o.F);
+      XRT_CUDA_OK(cudaMemcpy(t.data(), s->bvh.pred, t.size() * sizeof(float4), cudaMemcpyDeviceToHost));
+      float* o = (float*)dst;
+      for (size_t i = 0; i < t.size(); i++) { o[3 * i] = t[i].x; o[3 * i + 1] = t[i].y; o[3 * i + 2] = t[i].z; }
+      break;
+    }
+    case XRT_DBG_PARTICLE_HASH:
+      XRT_CUDA_OK(cudaMemcpy(dst, s->c.p_hash, V * 4, cudaMemcpyDeviceToHost));
+      XRT_CUDA_OK(cudaMemcpy((char*)dst + V * 4, s->c.p_index, V * 4, cudaMemcpyDeviceToHost));
+      break;
+    case XRT_DBG_STATS: {
+      memset(&stats, 0, sizeof(stats));
+      std::vector<float> x(3 * V);
+      int rc = download_xyz(s, s->c.x0, V, x.data());
+      if (rc) return rc;
+      auto P = [&](uint32_t i) { return f3{x[3 * i], x[3 * i + 1], x[3 * i + 2]}; };
+      double acc = 0, mx = 0;
+      const size_t ns = s->s_rest.size();
+      for (size_t i = 0; i < ns; i++) {
+        const double r = s->s_rest[i];
+        const double e = r > 0 ? (len3(P(s->s_idx[2 * i]) - P(s->s_idx[2 * i + 1])) - r) / r : 0.0;
+        acc += e * e;
+        mx = std::max(mx, std::fabs(e));
+      }
+      stats.stretch_rms = ns ? std::sqrt(acc / ns) : 0;
+      stats.stretch_max = mx;
+      acc = 0;
+      const size_t nb = s->b_theta.size();
+      for (size_t i = 0; i < nb; i++) {
+        const uint32_t* q = &s->b_idx[4 * i];
+        const f3 p1 = P(q[0]), p2 = P(q[1]) - p1, p3 = P(q[2]) - p1, p4 = P(q[3]) - p1;
+        const f3 n1 = normalize3(cross3(p2, p3)), n2 = normalize3(cross3(p2, p4));
+        const float d = clampf(dot3(n1, n2), 0.f, 1.f);
+        const double e = std::isnan(d) ? 0.0 : std::acos((double)d) - s->b_theta[i];
+        acc += e * e;
+      }
+      stats.bend_rms = nb ? std::sqrt(acc / nb) : 0;
+      if (s->o.F) {
+        std::vector<VFContact> vf(V);
+        std::vector<float4> pr(3 * (size_t)s->o.F);
+        XRT_CUDA_OK(cudaMemcpy(vf.data(), s->c.vf, V * sizeof(VFContact), cudaMemcpyDeviceToHost));
+        XRT_CUDA_OK(cudaMemcpy(pr.data(), s->bvh.pred, pr.size() * sizeof(float4), cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < V; i++) {
+          if (vf[i].index < 0) continue;
+          const size_t o = 3 * (size_t)vf[i].index;
+          const f3 nn = face_normal(mk3(pr[o]), mk3(pr[o + 1]), mk3(pr[o + 2]));
+          if (dot3(nn, P((uint32_t)i) - f3{vf[i].q[0], vf[i].q[1], vf[i].q[2]}) < 0.f) stats.vf_penetrations++;
+        }
+      }
+      stats.n_stretch_colors = s->c.n_sc;
+      stats.n_bend_colors = s->c.n_bc;
+      const int moved = s->graph[1] && !s->graph[0] ? 1 : 0;
+      stats.launches_per_frame = s->launches[moved];
+      stats.bytes_per_frame = frame_bytes(s, moved != 0);
+      memcpy(dst, &stats, sizeof(stats));
+      break;
+    }
+    default: break;
+  }
+  return XRT_OK;
+}
+
+extern "C" int xrt_debug_candidates(xrt_solver* s, int kind, uint32_t* offsets, uint32_t* items, size_t* n_items) {
+  XRT_READY();
+  XRT_REQUIRE(kind >= 0 && kind <= 2 && offsets && n_items, "debug_candidates: bad argument");
+  XRT_REQUIRE(s->o.F, "no obstacle");
+  const uint32_t n = kind == 2 ? s->c.E : s->c.V;
+  uint32_t* d_counts = kind == 0 ? s->c.cnt_vf : (kind == 1 ? s->c.cnt_rt : s->c.cnt_ee);
+  launch_candidates(s->c, s->bvh, kind, nullptr, nullptr, d_counts, s->st);
+  std::vector<uint32_t> cnt(n);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  if (n) XRT_CUDA_OK(cudaMemcpy(cnt.data(), d_counts, n * 4, cudaMemcpyDeviceToHost));
+  offsets[0] = 0;
+  for (uint32_t i = 0; i < n; i++) offsets[i + 1] = offsets[i] + cnt[i];
+  const size_t total = offsets[n];
+  const size_t cap = *n_items;
+  *n_items = total;
+  if (!items) return XRT_OK;
+  XRT_REQUIRE(cap >= total, "debug_candidates: items too small");
+  uint32_t *d_off = nullptr, *d_items = nullptr;
+  XRT_CUDA_OK(cudaMalloc((void**)&d_off, (n + 1) * 4));
+  XRT_CUDA_OK(cudaMalloc((void**)&d_items, (total ? total : 1) * 4));
+  XRT_CUDA_OK(cudaMemcpy(d_off, offsets, (n + 1) * 4, cudaMemcpyHostToDevice));
+  launch_candidates(s->c, s->bvh, kind, d_off, d_items, nullptr, s->st);
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  if (total) XRT_CUDA_OK(cudaMemcpy(items, d_items, total * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_off);
+  cudaFree(d_items);
+  return XRT_OK;
+}
+
+extern "C" void xrt_destroy(xrt_solver* s) {
+  if (!s) return;
+  cudaSetDevice(s->p.device);
+  if (s->st) cudaStreamSynchronize(s->st);
+  for (int i = 0; i < 2; i++)
+    if (s->graph[i]) cudaGraphExecDestroy(s->graph[i]);
+  ClothDev& c = s->c;
+  void* ptrs[] = {c.x0, c.x, c.v, c.n, c.rest, c.tri, c.edge, c.vf_off, c.vf_idx, c.s_idx, c.s_rest, c.s_lambda,
+                  c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
+                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf,
+                  c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
+                  s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage};
+  for (void* p : ptrs) cudaFree(p);
+  if (s->bvh.n_obj) bvh_free(&s->bvh, &s->bw);
+  if (s->stage) cudaFreeHost(s->stage);
+  if (s->ev0) cudaEventDestroy(s->ev0);
+  if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->st) cudaStreamDestroy(s->st);
+  delete s;
+}
+
+extern "C" int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts, const uint32_t* indices,
+                                        uint32_t n_faces, int morton_fast_div, int device, uint32_t* morton,
+                                        uint32_t* sorted_object, uint32_t* nodes, float* aabbs, int32_t* esc_int,
+                                        int32_t* esc_ext, float* build_ms) {
+  if (!positions || !indices || !n_verts || !n_faces) return XRT_ERR_INVALID;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) return XRT_ERR_CUDA;
+  if (cudaSetDevice(device) != cudaSuccess) return XRT_ERR_CUDA;
+  std::vector<float4> hx(n_verts);
+  for (uint32_t i = 0; i < n_verts; i++) hx[i] = make_float4(positions[3 * i], positions[3 * i + 1], positions[3 * i + 2], 0.f);
+  float4* dx = nullptr;
+  uint32_t* dt = nullptr;
+  DevBVH b{};
+  BvhWork w;
+  cudaEvent_t e0, e1;
+  int rc = XRT_OK;
+  const size_t F = n_faces;
+  if (cudaMalloc((void**)&dx, n_verts * sizeof(float4)) != cudaSuccess ||
+      cudaMalloc((void**)&dt, 3 * F * 4) != cudaSuccess || bvh_alloc(&b, &w, n_faces) != 0)
+    rc = XRT_ERR_CUDA;
+  if (rc == XRT_OK) {
+    cudaMemcpy(dx, hx.data(), n_verts * sizeof(float4), cudaMemcpyHostToDevice);
+    cudaMemcpy(dt, indices, 3 * F * 4, cudaMemcpyHostToDevice);
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    bvh_build(b, w, dx, dt, n_faces, morton_fast_div, 0);  // warm-up (also sizes cub state)
+    cudaEventRecord(e0, 0);
+    bvh_build(b, w, dx, dt, n_faces, morton_fast_div, 0);
+    cudaEventRecord(e1, 0);
+    if (cudaDeviceSynchronize() != cudaSuccess) rc = XRT_ERR_CUDA;
+    if (rc == XRT_OK && build_ms) cudaEventElapsedTime(build_ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+  }
+  if (rc == XRT_OK) {
+    if (morton) cudaMemcpy(morton, b.morton, F * 4, cudaMemcpyDeviceToHost);
+    if (sorted_object) cudaMemcpy(sorted_object, b.sorted_obj, F * 4, cudaMemcpyDeviceToHost);
+    if (nodes) cudaMemcpy(nodes, b.nodes, (2 * F - 1) * sizeof(BVNode), cudaMemcpyDeviceToHost);
+    if (esc_int && F > 1) cudaMemcpy(esc_int, b.esc_int, (F - 1) * 4, cudaMemcpyDeviceToHost);
+    if (esc_ext) cudaMemcpy(esc_ext, b.esc_ext, F * 4, cudaMemcpyDeviceToHost);
+    if (aabbs) {
+      std::vector<TNode> t(2 * F - 1);
+      cudaMemcpy(t.data(), b.tnodes, t.size() * sizeof(TNode), cudaMemcpyDeviceToHost);
+      for (size_t i = 0; i < t.size(); i++) {
+        aabbs[6 * i] = t[i].lx; aabbs[6 * i + 1] = t[i].ly; aabbs[6 * i + 2] = t[i].lz;
+        aabbs[6 * i + 3] = t[i].ux; aabbs[6 * i + 4] = t[i].uy; aabbs[6 * i + 5] = t[i].uz;
+      }
+    }
+    if (cudaGetLastError() != cudaSuccess) rc = XRT_ERR_CUDA;
+  }
+  cudaFree(dx);
+  cudaFree(dt);
+  if (b.n_obj) bvh_free(&b, &w);
+  return rc;
+}
