@@ -1,0 +1,518 @@
+/*
+ * xrt_oracle.c — CPU restatement of XRTailor's Swift-mode hot path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  Imported by tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs as the checker; the product
+ * (xrtailor_b200/) never links or calls it.
+ *
+ * Parity status: the reference (openxrlab/xrtailor @ 4eaf5c3) has no tests,
+ * golden vectors or CPU path, so this restatement is
+ * pinned against (a) the reference's own __host__ __device__ helpers compiled
+ * for the host from /root/reference (oracle/_ref, see oracle/Makefile) and
+ * (b) hand-derived known answers in tests/golden/.  Float position parity
+ * against the reference's CUDA itself can only run on a GPU box.
+ *
+ * Every function cites the reference file:line it follows (paths relative to
+ * /root/reference/xrtailor/).  Plain C, scalar, one thread, IEEE arithmetic
+ * (the reference's CUDA build uses --use_fast_math; differences are a few ulp).
+ */
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define EPS 1e-6f            /* core/Scalar.hpp:39 */
+#define SCALAR_MAX FLT_MAX   /* core/Scalar.cuh:10 */
+#define MAX_HITS 256         /* core/Common.cuh:23 LBVH_MAX_BUFFER_SIZE */
+
+typedef struct { float x, y, z; } v3;
+static v3 V(float x, float y, float z) { v3 r = {x, y, z}; return r; }
+static v3 add(v3 a, v3 b) { return V(a.x + b.x, a.y + b.y, a.z + b.z); }
+static v3 sub(v3 a, v3 b) { return V(a.x - b.x, a.y - b.y, a.z - b.z); }
+static v3 mul(v3 a, float s) { return V(a.x * s, a.y * s, a.z * s); }
+static v3 divs(v3 a, float s) { return V(a.x / s, a.y / s, a.z / s); }
+static v3 neg(v3 a) { return V(-a.x, -a.y, -a.z); }
+static float dot(v3 a, v3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+static v3 cross(v3 a, v3 b) { return V(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
+static float len(v3 a) { return sqrtf(dot(a, a)); }
+static v3 normalize(v3 a) { return mul(a, 1.0f / sqrtf(dot(a, a))); } /* glm::normalize */
+static float fmin2(float a, float b) { return a < b ? a : b; }        /* math/MathFunctions.cuh:24 */
+static float fmax2(float a, float b) { return a > b ? a : b; }        /* math/MathFunctions.cuh:39 */
+static float clampf(float x, float a, float b) { return x < a ? a : (x > b ? b : x); } /* :75 */
+static v3 ld3(const float* p, uint32_t i) { return V(p[3 * i], p[3 * i + 1], p[3 * i + 2]); }
+static void st3(float* p, uint32_t i, v3 a) { p[3 * i] = a.x; p[3 * i + 1] = a.y; p[3 * i + 2] = a.z; }
+static v3 face_normal(v3 a, v3 b, v3 c) { return normalize(cross(sub(b, a), sub(c, a))); } /* math/MathFunctions.cu:14 */
+
+/* ------------------------------------------------------------------------- */
+/* LBVH: physics/broad_phase/lbvh/BVH.cu                                      */
+/* ------------------------------------------------------------------------- */
+
+/* expand_bits, BVH.cu:18-24 */
+uint32_t oracle_expand_bits(uint32_t v) {
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+
+static uint32_t quant(float t) {
+  t = fmin2(fmax2(t * 1024.0f, 0.0f), 1023.0f);
+  if (t != t) return 0; /* NaN (flat scene axis): the GPU cast gives 0 */
+  return (uint32_t)t;
+}
+/* morton_code, BVH.cu:27-40 */
+uint32_t oracle_morton_code(float x, float y, float z) {
+  return oracle_expand_bits(quant(x)) * 4 + oracle_expand_bits(quant(y)) * 2 + oracle_expand_bits(quant(z));
+}
+
+typedef struct {
+  uint32_t F;
+  uint32_t* morton;  /* [F] sorted */
+  uint32_t* object;  /* [F] */
+  uint32_t* nodes;   /* [4*(2F-1)] parent,left,right,object */
+  float* aabb;       /* [6*(2F-1)] */
+  int32_t* esc_int;  /* [F-1] */
+  int32_t* esc_ext;  /* [F] */
+  float* pred;       /* [9*F] primitive pred1..3 (object order) */
+  float* v;          /* [9*F] primitive v1..3 */
+  int used64;        /* duplicate Morton codes -> 64-bit keys, BVH.cu:671-683 */
+} OBvh;
+
+static int clz32(uint32_t x) { return x ? __builtin_clz(x) : 32; }
+static int clz64(uint64_t x) { return x ? __builtin_clzll(x) : 64; }
+
+/* determine_range, BVH.cu:57-105 (32-bit) and :106-156 (64-bit) through one key array */
+static int key_delta(const uint64_t* key, int wide, int n, int i, int j) {
+  if (j < 0 || j >= n) return -1;
+  return wide ? clz64(key[i] ^ key[j]) : clz32((uint32_t)key[i] ^ (uint32_t)key[j]);
+}
+static void determine_range(const uint64_t* key, int wide, int n, int idx, int* first, int* last) {
+  if (idx == 0) { *first = 0; *last = n - 1; return; }
+  const int L = key_delta(key, wide, n, idx, idx - 1), R = key_delta(key, wide, n, idx, idx + 1);
+  const int d = R > L ? 1 : -1;
+  const int dmin = L < R ? L : R;
+  int lmax = 2;
+  int delta = key_delta(key, wide, n, idx, idx + d * lmax);
+  while (delta > dmin) {
+    lmax <<= 1;
+    delta = key_delta(key, wide, n, idx, idx + d * lmax);
+  }
+  int l = 0;
+  for (int t = lmax >> 1; t > 0; t >>= 1) {
+    delta = key_delta(key, wide, n, idx, idx + (l + t) * d);
+    if (delta > dmin) l += t;
+  }
+  int j = idx + l * d;
+  if (d < 0) { int t = idx; idx = j; j = t; }
+  *first = idx; *last = j;
+}
+/* find_split, BVH.cu:158-210 */
+static int find_split(const uint64_t* key, int wide, int first, int last) {
+  if (key[first] == key[last]) return (first + last) >> 1;
+  const int dnode = wide ? clz64(key[first] ^ key[last]) : clz32((uint32_t)key[first] ^ (uint32_t)key[last]);
+  int split = first, stride = last - first;
+  do {
+    stride = (stride + 1) >> 1;
+    const int mid = split + stride;
+    if (mid < last) {
+      const int d = wide ? clz64(key[first] ^ key[mid]) : clz32((uint32_t)key[first] ^ (uint32_t)key[mid]);
+      if (d > dnode) split = mid;
+    }
+  } while (stride > 1);
+  return split;
+}
+
+typedef struct { uint32_t key, idx; } SortItem;
+static int cmp_item(const void* a, const void* b) {
+  const SortItem *x = (const SortItem*)a, *y = (const SortItem*)b;
+  if (x->key != y->key) return x->key < y->key ? -1 : 1;
+  return x->idx < y->idx ? -1 : (x->idx > y->idx); /* stable: initial indices ascend */
+}
+
+void oracle_bvh_free(OBvh* b) {
+  if (!b) return;
+  free(b->morton); free(b->object); free(b->nodes); free(b->aabb);
+  free(b->esc_int); free(b->esc_ext); free(b->pred); free(b->v);
+  free(b);
+}
+
+/* BVH::UpdateData (BVH.cu:565-573, UpdateObjects_Kernel :382-421) + BVH::Construct (:618-722).
+ * x0 / x / n: float[3*V]; tol = torlence; ccd selects pred = x + tol*n. */
+OBvh* oracle_bvh_build(const float* x0, const float* x, const float* nrm, const uint32_t* tri, uint32_t F,
+                       float tol, int ccd) {
+  OBvh* b = (OBvh*)calloc(1, sizeof(OBvh));
+  const uint32_t NN = 2 * F - 1, NI = F - 1;
+  b->F = F;
+  b->morton = (uint32_t*)malloc(4 * F);
+  b->object = (uint32_t*)malloc(4 * F);
+  b->nodes = (uint32_t*)malloc(16 * (size_t)NN);
+  b->aabb = (float*)malloc(24 * (size_t)NN);
+  b->esc_int = (int32_t*)malloc(4 * (F > 1 ? NI : 1));
+  b->esc_ext = (int32_t*)malloc(4 * F);
+  b->pred = (float*)malloc(36 * (size_t)F);
+  b->v = (float*)malloc(36 * (size_t)F);
+  float* box = (float*)malloc(24 * (size_t)F);
+  float whole[6] = {INFINITY, INFINITY, INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  for (uint32_t i = 0; i < F; i++) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int k = 0; k < 3; k++) {
+      const uint32_t vi = tri[3 * i + k];
+      v3 nn = nrm ? ld3(nrm, vi) : V(0, 0, 0);
+      v3 a = tol != 0.0f ? add(ld3(x0, vi), mul(nn, tol)) : ld3(x0, vi);
+      v3 p = ccd ? (tol != 0.0f ? add(ld3(x, vi), mul(nn, tol)) : ld3(x, vi)) : a;
+      st3(b->v, 3 * i + k, a);
+      st3(b->pred, 3 * i + k, p);
+      const float c[6] = {a.x, a.y, a.z, p.x, p.y, p.z};
+      for (int q = 0; q < 6; q++) {  /* InitAABBs_Kernel, BVH.cu:423-462 with scr = 0 */
+        lo[q % 3] = fmin2(lo[q % 3], c[q]);
+        hi[q % 3] = fmax2(hi[q % 3], c[q]);
+      }
+    }
+    for (int k = 0; k < 3; k++) {
+      box[6 * i + k] = lo[k]; box[6 * i + 3 + k] = hi[k];
+      whole[k] = fmin2(whole[k], lo[k]); whole[3 + k] = fmax2(whole[3 + k], hi[k]); /* thrust::reduce, :642 */
+    }
+  }
+  /* ComputeMortons_Kernel, BVH.cu:464-481 */
+  SortItem* items = (SortItem*)malloc(sizeof(SortItem) * F);
+  for (uint32_t i = 0; i < F; i++) {
+    float p[3];
+    for (int k = 0; k < 3; k++) {
+      p[k] = 0.5f * (box[6 * i + k] + box[6 * i + 3 + k]);
+      p[k] -= whole[k];
+      p[k] /= (whole[3 + k] - whole[k]);
+    }
+    items[i].key = oracle_morton_code(p[0], p[1], p[2]);
+    items[i].idx = i;
+  }
+  qsort(items, F, sizeof(SortItem), cmp_item); /* stable_sort_by_key, :666 */
+  int unique = 1;
+  for (uint32_t i = 0; i < F; i++) {
+    b->morton[i] = items[i].key;
+    b->object[i] = items[i].idx;
+    if (i && items[i].key == items[i - 1].key) unique = 0;
+  }
+  b->used64 = !unique;
+  uint64_t* key = (uint64_t*)malloc(8 * (size_t)F);
+  for (uint32_t i = 0; i < F; i++)
+    key[i] = unique ? (uint64_t)b->morton[i] : (((uint64_t)b->morton[i]) << 32) | b->object[i]; /* :675-682 */
+  free(items);
+  /* default nodes / boxes, leaf nodes: :684-693 */
+  for (uint32_t i = 0; i < NN; i++) {
+    b->nodes[4 * i] = b->nodes[4 * i + 1] = b->nodes[4 * i + 2] = b->nodes[4 * i + 3] = 0xFFFFFFFFu;
+    for (int k = 0; k < 3; k++) { b->aabb[6 * i + k] = INFINITY; b->aabb[6 * i + 3 + k] = -INFINITY; }
+  }
+  for (uint32_t i = 0; i < F; i++) {
+    b->nodes[4 * (NI + i) + 3] = b->object[i];
+    memcpy(b->aabb + 6 * (size_t)(NI + i), box + 6 * (size_t)b->object[i], 24); /* AABBs travel with the sort */
+  }
+  /* ConstructInternalNodes{32,64}Bits_Kernel, :275-318 */
+  for (uint32_t idx = 0; idx < NI; idx++) {
+    int first, last;
+    determine_range(key, !unique, (int)F, (int)idx, &first, &last);
+    const int gamma = find_split(key, !unique, first, last);
+    uint32_t L = (uint32_t)gamma, R = (uint32_t)gamma + 1;
+    if ((first < last ? first : last) == gamma) L += NI;
+    if ((first > last ? first : last) == gamma + 1) R += NI;
+    b->nodes[4 * idx + 1] = L;
+    b->nodes[4 * idx + 2] = R;
+    b->nodes[4 * L] = idx;
+    b->nodes[4 * R] = idx;
+  }
+  /* AssignAABBAtomic_Kernel, :540-556: every node pushes its box into all ancestors */
+  for (uint32_t i = NI; i < NN; i++) {
+    uint32_t parent = b->nodes[4 * i];
+    while (parent != 0xFFFFFFFFu) {
+      for (int k = 0; k < 3; k++) {
+        b->aabb[6 * parent + k] = fmin2(b->aabb[6 * parent + k], b->aabb[6 * i + k]);
+        b->aabb[6 * parent + 3 + k] = fmax2(b->aabb[6 * parent + 3 + k], b->aabb[6 * i + 3 + k]);
+      }
+      parent = b->nodes[4 * parent];
+    }
+  }
+  /* BuildInternalEscapeIndexTable_Kernel, :212-249 */
+  for (uint32_t idx = 0; idx < NI; idx++) {
+    const uint32_t parent = b->nodes[4 * idx];
+    int32_t e = -1;
+    if (parent != 0xFFFFFFFFu) {
+      if (idx == b->nodes[4 * parent + 1]) e = (int32_t)b->nodes[4 * parent + 2];
+      else {
+        uint32_t cur = parent;
+        for (;;) {
+          const uint32_t pp = b->nodes[4 * cur];
+          if (pp == 0xFFFFFFFFu) { e = -1; break; }
+          if (cur == b->nodes[4 * pp + 2]) cur = pp;
+          else { e = (int32_t)b->nodes[4 * pp + 2]; break; }
+        }
+      }
+    }
+    b->esc_int[idx] = e;
+  }
+  /* BuildExternalEscapeIndexTable_Kernel, :251-264 */
+  for (uint32_t i = 0; i < F; i++) {
+    const uint32_t parent = b->nodes[4 * (NI + i)];
+    if (parent == 0xFFFFFFFFu) { b->esc_ext[i] = -1; continue; } /* F == 1 */
+    if (NI + i == b->nodes[4 * parent + 1]) b->esc_ext[i] = (int32_t)b->nodes[4 * parent + 2];
+    else b->esc_ext[i] = b->esc_int[parent];
+  }
+  free(key);
+  free(box);
+  return b;
+}
+
+/* BVH::RefitMidstep, BVH.cu:770-818: pred = x1 + tol*n1; leaf boxes only grow;
+ * internal boxes are recomputed as the merge of their children (AssignAABBCAS). */
+static void refit_internal(OBvh* b, uint32_t node) {
+  if (b->nodes[4 * node + 3] != 0xFFFFFFFFu) return;
+  const uint32_t L = b->nodes[4 * node + 1], R = b->nodes[4 * node + 2];
+  refit_internal(b, L);
+  refit_internal(b, R);
+  for (int k = 0; k < 3; k++) {
+    b->aabb[6 * node + k] = fminf(b->aabb[6 * L + k], b->aabb[6 * R + k]);
+    b->aabb[6 * node + 3 + k] = fmaxf(b->aabb[6 * L + 3 + k], b->aabb[6 * R + 3 + k]);
+  }
+}
+void oracle_bvh_refit_midstep(OBvh* b, const float* x1, const float* n1, const uint32_t* tri, float tol) {
+  const uint32_t NI = b->F - 1;
+  for (uint32_t i = 0; i < b->F; i++) {
+    const uint32_t o = b->nodes[4 * (NI + i) + 3];
+    for (int k = 0; k < 3; k++) {
+      const uint32_t vi = tri[3 * o + k];
+      const v3 p = add(ld3(x1, vi), mul(ld3(n1, vi), tol));
+      st3(b->pred, 3 * o + k, p);
+      float* bb = b->aabb + 6 * (size_t)(NI + i);
+      bb[0] = fmin2(bb[0], p.x); bb[1] = fmin2(bb[1], p.y); bb[2] = fmin2(bb[2], p.z);
+      bb[3] = fmax2(bb[3], p.x); bb[4] = fmax2(bb[4], p.y); bb[5] = fmax2(bb[5], p.z);
+    }
+  }
+  if (b->F > 1) refit_internal(b, 0);
+}
+
+/* accessors for ctypes */
+uint32_t* oracle_bvh_morton(OBvh* b) { return b->morton; }
+uint32_t* oracle_bvh_object(OBvh* b) { return b->object; }
+uint32_t* oracle_bvh_nodes(OBvh* b) { return b->nodes; }
+float* oracle_bvh_aabb(OBvh* b) { return b->aabb; }
+int32_t* oracle_bvh_esc_int(OBvh* b) { return b->esc_int; }
+int32_t* oracle_bvh_esc_ext(OBvh* b) { return b->esc_ext; }
+float* oracle_bvh_pred(OBvh* b) { return b->pred; }
+int oracle_bvh_used64(OBvh* b) { return b->used64; }
+
+/* ------------------------------------------------------------------------- */
+/* Bounds tests: physics/broad_phase/Bounds.cu                                */
+/* ------------------------------------------------------------------------- */
+
+/* Bounds::Overlap(const Vector3&), Bounds.cu:126-131 */
+int oracle_overlap_point(const float* bb, v3 p) {
+  return p.x > bb[0] && p.x < bb[3] && p.y > bb[1] && p.y < bb[4] && p.z > bb[2] && p.z < bb[5];
+}
+/* GetIntersection, Bounds.cu:132-140 */
+static int get_isect(float d1, float d2, v3 p1, v3 p2, v3* hit) {
+  if ((d1 * d2) >= 0.0f) return 0;
+  if (d1 == d2) return 0;
+  *hit = add(p1, mul(sub(p2, p1), (-d1 / (d2 - d1))));
+  return 1;
+}
+/* InBox, Bounds.cu:141-150 */
+static int in_box(v3 h, const float* bb, int axis) {
+  if (axis == 1 && h.z > bb[2] && h.z < bb[5] && h.y > bb[1] && h.y < bb[4]) return 1;
+  if (axis == 2 && h.z > bb[2] && h.z < bb[5] && h.x > bb[0] && h.x < bb[3]) return 1;
+  if (axis == 3 && h.x > bb[0] && h.x < bb[3] && h.y > bb[1] && h.y < bb[4]) return 1;
+  return 0;
+}
+/* Bounds::Overlap(p1, p2, hit), Bounds.cu:151-183 */
+int oracle_overlap_segment(const float* bb, v3 p1, v3 p2) {
+  v3 hit;
+  if (p2.x < bb[0] && p1.x < bb[0]) return 0;
+  if (p2.x > bb[3] && p1.x > bb[3]) return 0;
+  if (p2.y < bb[1] && p1.y < bb[1]) return 0;
+  if (p2.y > bb[4] && p1.y > bb[4]) return 0;
+  if (p2.z < bb[2] && p1.z < bb[2]) return 0;
+  if (p2.z > bb[5] && p1.z > bb[5]) return 0;
+  if (oracle_overlap_point(bb, p1)) return 1;
+  if ((get_isect(p1.x - bb[0], p2.x - bb[0], p1, p2, &hit) && in_box(hit, bb, 1)) ||
+      (get_isect(p1.y - bb[1], p2.y - bb[1], p1, p2, &hit) && in_box(hit, bb, 2)) ||
+      (get_isect(p1.z - bb[2], p2.z - bb[2], p1, p2, &hit) && in_box(hit, bb, 3)) ||
+      (get_isect(p1.x - bb[3], p2.x - bb[3], p1, p2, &hit) && in_box(hit, bb, 1)) ||
+      (get_isect(p1.y - bb[4], p2.y - bb[4], p1, p2, &hit) && in_box(hit, bb, 2)) ||
+      (get_isect(p1.z - bb[5], p2.z - bb[5], p1, p2, &hit) && in_box(hit, bb, 3)))
+    return 1;
+  return 0;
+}
+
+/* QueryDeviceStackless (point: BVH.cu:957-988, segment: :989-1022).
+ * kind 0 = point p1, 1 = segment p1-p2.  Returns hits in traversal order. */
+uint32_t oracle_query(const OBvh* b, int kind, v3 p1, v3 p2, uint32_t* out) {
+  int node = 0;
+  uint32_t found = 0;
+  const uint32_t NI = b->F - 1;
+  while (node != -1) {
+    const uint32_t obj = b->nodes[4 * node + 3];
+    const float* bb = b->aabb + 6 * (size_t)node;
+    if (found >= MAX_HITS) break;
+    const int hit = kind == 0 ? oracle_overlap_point(bb, p1) : oracle_overlap_segment(bb, p1, p2);
+    if (hit) {
+      if (obj != 0xFFFFFFFFu) {
+        out[found++] = obj;
+        node = b->esc_ext[node - (int)NI];
+      } else
+        node = (int)b->nodes[4 * node + 1];
+    } else {
+      if (obj != 0xFFFFFFFFu) node = b->esc_ext[node - (int)NI];
+      else node = b->esc_int[node];
+    }
+  }
+  return found;
+}
+
+/* ------------------------------------------------------------------------- */
+/* Primitive tests: math/BasicPrimitiveTests.cu                               */
+/* ------------------------------------------------------------------------- */
+
+/* NearestPoint(p, Primitive, qs, u, v, w), BasicPrimitiveTests.cu:6-84 */
+float oracle_nearest_point(v3 p, v3 a, v3 b, v3 c, v3* qs) {
+  const v3 e1 = sub(b, a), e2 = sub(c, a), e3 = sub(c, b);
+  const v3 v1 = sub(p, a);
+  const float d1 = dot(e1, v1), d2 = dot(e2, v1);
+  if (d1 <= 0 && d2 <= 0) { *qs = a; return len(sub(p, *qs)); }
+  const v3 v2 = sub(p, b);
+  const float d3 = dot(e1, v2), d4 = dot(e2, v2);
+  if (d3 >= 0 && d4 <= d3) { *qs = b; return len(sub(p, *qs)); }
+  const float vc = d1 * d4 - d3 * d2;
+  if (vc <= 0 && d1 >= 0 && d3 <= 0) {
+    const float v = d1 / (d1 - d3);
+    *qs = add(a, mul(e1, v));
+    return len(sub(p, *qs));
+  }
+  const v3 v3_ = sub(p, c);
+  const float d5 = dot(e1, v3_), d6 = dot(e2, v3_);
+  if (d6 >= 0 && d5 <= d6) { *qs = c; return len(sub(p, *qs)); }
+  const float vb = d5 * d2 - d1 * d6;
+  if (vb <= 0 && d2 >= 0 && d6 <= 0) {
+    const float w = d2 / (d2 - d6);
+    *qs = add(a, mul(e2, w));
+    return len(sub(p, *qs));
+  }
+  const float va = d3 * d6 - d5 * d4;
+  if (va <= 0 && (d4 - d3) >= 0 && (d5 - d6) >= 0) {
+    const float w = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+    *qs = add(b, mul(e3, w));
+    return len(sub(p, *qs));
+  }
+  const float d = 1 / (va + vb + vc);
+  const float v = vb * d, w = vc * d;
+  *qs = add(add(a, mul(e1, v)), mul(e2, w));
+  return len(sub(p, *qs));
+}
+
+/* RayIntersect(o, d, ray_length, Primitive), BasicPrimitiveTests.cu:242-284 */
+float oracle_ray_intersect(v3 o, v3 d, float ray_length, v3 a, v3 b, v3 c) {
+  const v3 e1 = sub(b, a), e2 = sub(c, a);
+  const v3 n = cross(d, e2);
+  const float det = dot(e1, n);
+  if (fabsf(det) < EPS) return SCALAR_MAX;
+  const float inv = 1 / det;
+  const v3 t = sub(o, a);
+  const float u = dot(t, n) * inv;
+  if (u < 0 || u > 1) return SCALAR_MAX;
+  const v3 q = cross(t, e1);
+  const float v = dot(d, q) * inv;
+  if (v < 0 || v + u > 1) return SCALAR_MAX;
+  const float s = dot(e2, q) * inv;
+  if (s > 0 && s < ray_length) return s;
+  return INFINITY;
+}
+
+/* ClosestPtSegmentSegment, BasicPrimitiveTests.cu:303-361 */
+float oracle_closest_seg_seg(v3 p1, v3 q1, v3 p2, v3 q2, float* s, float* t, v3* c1, v3* c2) {
+  const v3 d1 = sub(q1, p1), d2 = sub(q2, p2), r = sub(p1, p2);
+  const float a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r);
+  if (a <= EPS && e <= EPS) {
+    *s = *t = 0;
+    *c1 = p1; *c2 = p2;
+    return len(sub(*c1, *c2));
+  }
+  if (a <= EPS) {
+    *s = 0;
+    *t = clampf(f / e, 0.0f, 1.0f);
+  } else {
+    const float c = dot(d1, r);
+    if (e <= EPS) {
+      *t = 0;
+      *s = clampf(-c / a, 0.0f, 1.0f);
+    } else {
+      const float b = dot(d1, d2);
+      const float denom = a * e - b * b;
+      if (denom > EPS) *s = clampf((b * f - c * e) / denom, 0.0f, 1.0f);
+      else *s = 0;
+      *t = (b * *s + f) / e;
+      if (*t < EPS) {
+        *t = 0;
+        *s = clampf(-c / a, 0.0f, 1.0f);
+      } else if (*t > 1) {
+        *t = 1;
+        *s = clampf((b - c) / a, 0.0f, 1.0f);
+      }
+    }
+  }
+  *c1 = add(p1, mul(d1, *s));
+  *c2 = add(p2, mul(d2, *t));
+  return len(sub(*c1, *c2));
+}
+
+/* flat-array wrappers so Python can call the primitive tests directly */
+float oracle_nearest_point_f(const float* p, const float* tri9, float* qs) {
+  v3 q;
+  float d = oracle_nearest_point(ld3(p, 0), ld3(tri9, 0), ld3(tri9, 1), ld3(tri9, 2), &q);
+  st3(qs, 0, q);
+  return d;
+}
+float oracle_ray_intersect_f(const float* o, const float* d, float ray_length, const float* tri9) {
+  return oracle_ray_intersect(ld3(o, 0), ld3(d, 0), ray_length, ld3(tri9, 0), ld3(tri9, 1), ld3(tri9, 2));
+}
+float oracle_closest_seg_seg_f(const float* p1q1p2q2, float* st, float* c1c2) {
+  v3 c1, c2;
+  float d = oracle_closest_seg_seg(ld3(p1q1p2q2, 0), ld3(p1q1p2q2, 1), ld3(p1q1p2q2, 2), ld3(p1q1p2q2, 3), st,
+                                   st + 1, &c1, &c2);
+  st3(c1c2, 0, c1);
+  st3(c1c2, 1, c2);
+  return d;
+}
+int oracle_overlap_point_f(const float* bb, const float* p) { return oracle_overlap_point(bb, ld3(p, 0)); }
+int oracle_overlap_segment_f(const float* bb, const float* p1, const float* p2) {
+  return oracle_overlap_segment(bb, ld3(p1, 0), ld3(p2, 0));
+}
+uint32_t oracle_query_f(const OBvh* b, int kind, const float* p1, const float* p2, uint32_t* out) {
+  return oracle_query(b, kind, ld3(p1, 0), p2 ? ld3(p2, 0) : V(0, 0, 0), out);
+}
+
+/* RTriBuild_Kernel, physics/representative_triangle/RTriangle.cu:19-74.
+ * nb_vf / prefix: vertex -> incident faces, ascending (std::set order). */
+void oracle_rtri(const uint32_t* indices, const uint32_t* nb_vf, const uint32_t* nb_vf_prefix, uint32_t F,
+                 uint32_t* out) {
+  for (uint32_t fid = 0; fid < F; fid++) {
+    uint32_t fv[3] = {indices[3 * fid], indices[3 * fid + 1], indices[3 * fid + 2]};
+    uint32_t info = 0;
+    uint32_t j_start = nb_vf_prefix[fv[0]], j_end = nb_vf_prefix[fv[0] + 1];
+    for (uint32_t i_v = 0; i_v < 3; i_v++) {
+      uint32_t off = j_start, i_end = j_end;
+      uint32_t i_f = nb_vf[off++];
+      if (i_f == fid) info |= (1u << i_v);
+      const uint32_t j_v = (i_v + 1) % 3;
+      j_start = nb_vf_prefix[fv[j_v]];
+      j_end = nb_vf_prefix[fv[j_v] + 1];
+      uint32_t of = 0xFFFFFFFFu;
+      for (uint32_t jno = j_start; jno < j_end; jno++)
+        if (nb_vf[jno] == i_f && fid != i_f) { of = i_f; break; }
+      for (; off < i_end && of == 0xFFFFFFFFu; off++) {
+        i_f = nb_vf[off];
+        for (uint32_t jno = j_start; jno < j_end; jno++)
+          if (nb_vf[jno] == i_f && fid != i_f) { of = i_f; break; }
+      }
+      if (fid < of) info |= (1u << (i_v + 3u));
+    }
+    out[fid] = info;
+  }
+}
