@@ -516,3 +516,239 @@ void oracle_rtri(const uint32_t* indices, const uint32_t* nb_vf, const uint32_t*
     out[fid] = info;
   }
 }
+
+/* ------------------------------------------------------------------------- */
+/* Scene state + the Swift frame                                              */
+/* ------------------------------------------------------------------------- */
+
+typedef struct {
+  /* params: SimParams (core/Common.hpp:31-116) + swift self-contact config */
+  int S, N, C, max_nb, interleaved, self_collision, bending, lra_on;
+  float g[3], damping, relax, lra_stretch, friction, tol, s_compliance, b_compliance, diameter, cell_size, frame_dt;
+  /* cloth */
+  uint32_t V, E, F;
+  float *x0, *x, *v, *invm, *n, *rest;
+  uint32_t *tri, *edge;
+  /* constraints in the caller's order, colour per constraint like GraphColoring::colors */
+  uint32_t ns, nb, nl, n_sc, n_bc;
+  uint32_t *s_idx, *s_color, *b_idx, *b_color, *l_src, *l_tgt;
+  float *s_rest, *s_lambda, *b_theta, *l_rest;
+  /* obstacle */
+  uint32_t Vo, Fo;
+  float *ox0, *ox, *ox1, *on, *on1;
+  uint32_t *otri, *rtri;
+  OBvh* bvh;
+  int moved;
+  /* contacts */
+  int32_t *vf_idx, *rt_idx;
+  float *vf_q, *rt_q, *ee; /* ee: 14 floats per edge: dist,p2,q2,s,t,fn */
+  uint32_t *cnt_vf, *cnt_rt, *cnt_ee;
+  /* Jacobi accumulators */
+  float* delta;
+  int* delta_count;
+  /* spatial hash */
+  uint32_t *p_hash, *p_index, *cell_start, *cell_end, *neighbors;
+  int table_size;
+} OScene;
+
+static void* dup_mem(const void* p, size_t bytes) {
+  void* r = malloc(bytes ? bytes : 1);
+  if (p && bytes) memcpy(r, p, bytes);
+  return r;
+}
+
+OScene* oracle_scene_new(const int* ip, const float* fp) {
+  OScene* s = (OScene*)calloc(1, sizeof(OScene));
+  s->S = ip[0]; s->N = ip[1]; s->C = ip[2]; s->max_nb = ip[3]; s->interleaved = ip[4];
+  s->self_collision = ip[5]; s->bending = ip[6]; s->lra_on = ip[7];
+  s->g[0] = fp[0]; s->g[1] = fp[1]; s->g[2] = fp[2];
+  s->damping = fp[3]; s->relax = fp[4]; s->lra_stretch = fp[5]; s->friction = fp[6]; s->tol = fp[7];
+  s->s_compliance = fp[8]; s->b_compliance = fp[9]; s->diameter = fp[10]; s->cell_size = fp[11]; s->frame_dt = fp[12];
+  return s;
+}
+
+/* area-weighted vertex normals: updateNodeNormals_Kernel / UpdateNodeMidstepNormals_Kernel,
+ * physics/PhysicsMeshHelper.cu:200-230, then FinalizeNodeNormals (normalize) */
+static void vertex_normals(const float* x, const uint32_t* tri, uint32_t V_, uint32_t F, float* n) {
+  memset(n, 0, 12 * (size_t)V_);
+  for (uint32_t f = 0; f < F; f++)
+    for (int j = 0; j < 3; j++) {
+      const uint32_t a = tri[3 * f + j];
+      const v3 e0 = sub(ld3(x, tri[3 * f + (j + 1) % 3]), ld3(x, a));
+      const v3 e1 = sub(ld3(x, tri[3 * f + (j + 2) % 3]), ld3(x, a));
+      const v3 w = divs(cross(e0, e1), dot(e0, e0) * dot(e1, e1));
+      st3(n, a, add(ld3(n, a), w));
+    }
+  for (uint32_t i = 0; i < V_; i++) st3(n, i, normalize(ld3(n, i)));
+}
+
+void oracle_scene_set_cloth(OScene* s, const float* pos, const float* invm, uint32_t V_, const uint32_t* tri,
+                            uint32_t F, const uint32_t* edge, uint32_t E) {
+  s->V = V_; s->F = F; s->E = E;
+  s->x0 = (float*)dup_mem(pos, 12 * (size_t)V_);
+  s->x = (float*)dup_mem(pos, 12 * (size_t)V_);
+  s->rest = (float*)dup_mem(pos, 12 * (size_t)V_);
+  s->v = (float*)calloc(3 * (size_t)V_ + 1, 4);
+  s->n = (float*)calloc(3 * (size_t)V_ + 1, 4);
+  s->invm = (float*)dup_mem(invm, 4 * (size_t)V_);
+  s->tri = (uint32_t*)dup_mem(tri, 12 * (size_t)F);
+  s->edge = (uint32_t*)dup_mem(edge, 8 * (size_t)E);
+  s->vf_idx = (int32_t*)malloc(4 * (size_t)V_ + 4); s->rt_idx = (int32_t*)malloc(4 * (size_t)V_ + 4);
+  for (uint32_t i = 0; i < V_; i++) s->vf_idx[i] = s->rt_idx[i] = -1;
+  s->vf_q = (float*)calloc(3 * (size_t)V_ + 1, 4); s->rt_q = (float*)calloc(3 * (size_t)V_ + 1, 4);
+  s->ee = (float*)calloc(14 * (size_t)E + 1, 4);
+  for (uint32_t i = 0; i < E; i++) s->ee[14 * i] = SCALAR_MAX;
+  s->cnt_vf = (uint32_t*)calloc(V_ + 1, 4); s->cnt_rt = (uint32_t*)calloc(V_ + 1, 4); s->cnt_ee = (uint32_t*)calloc(E + 1, 4);
+  s->delta = (float*)calloc(3 * (size_t)V_ + 1, 4);
+  s->delta_count = (int*)calloc(V_ + 1, 4);
+  s->table_size = 2 * (int)V_; /* SpatialHashGPU ctor, SpatialHashGPU.cu:161-175 */
+  s->p_hash = (uint32_t*)calloc(V_ + 1, 4); s->p_index = (uint32_t*)calloc(V_ + 1, 4);
+  s->cell_start = (uint32_t*)calloc((size_t)s->table_size + 1, 4);
+  s->cell_end = (uint32_t*)calloc((size_t)s->table_size + 1, 4);
+  s->neighbors = (uint32_t*)malloc(4 * (size_t)V_ * s->max_nb + 4);
+  memset(s->neighbors, 0xFF, 4 * (size_t)V_ * s->max_nb);
+  vertex_normals(s->x0, s->tri, V_, F, s->n);
+}
+
+void oracle_scene_set_stretch(OScene* s, const uint32_t* idx, const float* rest, const uint32_t* color, uint32_t n) {
+  s->ns = n;
+  s->s_idx = (uint32_t*)dup_mem(idx, 8 * (size_t)n);
+  s->s_rest = (float*)dup_mem(rest, 4 * (size_t)n);
+  s->s_color = (uint32_t*)dup_mem(color, 4 * (size_t)n);
+  s->s_lambda = (float*)calloc(n + 1, 4);
+  s->n_sc = 0;
+  for (uint32_t i = 0; i < n; i++) if (color[i] + 1 > s->n_sc) s->n_sc = color[i] + 1;
+}
+void oracle_scene_set_bend(OScene* s, const uint32_t* idx, const float* theta, const uint32_t* color, uint32_t n) {
+  s->nb = n;
+  s->b_idx = (uint32_t*)dup_mem(idx, 16 * (size_t)n);
+  s->b_theta = (float*)dup_mem(theta, 4 * (size_t)n);
+  s->b_color = (uint32_t*)dup_mem(color, 4 * (size_t)n);
+  s->n_bc = 0;
+  for (uint32_t i = 0; i < n; i++) if (color[i] + 1 > s->n_bc) s->n_bc = color[i] + 1;
+}
+void oracle_scene_set_lra(OScene* s, const uint32_t* src, const uint32_t* tgt, const float* rest, uint32_t n) {
+  s->nl = n;
+  s->l_src = (uint32_t*)dup_mem(src, 4 * (size_t)n);
+  s->l_tgt = (uint32_t*)dup_mem(tgt, 4 * (size_t)n);
+  s->l_rest = (float*)dup_mem(rest, 4 * (size_t)n);
+}
+
+/* AddObstacle + ClothSolverUniversal::Start (impl/universal/ClothSolver.cpp:46-66):
+ * normals, BVH UpdateData(0, false) + Construct, RTriangle */
+void oracle_scene_set_obstacle(OScene* s, const float* pos, uint32_t Vo, const uint32_t* tri, uint32_t Fo) {
+  s->Vo = Vo; s->Fo = Fo;
+  s->ox0 = (float*)dup_mem(pos, 12 * (size_t)Vo);
+  s->ox = (float*)dup_mem(pos, 12 * (size_t)Vo);
+  s->ox1 = (float*)dup_mem(pos, 12 * (size_t)Vo);
+  s->on = (float*)calloc(3 * (size_t)Vo + 1, 4);
+  s->on1 = (float*)calloc(3 * (size_t)Vo + 1, 4);
+  s->otri = (uint32_t*)dup_mem(tri, 12 * (size_t)Fo);
+  vertex_normals(s->ox0, s->otri, Vo, Fo, s->on);
+  s->bvh = oracle_bvh_build(s->ox0, s->ox, s->on, s->otri, Fo, 0.0f, 0);
+  /* VF adjacency (BuildVFAdjacency, ClothSolverHelper.cu:377-401) -> RTriangle::Init */
+  uint32_t* prefix = (uint32_t*)calloc(Vo + 2, 4);
+  for (uint32_t i = 0; i < 3 * Fo; i++) prefix[tri[i] + 1]++;
+  for (uint32_t v = 0; v < Vo; v++) prefix[v + 1] += prefix[v];
+  uint32_t* nb = (uint32_t*)malloc(12 * (size_t)Fo + 4);
+  uint32_t* cur = (uint32_t*)dup_mem(prefix, 4 * (size_t)(Vo + 1));
+  for (uint32_t f = 0; f < Fo; f++)
+    for (int j = 0; j < 3; j++) nb[cur[tri[3 * f + j]]++] = f;
+  s->rtri = (uint32_t*)malloc(4 * (size_t)Fo + 4);
+  oracle_rtri(tri, nb, prefix, Fo, s->rtri);
+  free(prefix); free(nb); free(cur);
+}
+
+void oracle_scene_set_obstacle_target(OScene* s, const float* xyz) {
+  memcpy(s->ox, xyz, 12 * (size_t)s->Vo);
+  s->moved = 1;
+}
+
+/* PredictPositions_Kernel, ClothSolverHelper.cu:125-131 */
+void oracle_predict(OScene* s, float dt) {
+  for (uint32_t i = 0; i < s->V; i++) {
+    if (s->invm[i] > EPS) st3(s->v, i, add(ld3(s->v, i), mul(V(s->g[0], s->g[1], s->g[2]), dt)));
+    st3(s->x, i, add(ld3(s->x0, i), mul(ld3(s->v, i), dt)));
+  }
+}
+/* Finalize_Kernel, ClothSolverHelper.cu:222-229 */
+void oracle_finalize(OScene* s, float dt) {
+  for (uint32_t i = 0; i < s->V; i++) {
+    const v3 np = ld3(s->x, i);
+    const v3 raw = divs(sub(np, ld3(s->x0, i)), dt);
+    st3(s->v, i, mul(raw, (1 - s->damping * dt)));
+    st3(s->x0, i, np);
+  }
+}
+/* SolveStretch_Kernel, BasicSolverHelper.cu:80-127: full sweep, colour filter */
+void oracle_solve_stretch(OScene* s, uint32_t color, float dt, int iter) {
+  for (uint32_t id = 0; id < s->ns; id++) {
+    if (s->s_color[id] != color) continue;
+    if (iter == 0) s->s_lambda[id] = 0;
+    const uint32_t i1 = s->s_idx[2 * id], i2 = s->s_idx[2 * id + 1];
+    const float rest = s->s_rest[id];
+    const v3 diff = sub(ld3(s->x, i1), ld3(s->x, i2));
+    const float distance = len(diff);
+    const float w1 = s->invm[i1], w2 = s->invm[i2];
+    if (distance != rest && w1 + w2 > 0.0f) {
+      const v3 gradient = divs(diff, distance + EPS);
+      const float alpha_tilde = s->s_compliance / (dt * dt);
+      const float constraint = distance - rest;
+      const float dl = (-constraint - alpha_tilde * s->s_lambda[id]) / (w1 + w2 + alpha_tilde);
+      const v3 corr = mul(gradient, dl);
+      s->s_lambda[id] += dl;
+      st3(s->x, i1, add(ld3(s->x, i1), mul(corr, w1)));
+      st3(s->x, i2, add(ld3(s->x, i2), mul(neg(corr), w2)));
+    }
+  }
+}
+/* SolveBend_Kernel, BasicSolverHelper.cu:8-66 */
+void oracle_solve_bend(OScene* s, uint32_t color, float dt) {
+  for (uint32_t id = 0; id < s->nb; id++) {
+    if (s->b_color[id] != color) continue;
+    const uint32_t* q = s->b_idx + 4 * (size_t)id;
+    const float w1 = s->invm[q[0]], w2 = s->invm[q[1]], w3 = s->invm[q[2]], w4 = s->invm[q[3]];
+    const v3 p1 = ld3(s->x, q[0]);
+    const v3 p2 = sub(ld3(s->x, q[1]), p1), p3 = sub(ld3(s->x, q[2]), p1), p4 = sub(ld3(s->x, q[3]), p1);
+    const v3 n1 = normalize(cross(p2, p3)), n2 = normalize(cross(p2, p4));
+    const float d = clampf(dot(n1, n2), 0.0f, 1.0f);
+    const float angle = acosf(d);
+    if (angle < EPS || d != d) continue;
+    const float l23 = len(cross(p2, p3)) + EPS, l24 = len(cross(p2, p4)) + EPS;
+    const v3 q3 = divs(add(cross(p2, n2), mul(cross(n1, p2), d)), l23);
+    const v3 q4 = divs(add(cross(p2, n1), mul(cross(n2, p2), d)), l24);
+    const v3 q2 = sub(neg(divs(add(cross(p3, n2), mul(cross(n1, p3), d)), l23)),
+                      divs(add(cross(p4, n1), mul(cross(n2, p4), d)), l24));
+    const v3 q1 = sub(sub(neg(q2), q3), q4);
+    const float xpbd = s->b_compliance / dt / dt;
+    const float denom = xpbd + (w1 * dot(q1, q1) + w2 * dot(q2, q2) + w3 * dot(q3, q3) + w4 * dot(q4, q4));
+    if (denom < EPS) continue;
+    const float lambda = sqrtf(1.0f - d * d) * (angle - s->b_theta[id]) / denom;
+    st3(s->x, q[0], add(ld3(s->x, q[0]), mul(q1, w1 * lambda)));
+    st3(s->x, q[1], add(ld3(s->x, q[1]), mul(q2, w2 * lambda)));
+    st3(s->x, q[2], add(ld3(s->x, q[2]), mul(q3, w3 * lambda)));
+    st3(s->x, q[3], add(ld3(s->x, q[3]), mul(q4, w4 * lambda)));
+  }
+}
+/* SolveGeodesicLRA_Kernel, LongRangeAttachments.cu:5-26 */
+void oracle_solve_lra(OScene* s) {
+  for (uint32_t i = 0; i < s->nl; i++) {
+    const uint32_t src = s->l_src[i], tgt = s->l_tgt[i];
+    const float target = s->l_rest[i] * s->lra_stretch;
+    if (s->invm[tgt] < EPS && target > 0) continue;
+    const v3 diff = sub(ld3(s->x, tgt), ld3(s->x, src));
+    const float dist = len(diff);
+    if (dist > target) st3(s->x, tgt, add(ld3(s->x, tgt), add(neg(diff), mul(divs(diff, dist), target))));
+  }
+}
+/* ApplyDeltas_Kernel, ClothSolverHelper.cu:139-148 */
+void oracle_apply_deltas(OScene* s) {
+  for (uint32_t i = 0; i < s->V; i++) {
+    const float count = (float)s->delta_count[i];
+    if (count > 0.0f) {
+      st3(s->x, i, add(ld3(s->x, i), mul(divs(ld3(s->delta, i), count), s->relax)));
+      st3(s->delta, i, V(0, 0, 0));
+      s->delta_count[i] = 0;
+    }
+  }
+}
