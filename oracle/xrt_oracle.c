@@ -752,3 +752,321 @@ void oracle_apply_deltas(OScene* s) {
     }
   }
 }
+
+/* ------------------------------------------------------------------------- */
+/* Obstacle contact: physics/pbd_collision/PBDCollision.cu                    */
+/* ------------------------------------------------------------------------- */
+
+/* GenerateVF_DCD_Kernel :17-47, GenerateVFCCD_Kernel :236-268, GenerateEE_DCD_Kernel :100-153 */
+void oracle_generate_contacts(OScene* s) {
+  const OBvh* b = s->bvh;
+  if (!b) return;
+  uint32_t buffer[MAX_HITS];
+  for (uint32_t i = 0; i < s->V; i++) {
+    const v3 pred = ld3(s->x, i);
+    uint32_t nf = oracle_query(b, 0, pred, pred, buffer);
+    float hit = SCALAR_MAX;
+    int hit_idx = -1;
+    v3 hit_qs = V(0, 0, 0);
+    for (uint32_t k = 0; k < nf; k++) {
+      v3 qs;
+      const uint32_t o = buffer[k];
+      const float d = oracle_nearest_point(pred, ld3(b->pred, 3 * o), ld3(b->pred, 3 * o + 1), ld3(b->pred, 3 * o + 2), &qs);
+      if (d < hit) { hit = d; hit_qs = qs; hit_idx = (int)o; }
+    }
+    s->vf_idx[i] = hit_idx;
+    st3(s->vf_q, i, hit_qs);
+    s->cnt_vf[i] = nf;
+    /* vertex ray */
+    s->rt_idx[i] = -1;
+    st3(s->rt_q, i, V(0, 0, 0));
+    s->cnt_rt[i] = 0;
+    const v3 p1 = ld3(s->x0, i), p2 = pred;
+    v3 d = sub(p2, p1);
+    const float length = len(d);
+    if (length < EPS) continue;
+    d = divs(d, length);
+    nf = oracle_query(b, 1, p1, p2, buffer);
+    s->cnt_rt[i] = nf;
+    hit = SCALAR_MAX;
+    hit_idx = -1;
+    v3 qc = V(0, 0, 0);
+    for (uint32_t k = 0; k < nf; k++) {
+      const uint32_t o = buffer[k];
+      const float dist = oracle_ray_intersect(p1, d, length, ld3(b->pred, 3 * o), ld3(b->pred, 3 * o + 1), ld3(b->pred, 3 * o + 2));
+      if (dist < hit) { qc = add(p1, mul(d, dist)); hit = dist; hit_idx = (int)o; }
+    }
+    s->rt_idx[i] = hit_idx;
+    st3(s->rt_q, i, qc);
+  }
+  for (uint32_t i = 0; i < s->E; i++) {
+    const v3 pc = ld3(s->x, s->edge[2 * i]), qc = ld3(s->x, s->edge[2 * i + 1]);
+    const uint32_t nf = oracle_query(b, 1, pc, qc, buffer);
+    s->cnt_ee[i] = nf;
+    float ss = 0, tt = 0, min_dist = SCALAR_MAX;
+    v3 p2 = V(0, 0, 0), q2 = V(0, 0, 0), fn = V(0, 0, 0);
+    for (uint32_t k = 0; k < nf; k++) {
+      const uint32_t f = buffer[k];
+      const uint32_t info = s->rtri[f];
+      const v3 ov[3] = {ld3(b->pred, 3 * f), ld3(b->pred, 3 * f + 1), ld3(b->pred, 3 * f + 2)};
+      for (uint32_t e = 0; e < 3; e++) {
+        if ((info >> (e + 3u)) & 1u) { /* RTriEdge */
+          float _s, _t;
+          v3 c1, c2;
+          const uint32_t j = (e + 1u) % 3u;
+          if (oracle_closest_seg_seg(pc, qc, ov[e], ov[j], &_s, &_t, &c1, &c2)) {
+            const float dist = len(sub(c1, c2));
+            if (dist < min_dist) {
+              min_dist = dist; p2 = ov[e]; q2 = ov[j]; ss = _s; tt = _t;
+              fn = face_normal(ov[0], ov[1], ov[2]);
+            }
+          }
+        }
+      }
+    }
+    float* c = s->ee + 14 * (size_t)i;
+    c[0] = min_dist; st3(c + 1, 0, p2); st3(c + 4, 0, q2); c[7] = ss; c[8] = tt; st3(c + 9, 0, fn);
+  }
+}
+
+/* SolveVFCCD_Kernel :279-297 */
+void oracle_solve_vf_ccd(OScene* s) {
+  if (!s->bvh) return;
+  for (uint32_t i = 0; i < s->V; i++) {
+    const int o = s->rt_idx[i];
+    if (o == -1) continue;
+    const v3 nc = face_normal(ld3(s->bvh->pred, 3 * o), ld3(s->bvh->pred, 3 * o + 1), ld3(s->bvh->pred, 3 * o + 2));
+    const float lambda = dot(nc, sub(ld3(s->x, i), ld3(s->rt_q, i)));
+    if (lambda < 0) st3(s->x, i, add(ld3(s->x, i), mul(nc, -lambda)));
+  }
+}
+/* SolveVFDCD_Kernel :57-75 */
+void oracle_solve_vf_dcd(OScene* s) {
+  if (!s->bvh) return;
+  for (uint32_t i = 0; i < s->V; i++) {
+    const int o = s->vf_idx[i];
+    if (o == -1) continue;
+    const v3 ns = face_normal(ld3(s->bvh->pred, 3 * o), ld3(s->bvh->pred, 3 * o + 1), ld3(s->bvh->pred, 3 * o + 2));
+    const float lambda = dot(ns, sub(ld3(s->x, i), ld3(s->vf_q, i))) - 1e-3f;
+    if (lambda < 0) st3(s->x, i, add(ld3(s->x, i), mul(ns, -lambda)));
+  }
+}
+/* SolveEEDCD_Kernel :163-207 */
+void oracle_solve_ee_dcd(OScene* s) {
+  if (!s->bvh) return;
+  for (uint32_t i = 0; i < s->E; i++) {
+    const float* c = s->ee + 14 * (size_t)i;
+    if (c[0] > 1e6f) continue;
+    const uint32_t i1 = s->edge[2 * i], i2 = s->edge[2 * i + 1];
+    const v3 p1 = ld3(s->x, i1), q1 = ld3(s->x, i2);
+    const v3 p2 = ld3(c + 1, 0), q2 = ld3(c + 4, 0), fn = ld3(c + 9, 0);
+    const float ss = c[7], tt = c[8];
+    const v3 c1 = add(mul(p1, 1 - ss), mul(q1, ss));
+    const v3 c2 = add(mul(p2, 1 - tt), mul(q2, tt));
+    const v3 d = sub(c1, c2);
+    if (len(d) < EPS) continue;
+    const float lambda = dot(d, fn) - 1e-3f;
+    if (lambda > 0) continue;
+    st3(s->delta, i1, add(ld3(s->delta, i1), mul(fn, -(1 - ss) * lambda)));
+    st3(s->delta, i2, add(ld3(s->delta, i2), mul(fn, -(ss)*lambda)));
+    s->delta_count[i1]++;
+    s->delta_count[i2]++;
+  }
+}
+
+/* ------------------------------------------------------------------------- */
+/* Self contact: broad_phase/spatial_hash/SpatialHashGPU.cu + CollideParticles */
+/* ------------------------------------------------------------------------- */
+
+static int int_coord(float v, float cell) { return (int)floorf(v / cell); }  /* :6-8 */
+static int hash_coords(int x, int y, int z, int table) {                    /* :9-12 */
+  const int h = (int)(((uint32_t)x * 92837111u) ^ ((uint32_t)y * 689287499u) ^ ((uint32_t)z * 283923481u));
+  return abs(h % table);
+}
+static int cmp_hash(const void* a, const void* b) {
+  const SortItem *x = (const SortItem*)a, *y = (const SortItem*)b;
+  if (x->key != y->key) return x->key < y->key ? -1 : 1;
+  return x->idx < y->idx ? -1 : (x->idx > y->idx); /* radix sort is stable */
+}
+/* HashObjects, SpatialHashGPU.cu:128-160 */
+void oracle_hash(OScene* s) {
+  const uint32_t n = s->V;
+  const float cell = s->diameter * s->cell_size;
+  SortItem* it = (SortItem*)malloc(sizeof(SortItem) * (n + 1));
+  for (uint32_t i = 0; i < n; i++) {
+    const v3 p = ld3(s->x, i);
+    it[i].key = (uint32_t)hash_coords(int_coord(p.x, cell), int_coord(p.y, cell), int_coord(p.z, cell), s->table_size);
+    it[i].idx = i;
+  }
+  qsort(it, n, sizeof(SortItem), cmp_hash);
+  for (uint32_t i = 0; i < n; i++) { s->p_hash[i] = it[i].key; s->p_index[i] = it[i].idx; }
+  free(it);
+  memset(s->cell_start, 0xFF, 4 * (size_t)s->table_size);
+  for (uint32_t i = 0; i < n; i++) { /* FindCellStart_Kernel :27-55 */
+    const uint32_t h = s->p_hash[i];
+    if (i == 0 || h != s->p_hash[i - 1]) {
+      s->cell_start[h] = i;
+      if (i > 0) s->cell_end[s->p_hash[i - 1]] = i;
+    }
+    if (i == n - 1) s->cell_end[h] = i + 1;
+  }
+  const float cell2 = cell * cell, diam2 = s->diameter * s->diameter;
+  const long long limit = (long long)n * s->max_nb;
+  for (uint32_t t = 0; t < n; t++) { /* CacheNeighbors_Kernel :56-100 */
+    const uint32_t id = s->p_index[t];
+    const v3 p = ld3(s->x, id), r = ld3(s->rest, id);
+    const int ix = int_coord(p.x, cell), iy = int_coord(p.y, cell), iz = int_coord(p.z, cell);
+    long long ni = id;
+    int full = 0;
+    for (int x = ix - 1; x <= ix + 1 && !full; x++)
+      for (int y = iy - 1; y <= iy + 1 && !full; y++)
+        for (int z = iz - 1; z <= iz + 1 && !full; z++) {
+          const int h = hash_coords(x, y, z, s->table_size);
+          const int start = (int)s->cell_start[h];
+          if (start == -1) continue;
+          int end = (int)s->cell_end[h];
+          if (start + s->max_nb < end) end = start + s->max_nb;
+          for (int k = start; k < end; k++) {
+            const uint32_t nb = s->p_index[k];
+            const v3 d = sub(p, ld3(s->x, nb)), dr = sub(r, ld3(s->rest, nb));
+            if (nb != id && dot(d, d) < cell2 && dot(dr, dr) > diam2) {
+              s->neighbors[ni] = nb;
+              ni += n;
+              if (ni >= limit) { full = 1; break; }
+            }
+          }
+        }
+    if (!full && ni < limit) s->neighbors[ni] = 0xFFFFFFFFu;
+  }
+}
+
+/* ComputeFriction + CollideParticles_Kernel, ClothSolverHelper.cu:150-211, then ApplyDeltas */
+void oracle_collide_particles(OScene* s) {
+  const uint32_t n = s->V;
+  for (uint32_t id = 0; id < n; id++) {
+    v3 acc = V(0, 0, 0);
+    int count = 0;
+    const v3 pi = ld3(s->x, id);
+    const v3 vi = sub(pi, ld3(s->x0, id));
+    const float wi = s->invm[id];
+    for (long long k = id; k < (long long)n * s->max_nb; k += n) {
+      const uint32_t j = s->neighbors[k];
+      if (j > n) break;
+      const float denom = wi + s->invm[j];
+      if (denom <= 0) continue;
+      const v3 pj = ld3(s->x, j);
+      const v3 diff = sub(pi, pj);
+      const float distance = len(diff);
+      if (distance >= s->diameter) continue;
+      const v3 grad = divs(diff, distance + EPS);
+      const float lambda = (distance - s->diameter) / denom;
+      const v3 common = mul(grad, lambda);
+      count++;
+      acc = sub(acc, mul(common, wi));
+      const v3 rel = sub(vi, sub(pj, ld3(s->x0, j)));
+      v3 fr = V(0, 0, 0);
+      const float cl = len(common);
+      if (s->friction > 0 && cl > 0) {
+        const v3 nrm = divs(common, cl);
+        const v3 tan = sub(rel, mul(nrm, dot(rel, nrm)));
+        const float tl = len(tan);
+        fr = mul(neg(tan), fmin2(cl * s->friction / tl, 1.0f));
+      }
+      acc = add(acc, mul(fr, wi));
+    }
+    st3(s->delta, id, acc);
+    s->delta_count[id] = count;
+  }
+  oracle_apply_deltas(s);
+}
+
+/* ------------------------------------------------------------------------- */
+/* The frame: ClothSolverBase::SimulateSwift, pipeline/base/ClothSolverBase.cpp:171-247 */
+/* ------------------------------------------------------------------------- */
+
+void oracle_collision_pass(OScene* s, int cnt) {
+  if (!s->bvh) return;
+  if (s->moved) {
+    const float alpha = ((float)cnt + 1.0f) / (float)s->C; /* Interpolate_Kernel, PhysicsMesh.cu:610-614 */
+    for (uint32_t i = 0; i < s->Vo; i++)
+      st3(s->ox1, i, add(mul(ld3(s->ox0, i), 1.0f - alpha), mul(ld3(s->ox, i), alpha)));
+    vertex_normals(s->ox1, s->otri, s->Vo, s->Fo, s->on1);
+    oracle_bvh_refit_midstep(s->bvh, s->ox1, s->on1, s->otri, s->tol);
+  }
+  oracle_generate_contacts(s);
+}
+
+void oracle_iteration(OScene* s, float dt, int iteration) {
+  for (uint32_t c = 0; c < s->n_sc; c++) oracle_solve_stretch(s, c, dt, iteration);
+  if (s->bending)
+    for (uint32_t c = 0; c < s->n_bc; c++) oracle_solve_bend(s, c, dt);
+  if (s->lra_on) oracle_solve_lra(s);
+  oracle_solve_vf_ccd(s);
+  oracle_solve_vf_dcd(s);
+  oracle_solve_ee_dcd(s);
+  if (s->bvh) oracle_apply_deltas(s);
+}
+
+void oracle_step_frame(OScene* s) {
+  const float dt = s->frame_dt / (float)s->S;
+  if (s->moved && s->bvh) { /* UpdateObstacleAnimationFrame: UpdateData(0,false) + Construct */
+    oracle_bvh_free(s->bvh);
+    s->bvh = oracle_bvh_build(s->ox0, s->ox, s->on, s->otri, s->Fo, 0.0f, 0);
+  }
+  uint32_t frequency = (uint32_t)(s->S * s->N) / (uint32_t)s->C;
+  if (frequency == 0) frequency = 1;
+  int cnt = 0;
+  for (int substep = 0; substep < s->S; substep++) {
+    oracle_predict(s, dt);
+    if (s->self_collision && substep % (s->interleaved > 0 ? s->interleaved : 1) == 0) oracle_hash(s);
+    for (int it = 0; it < s->N; it++) {
+      if (s->self_collision) oracle_collide_particles(s);
+      const uint32_t step = (uint32_t)(substep * s->N + it);
+      if (step % frequency == 0) { oracle_collision_pass(s, cnt); cnt++; }
+      oracle_iteration(s, dt, it);
+    }
+    oracle_finalize(s, dt);
+  }
+  if (s->Vo) {
+    if (s->moved) memcpy(s->ox0, s->ox, 12 * (size_t)s->Vo); /* PredictedToPositions */
+    vertex_normals(s->ox0, s->otri, s->Vo, s->Fo, s->on);
+  }
+  vertex_normals(s->x0, s->tri, s->V, s->F, s->n);
+  s->moved = 0;
+}
+
+/* accessors */
+float* oracle_scene_x0(OScene* s) { return s->x0; }
+float* oracle_scene_x(OScene* s) { return s->x; }
+float* oracle_scene_v(OScene* s) { return s->v; }
+float* oracle_scene_n(OScene* s) { return s->n; }
+float* oracle_scene_ox0(OScene* s) { return s->ox0; }
+float* oracle_scene_on(OScene* s) { return s->on; }
+OBvh* oracle_scene_bvh(OScene* s) { return s->bvh; }
+uint32_t* oracle_scene_rtri(OScene* s) { return s->rtri; }
+int32_t* oracle_scene_vf_idx(OScene* s) { return s->vf_idx; }
+float* oracle_scene_vf_q(OScene* s) { return s->vf_q; }
+int32_t* oracle_scene_rt_idx(OScene* s) { return s->rt_idx; }
+float* oracle_scene_rt_q(OScene* s) { return s->rt_q; }
+float* oracle_scene_ee(OScene* s) { return s->ee; }
+uint32_t* oracle_scene_cnt(OScene* s, int kind) { return kind == 0 ? s->cnt_vf : (kind == 1 ? s->cnt_rt : s->cnt_ee); }
+uint32_t* oracle_scene_neighbors(OScene* s) { return s->neighbors; }
+uint32_t* oracle_scene_p_hash(OScene* s) { return s->p_hash; }
+uint32_t* oracle_scene_p_index(OScene* s) { return s->p_index; }
+void oracle_scene_set_state(OScene* s, const float* x0, const float* v) {
+  if (x0) { memcpy(s->x0, x0, 12 * (size_t)s->V); memcpy(s->x, x0, 12 * (size_t)s->V); }
+  if (v) memcpy(s->v, v, 12 * (size_t)s->V);
+}
+
+void oracle_scene_free(OScene* s) {
+  if (!s) return;
+  free(s->x0); free(s->x); free(s->v); free(s->invm); free(s->n); free(s->rest); free(s->tri); free(s->edge);
+  free(s->s_idx); free(s->s_color); free(s->b_idx); free(s->b_color); free(s->l_src); free(s->l_tgt);
+  free(s->s_rest); free(s->s_lambda); free(s->b_theta); free(s->l_rest);
+  free(s->ox0); free(s->ox); free(s->ox1); free(s->on); free(s->on1); free(s->otri); free(s->rtri);
+  oracle_bvh_free(s->bvh);
+  free(s->vf_idx); free(s->rt_idx); free(s->vf_q); free(s->rt_q); free(s->ee);
+  free(s->cnt_vf); free(s->cnt_rt); free(s->cnt_ee); free(s->delta); free(s->delta_count);
+  free(s->p_hash); free(s->p_index); free(s->cell_start); free(s->cell_end); free(s->neighbors);
+  free(s);
+}
