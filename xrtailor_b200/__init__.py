@@ -1,0 +1,12 @@
+"""xrtailor_b200 — B200-native Swift-mode cloth hot path of XRTailor.
+
+The product is the C-ABI shared library ``libxrt_b200.so`` (``include/xrt_b200.h``)
+built from ``csrc/``.  This package is the thin host-side mirror of the
+reference's solver component (``ClothSolverBase``,
+xrtailor/include/xrtailor/pipeline/base/ClothSolverBase.hpp:55-189) used by the
+tests and the bench.  There is no CPU fallback: importing works without a GPU,
+creating a solver does not.
+"""
+from ._abi import lib, XrtParams, XrtError, default_params  # noqa: F401
+from .solver import ClothSolver, bvh_build_standalone, greedy_color  # noqa: F401
+from . import scene  # noqa: F401

@@ -1,0 +1,112 @@
+"""ctypes binding of include/xrt_b200.h.  Loads the in-tree libxrt_b200.so and
+fails loudly when it is missing — there is no other implementation to fall
+back to."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libxrt_b200.so")
+
+
+class XrtError(RuntimeError):
+    def __init__(self, code, msg=""):
+        super().__init__(f"xrt_b200 error {code}: {msg}")
+        self.code = code
+
+
+class XrtParams(C.Structure):
+    _fields_ = [
+        ("num_substeps", C.c_int32), ("num_iterations", C.c_int32),
+        ("num_collision_passes", C.c_int32), ("max_num_neighbors", C.c_int32),
+        ("gravity", C.c_float * 3), ("damping", C.c_float), ("relaxation_factor", C.c_float),
+        ("long_range_stretchiness", C.c_float), ("sdf_friction", C.c_float), ("bvh_tolerance", C.c_float),
+        ("stretch_compliance", C.c_float), ("bend_compliance", C.c_float), ("particle_diameter", C.c_float),
+        ("hash_cell_size", C.c_float), ("inter_leaved_hash", C.c_int32), ("enable_self_collision", C.c_int32),
+        ("solve_bending", C.c_int32), ("geodesic_lra", C.c_int32), ("frame_dt", C.c_float),
+        ("morton_fast_div", C.c_int32), ("fused_iterations", C.c_int32), ("device", C.c_int32),
+    ]
+
+
+class XrtMeshDesc(C.Structure):
+    _fields_ = [
+        ("positions", C.POINTER(C.c_float)), ("indices", C.POINTER(C.c_uint32)),
+        ("edges", C.POINTER(C.c_uint32)), ("inv_mass", C.POINTER(C.c_float)),
+        ("n_verts", C.c_uint32), ("n_faces", C.c_uint32), ("n_edges", C.c_uint32),
+    ]
+
+
+class XrtStats(C.Structure):
+    _fields_ = [
+        ("stretch_rms", C.c_double), ("stretch_max", C.c_double), ("bend_rms", C.c_double),
+        ("vf_penetrations", C.c_uint32), ("n_stretch_colors", C.c_uint32), ("n_bend_colors", C.c_uint32),
+        ("launches_per_frame", C.c_uint32), ("bytes_per_frame", C.c_double),
+    ]
+
+
+# every symbol include/xrt_b200.h declares
+SYMBOLS = [
+    "xrt_default_params", "xrt_create", "xrt_destroy", "xrt_last_error", "xrt_add_cloth", "xrt_add_obstacle",
+    "xrt_set_stretch", "xrt_set_bend", "xrt_add_geodesic", "xrt_set_colors", "xrt_finalize_setup",
+    "xrt_set_obstacle_target", "xrt_step_frame", "xrt_step_frame_async", "xrt_sync", "xrt_get_positions",
+    "xrt_set_cloth_state", "xrt_bvh_build_obstacle", "xrt_bvh_refit_obstacle", "xrt_generate_contacts",
+    "xrt_hash_particles", "xrt_predict", "xrt_solve_iteration", "xrt_finalize", "xrt_debug_get",
+    "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone",
+]
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  xrtailor_b200 has no CPU or PyTorch fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp, u32p, f32p, i32p = C.c_void_p, C.POINTER(C.c_uint32), C.POINTER(C.c_float), C.POINTER(C.c_int32)
+    sig = {
+        "xrt_default_params": [C.POINTER(XrtParams)],
+        "xrt_create": [C.POINTER(XrtParams), C.POINTER(vp)],
+        "xrt_add_cloth": [vp, C.POINTER(XrtMeshDesc), i32p],
+        "xrt_add_obstacle": [vp, C.POINTER(XrtMeshDesc), i32p],
+        "xrt_set_stretch": [vp, u32p, f32p, C.c_size_t],
+        "xrt_set_bend": [vp, u32p, f32p, C.c_size_t],
+        "xrt_add_geodesic": [vp, u32p, u32p, f32p, C.c_size_t],
+        "xrt_set_colors": [vp, C.c_int, u32p, C.c_size_t],
+        "xrt_finalize_setup": [vp],
+        "xrt_set_obstacle_target": [vp, f32p, C.c_size_t],
+        "xrt_step_frame": [vp, f32p],
+        "xrt_step_frame_async": [vp],
+        "xrt_sync": [vp],
+        "xrt_get_positions": [vp, C.c_int, f32p, f32p],
+        "xrt_set_cloth_state": [vp, f32p, f32p],
+        "xrt_bvh_build_obstacle": [vp],
+        "xrt_bvh_refit_obstacle": [vp, C.c_int],
+        "xrt_generate_contacts": [vp],
+        "xrt_hash_particles": [vp],
+        "xrt_predict": [vp],
+        "xrt_solve_iteration": [vp, C.c_int],
+        "xrt_finalize": [vp],
+        "xrt_debug_get": [vp, C.c_int, vp, C.POINTER(C.c_size_t)],
+        "xrt_debug_candidates": [vp, C.c_int, u32p, u32p, C.POINTER(C.c_size_t)],
+        "xrt_greedy_color": [u32p, C.c_size_t, C.c_int, C.c_uint32, u32p, u32p],
+        "xrt_bvh_build_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, C.c_int, C.c_int, u32p, u32p, u32p, f32p,
+                                     i32p, i32p, f32p],
+    }
+    for name, args in sig.items():
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = C.c_int
+    L.xrt_destroy.argtypes = [vp]
+    L.xrt_destroy.restype = None
+    L.xrt_last_error.argtypes = [vp]
+    L.xrt_last_error.restype = C.c_char_p
+    return L
+
+
+lib = _load()
+
+
+def default_params() -> XrtParams:
+    p = XrtParams()
+    rc = lib.xrt_default_params(C.byref(p))
+    if rc:
+        raise XrtError(rc)
+    return p
