@@ -1,0 +1,160 @@
+"""Synthetic scenes of BASELINE.md (C1 / C100k / C2-like) and the setup-time
+derivations the reference performs on the host before the solver starts:
+unique edges, stretch constraints (PrepareBasicStretchData,
+xrtailor/src/physics/ClothSolverHelper.cpp:90-109), bend elements
+(GenerateBendingElements, :4-88).  numpy only; every RNG seeded 20261104."""
+import numpy as np
+
+SEED = 20261104
+
+
+def unique_edges(tri):
+    tri = np.asarray(tri, np.int64).reshape(-1, 3)
+    e = np.concatenate([tri[:, [0, 1]], tri[:, [1, 2]], tri[:, [2, 0]]])
+    e.sort(axis=1)
+    return np.unique(e, axis=0).astype(np.uint32)
+
+
+def stretch_constraints(pos, edges):
+    """(idx01, rest) — one distance constraint per mesh edge."""
+    pos = np.asarray(pos, np.float32)
+    d = pos[edges[:, 0]] - pos[edges[:, 1]]
+    rest = np.sqrt((d * d).sum(1, dtype=np.float32)).astype(np.float32)
+    return edges.astype(np.uint32), rest
+
+
+def bend_constraints(pos, tri):
+    """(idx0123, theta): [0],[1] = shared edge in the winding of the first
+    (lower-index) face, [2] = its opposite vertex, [3] = the other face's
+    opposite vertex; theta = acos(clamp(n1.n2)) with the reference's normals."""
+    pos = np.asarray(pos, np.float32)
+    tri = np.asarray(tri, np.int64).reshape(-1, 3)
+    F = len(tri)
+    a = np.concatenate([tri[:, 0], tri[:, 1], tri[:, 2]])
+    b = np.concatenate([tri[:, 1], tri[:, 2], tri[:, 0]])
+    opp = np.concatenate([tri[:, 2], tri[:, 0], tri[:, 1]])
+    face = np.tile(np.arange(F), 3)
+    lo, hi = np.minimum(a, b), np.maximum(a, b)
+    nv = int(tri.max()) + 1
+    key = lo * nv + hi
+    order = np.lexsort((face, key))
+    key, a, b, opp = key[order], a[order], b[order], opp[order]
+    same = key[1:] == key[:-1]
+    # manifold interior edges: exactly two half-edges share the key
+    first = np.nonzero(same)[0]
+    if len(first):
+        run_prev = np.concatenate([[False], same[:-1]])[first]
+        run_next = np.concatenate([same[1:], [False]])[first]
+        first = first[~run_prev & ~run_next]
+    i1, i2, i3, i4 = a[first], b[first], opp[first], opp[first + 1]
+    v1, v2, v3, v4 = pos[i1], pos[i2], pos[i3], pos[i4]
+
+    def nrm(v):
+        return v / np.sqrt((v * v).sum(1, keepdims=True, dtype=np.float32))
+
+    n1 = nrm(np.cross(v1 - v3, v2 - v3))
+    n2 = nrm(np.cross(v2 - v4, v1 - v4))
+    d = np.clip((n1 * n2).sum(1, dtype=np.float32), -1.0, 1.0)
+    theta = np.arccos(d).astype(np.float32)
+    idx = np.stack([i1, i2, i3, i4], 1).astype(np.uint32)
+    return idx, theta
+
+
+def grid_cloth(n, side=1.0, y=1.0, jitter=1e-4, seed=SEED):
+    """n x n regular grid in the xz plane at height y (C1: n=224, C100k: n=317)."""
+    rng = np.random.default_rng(seed)
+    u = np.linspace(-side / 2, side / 2, n, dtype=np.float32)
+    xx, zz = np.meshgrid(u, u, indexing="ij")
+    pos = np.stack([xx.ravel(), np.full(n * n, y, np.float32), zz.ravel()], 1).astype(np.float32)
+    pos += rng.uniform(-jitter, jitter, pos.shape).astype(np.float32)
+    i, j = np.meshgrid(np.arange(n - 1), np.arange(n - 1), indexing="ij")
+    v00 = (i * n + j).ravel()
+    v01, v10, v11 = v00 + 1, v00 + n, v00 + n + 1
+    tri = np.concatenate([np.stack([v00, v01, v11], 1), np.stack([v00, v11, v10], 1)]).astype(np.uint32)
+    return pos, tri
+
+
+def uv_sphere(r=0.3, stacks=64, slices=128, center=(0.0, 0.0, 0.0)):
+    """UV sphere with outward normals: (stacks-1)*slices + 2 verts, 2*slices*(stacks-1) faces."""
+    th = np.pi * np.arange(1, stacks, dtype=np.float64) / stacks
+    ph = 2 * np.pi * np.arange(slices, dtype=np.float64) / slices
+    T, P = np.meshgrid(th, ph, indexing="ij")
+    ring = np.stack([np.sin(T) * np.cos(P), np.cos(T), np.sin(T) * np.sin(P)], -1).reshape(-1, 3)
+    pos = np.concatenate([[[0, 1, 0]], ring, [[0, -1, 0]]]) * r + np.asarray(center)
+    top, bot = 0, 1 + (stacks - 1) * slices
+    tris = []
+    s = np.arange(slices)
+    s1 = (s + 1) % slices
+    tris.append(np.stack([np.full(slices, top), 1 + s1, 1 + s], 1))
+    for k in range(stacks - 2):
+        a, b = 1 + k * slices, 1 + (k + 1) * slices
+        tris.append(np.stack([a + s, a + s1, b + s1], 1))
+        tris.append(np.stack([a + s, b + s1, b + s], 1))
+    a = 1 + (stacks - 2) * slices
+    tris.append(np.stack([np.full(slices, bot), a + s, a + s1], 1))
+    tri = np.concatenate(tris).astype(np.uint32)
+    pos = pos.astype(np.float32)
+    # orient outward
+    c = np.asarray(center, np.float32)
+    fn = np.cross(pos[tri[:, 1]] - pos[tri[:, 0]], pos[tri[:, 2]] - pos[tri[:, 0]])
+    flip = ((pos[tri].mean(1) - c) * fn).sum(1) < 0
+    tri[flip] = tri[flip][:, [0, 2, 1]]
+    return pos, tri
+
+
+class Scene:
+    """Everything AddCloth/AddObstacle + the constraint generators hand to the solver."""
+
+    def __init__(self, cloth_pos, cloth_tri, obs_pos=None, obs_tri=None, fixed=()):
+        self.cloth_pos = np.ascontiguousarray(cloth_pos, np.float32)
+        self.cloth_tri = np.ascontiguousarray(cloth_tri, np.uint32)
+        self.cloth_edges = unique_edges(self.cloth_tri)
+        self.inv_mass = np.ones(len(self.cloth_pos), np.float32)
+        self.inv_mass[list(fixed)] = 0.0
+        self.stretch_idx, self.stretch_rest = stretch_constraints(self.cloth_pos, self.cloth_edges)
+        self.bend_idx, self.bend_theta = bend_constraints(self.cloth_pos, self.cloth_tri)
+        self.obs_pos = None if obs_pos is None else np.ascontiguousarray(obs_pos, np.float32)
+        self.obs_tri = None if obs_tri is None else np.ascontiguousarray(obs_tri, np.uint32)
+        self.obs_edges = None if obs_tri is None else unique_edges(self.obs_tri)
+
+    def particle_diameter(self, scale=1.0):
+        # ClothObjectUniversal::Start, impl/universal/ClothObject.hpp:36-37
+        t = self.cloth_tri[0]
+        return float(np.linalg.norm(self.cloth_pos[t[0]] - self.cloth_pos[t[1]])) * scale
+
+
+def drop_scene(n=224, sphere=(64, 128), y=None, seed=SEED, fixed=()):
+    """C1 / C100k: n x n cloth dropped on a UV sphere r = 0.3 m at the origin."""
+    r = 0.3
+    if y is None:
+        y = r + 0.02
+    cp, ct = grid_cloth(n, 1.0, y, 1e-4, seed)
+    op, ot = uv_sphere(r, sphere[0], sphere[1])
+    return Scene(cp, ct, op, ot, fixed)
+
+
+def sphere_motion(obs_pos, frame, amp=0.05, hz=1.0, fps=60.0):
+    """Synthetic body motion: the obstacle bobs vertically and breathes."""
+    t = frame / fps
+    s = 1.0 + 0.03 * np.sin(2 * np.pi * hz * t)
+    out = obs_pos * np.float32(s)
+    out[:, 1] += np.float32(amp * np.sin(2 * np.pi * hz * t))
+    return out.astype(np.float32)
+
+
+def make_solver(scene, colors=None, **params):
+    """Reference call order: AddCloth, AddObstacle, constraints, (colours), Start."""
+    from .solver import ClothSolver
+    if "particle_diameter" not in params:
+        params["particle_diameter"] = scene.particle_diameter()
+    s = ClothSolver(**params)
+    s.AddCloth(scene.cloth_pos, scene.cloth_tri, scene.cloth_edges, scene.inv_mass)
+    if scene.obs_pos is not None:
+        s.AddObstacle(scene.obs_pos, scene.obs_tri, scene.obs_edges)
+    s.SetStretch(scene.stretch_idx, scene.stretch_rest)
+    s.SetBend(scene.bend_idx, scene.bend_theta)
+    if colors is not None:
+        s.SetColors(0, colors[0])
+        s.SetColors(1, colors[1])
+    s.Start()
+    return s

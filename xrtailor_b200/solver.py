@@ -1,0 +1,247 @@
+"""Host-side mirror of the reference's solver component for the Swift path.
+
+Method names follow ``ClothSolverBase`` / ``ClothSolverUniversal``
+(xrtailor/include/xrtailor/pipeline/base/ClothSolverBase.hpp:55-189,
+xrtailor/src/pipeline/impl/universal/ClothSolver.cpp:189-350): ``AddCloth``,
+``AddObstacle``, ``AddGeodesic``, ``Start``, ``SimulateSwift``, ``SaveCache``.
+All numerics happen in libxrt_b200.so; this file only marshals numpy arrays
+across the C ABI.
+"""
+import ctypes as C
+
+import numpy as np
+
+from ._abi import XrtError, XrtMeshDesc, XrtParams, XrtStats, default_params, lib
+
+DBG = dict(MORTON=0, SORTED_OBJECT=1, NODES=2, AABBS=3, ESCAPE_INT=4, ESCAPE_EXT=5, VF_CONTACTS=6, RT_CONTACTS=7,
+           EE_CONTACTS=8, PREDICTED=9, VELOCITY=10, COLORS_STRETCH=11, COLORS_BEND=12, NEIGHBORS=13, RTRI=14,
+           OBSTACLE_PRED=15, STATS=16, PARTICLE_HASH=17, VF_CAND_COUNT=18, RT_CAND_COUNT=19, EE_CAND_COUNT=20)
+
+_f32p = C.POINTER(C.c_float)
+_u32p = C.POINTER(C.c_uint32)
+_i32p = C.POINTER(C.c_int32)
+
+
+def _f32(a):
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _u32(a):
+    return np.ascontiguousarray(a, dtype=np.uint32)
+
+
+def _pf(a):
+    return a.ctypes.data_as(_f32p) if a is not None else None
+
+
+def _pu(a):
+    return a.ctypes.data_as(_u32p) if a is not None else None
+
+
+class ClothSolver:
+    """One solver handle = one CUDA stream on one device."""
+
+    def __init__(self, params: XrtParams = None, **overrides):
+        self.params = params if params is not None else default_params()
+        for k, v in overrides.items():
+            if k == "gravity":
+                for i in range(3):
+                    self.params.gravity[i] = float(v[i])
+            else:
+                setattr(self.params, k, v)
+        self._h = C.c_void_p()
+        rc = lib.xrt_create(C.byref(self.params), C.byref(self._h))
+        if rc:
+            raise XrtError(rc, "xrt_create failed (no usable CUDA device? there is no CPU fallback)")
+        self.n_cloth_verts = self.n_cloth_edges = self.n_obstacle_verts = self.n_obstacle_faces = 0
+        self.solver_time = 0.0
+        # host frame cache like ClothSolverBase::h_cloth_positions_cache (ClothSolverBase.hpp:107-112)
+        self.h_cloth_positions_cache, self.h_cloth_normals_cache = [], []
+
+    # -- lifetime ---------------------------------------------------------
+    def OnDestroy(self):
+        if self._h:
+            lib.xrt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    close = OnDestroy
+
+    def __del__(self):
+        try:
+            self.OnDestroy()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.OnDestroy()
+
+    def _ck(self, rc):
+        if rc:
+            raise XrtError(rc, lib.xrt_last_error(self._h).decode(errors="replace"))
+
+    # -- setup ------------------------------------------------------------
+    def _mesh(self, positions, indices, edges, inv_mass):
+        pos, idx, edg = _f32(positions).reshape(-1, 3), _u32(indices).reshape(-1, 3), _u32(edges).reshape(-1, 2)
+        inv = _f32(inv_mass) if inv_mass is not None else None
+        d = XrtMeshDesc(_pf(pos), _pu(idx), _pu(edg), _pf(inv), len(pos), len(idx), len(edg))
+        return d, (pos, idx, edg, inv)
+
+    def AddCloth(self, positions, indices, edges, inv_mass=None):
+        d, keep = self._mesh(positions, indices, edges, inv_mass)
+        off = C.c_int32()
+        self._ck(lib.xrt_add_cloth(self._h, C.byref(d), C.byref(off)))
+        self.n_cloth_verts, self.n_cloth_edges = d.n_verts, d.n_edges
+        return off.value
+
+    def AddObstacle(self, positions, indices, edges=None, inv_mass=None):
+        if edges is None:
+            edges = np.zeros((0, 2), np.uint32)
+        d, keep = self._mesh(positions, indices, edges, inv_mass)
+        off = C.c_int32()
+        self._ck(lib.xrt_add_obstacle(self._h, C.byref(d), C.byref(off)))
+        self.n_obstacle_verts, self.n_obstacle_faces = d.n_verts, d.n_faces
+        return off.value
+
+    def SetStretch(self, idx01, rest):
+        idx, r = _u32(idx01).reshape(-1, 2), _f32(rest)
+        self._ck(lib.xrt_set_stretch(self._h, _pu(idx), _pf(r), len(r)))
+
+    def SetBend(self, idx0123, theta):
+        idx, t = _u32(idx0123).reshape(-1, 4), _f32(theta)
+        self._ck(lib.xrt_set_bend(self._h, _pu(idx), _pf(t), len(t)))
+
+    def AddGeodesic(self, src, tgt, rest):
+        s, t, r = _u32(src), _u32(tgt), _f32(rest)
+        self._ck(lib.xrt_add_geodesic(self._h, _pu(s), _pu(t), _pf(r), len(r)))
+
+    def SetColors(self, kind, colors):
+        c = _u32(colors)
+        self._ck(lib.xrt_set_colors(self._h, int(kind), _pu(c), len(c)))
+
+    def Start(self):
+        self._ck(lib.xrt_finalize_setup(self._h))
+
+    # -- per frame --------------------------------------------------------
+    def UpdateObstacleAnimationFrame(self, target_xyz):
+        t = _f32(target_xyz).reshape(-1, 3)
+        self._ck(lib.xrt_set_obstacle_target(self._h, _pf(t), len(t)))
+
+    def SimulateSwift(self):
+        ms = C.c_float()
+        self._ck(lib.xrt_step_frame(self._h, C.byref(ms)))
+        self.solver_time = ms.value
+        return ms.value
+
+    def SimulateSwiftAsync(self):
+        self._ck(lib.xrt_step_frame_async(self._h))
+
+    def Sync(self):
+        self._ck(lib.xrt_sync(self._h))
+
+    def GetPositions(self, which=0, normals=False):
+        n = self.n_cloth_verts if which == 0 else self.n_obstacle_verts
+        xyz = np.empty((n, 3), np.float32)
+        nrm = np.empty((n, 3), np.float32) if normals else None
+        self._ck(lib.xrt_get_positions(self._h, which, _pf(xyz), _pf(nrm)))
+        return (xyz, nrm) if normals else xyz
+
+    def SaveCache(self):
+        xyz, nrm = self.GetPositions(0, normals=True)
+        self.h_cloth_positions_cache.append(xyz)
+        self.h_cloth_normals_cache.append(nrm)
+
+    def SetClothState(self, xyz=None, vel=None):
+        x = _f32(xyz).reshape(-1, 3) if xyz is not None else None
+        v = _f32(vel).reshape(-1, 3) if vel is not None else None
+        self._ck(lib.xrt_set_cloth_state(self._h, _pf(x), _pf(v)))
+
+    # -- building blocks (parity tests) ------------------------------------
+    def BvhBuildObstacle(self):
+        self._ck(lib.xrt_bvh_build_obstacle(self._h))
+
+    def BvhRefitObstacle(self, step):
+        self._ck(lib.xrt_bvh_refit_obstacle(self._h, int(step)))
+
+    def GenerateContacts(self):
+        self._ck(lib.xrt_generate_contacts(self._h))
+
+    def HashParticles(self):
+        self._ck(lib.xrt_hash_particles(self._h))
+
+    def PredictPositions(self):
+        self._ck(lib.xrt_predict(self._h))
+
+    def SolveIteration(self, iteration):
+        self._ck(lib.xrt_solve_iteration(self._h, int(iteration)))
+
+    def Finalize(self):
+        self._ck(lib.xrt_finalize(self._h))
+
+    # -- debug ------------------------------------------------------------
+    def debug(self, what, dtype=np.uint8):
+        code = DBG[what] if isinstance(what, str) else int(what)
+        n = C.c_size_t(0)
+        self._ck(lib.xrt_debug_get(self._h, code, None, C.byref(n)))
+        buf = np.empty(n.value, np.uint8)
+        self._ck(lib.xrt_debug_get(self._h, code, buf.ctypes.data_as(C.c_void_p), C.byref(n)))
+        return buf.view(dtype)
+
+    def stats(self):
+        raw = self.debug("STATS")
+        st = XrtStats.from_buffer_copy(raw.tobytes())
+        return {f: getattr(st, f) for f, _ in XrtStats._fields_}
+
+    def bvh(self):
+        """Obstacle BVH as the reference's host accessors return it (BVH.cu:579-602)."""
+        return dict(
+            morton=self.debug("MORTON", np.uint32), object=self.debug("SORTED_OBJECT", np.uint32),
+            nodes=self.debug("NODES", np.uint32).reshape(-1, 4), aabb=self.debug("AABBS", np.float32).reshape(-1, 6),
+            esc_int=self.debug("ESCAPE_INT", np.int32), esc_ext=self.debug("ESCAPE_EXT", np.int32))
+
+    def contacts(self):
+        vf = self.debug("VF_CONTACTS", np.dtype([("index", np.int32), ("q", np.float32, 3)]))
+        rt = self.debug("RT_CONTACTS", np.dtype([("index", np.int32), ("q", np.float32, 3)]))
+        ee = self.debug("EE_CONTACTS", np.float32).reshape(-1, 14)
+        return vf, rt, ee
+
+    def candidates(self, kind):
+        n = self.n_cloth_edges if kind == 2 else self.n_cloth_verts
+        off = np.zeros(n + 1, np.uint32)
+        cnt = C.c_size_t(0)
+        self._ck(lib.xrt_debug_candidates(self._h, kind, _pu(off), None, C.byref(cnt)))
+        items = np.zeros(max(cnt.value, 1), np.uint32)
+        cnt2 = C.c_size_t(cnt.value)
+        self._ck(lib.xrt_debug_candidates(self._h, kind, _pu(off), _pu(items), C.byref(cnt2)))
+        return off, items[:cnt.value]
+
+
+def greedy_color(idx, n_verts):
+    idx = _u32(idx)
+    arity = idx.shape[1]
+    colors = np.zeros(len(idx), np.uint32)
+    nc = C.c_uint32()
+    rc = lib.xrt_greedy_color(_pu(idx), len(idx), arity, n_verts, _pu(colors), C.byref(nc))
+    if rc:
+        raise XrtError(rc, "greedy colouring failed")
+    return colors, nc.value
+
+
+def bvh_build_standalone(positions, indices, fast_div=1, device=0):
+    pos, tri = _f32(positions).reshape(-1, 3), _u32(indices).reshape(-1, 3)
+    F = len(tri)
+    out = dict(morton=np.zeros(F, np.uint32), object=np.zeros(F, np.uint32), nodes=np.zeros((2 * F - 1, 4), np.uint32),
+               aabb=np.zeros((2 * F - 1, 6), np.float32), esc_int=np.zeros(max(F - 1, 1), np.int32),
+               esc_ext=np.zeros(F, np.int32))
+    ms = C.c_float()
+    rc = lib.xrt_bvh_build_standalone(_pf(pos), len(pos), _pu(tri), F, fast_div, device, _pu(out["morton"]),
+                                      _pu(out["object"]), _pu(out["nodes"]), _pf(out["aabb"]),
+                                      out["esc_int"].ctypes.data_as(_i32p), out["esc_ext"].ctypes.data_as(_i32p),
+                                      C.byref(ms))
+    if rc:
+        raise XrtError(rc, "standalone BVH build failed (no CUDA device? there is no CPU fallback)")
+    out["esc_int"] = out["esc_int"][:F - 1]
+    out["build_ms"] = ms.value
+    return out
