@@ -1,0 +1,209 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle.
+Integer / index / box results: bit exact.  Positions: relative RMS <= 1e-5
+after one substep, <= 1e-3 m RMS after 10 frames (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+import xrtailor_b200 as X
+from oracle import oracle as O
+from xrtailor_b200 import scene
+from tests.common import assert_bvh_equal, pair, rel_rms, rms
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def small():
+    return scene.drop_scene(64, sphere=(24, 48))
+
+
+def test_bvh_build_bit_exact(small):
+    s, o = pair(small)
+    assert_bvh_equal(s.bvh(), o.bvh())
+    np.testing.assert_array_equal(s.debug("RTRI", np.uint32), o.rtri())
+    s.close()
+
+
+@pytest.mark.parametrize("n,sph", [(8, (4, 6)), (33, (9, 17)), (120, (64, 128))])
+def test_bvh_standalone_sizes(n, sph):
+    pos, tri = scene.uv_sphere(0.3, *sph)
+    g = X.bvh_build_standalone(pos, tri, fast_div=0)
+    assert_bvh_equal(g, O.Bvh(pos, tri).arrays())
+    pos, tri = scene.grid_cloth(n, jitter=1e-4)
+    g = X.bvh_build_standalone(pos, tri, fast_div=0)
+    assert_bvh_equal(g, O.Bvh(pos, tri).arrays())
+
+
+def test_bvh_duplicate_morton_codes():
+    # no jitter, flat in y: many identical codes -> the reference's 64-bit key path
+    pos, tri = scene.grid_cloth(40, jitter=0.0)
+    tri = np.concatenate([tri, tri])  # every face twice
+    o = O.Bvh(pos, tri).arrays()
+    assert o["used64"] == 1
+    assert_bvh_equal(X.bvh_build_standalone(pos, tri, fast_div=0), o)
+
+
+def test_bvh_tiny():
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [1, 1, 1]], np.float32)
+    for tri in ([[0, 1, 2]], [[0, 1, 2], [1, 2, 3]], [[0, 1, 2], [1, 2, 3], [0, 2, 3]]):
+        assert_bvh_equal(X.bvh_build_standalone(pos, np.array(tri, np.uint32), fast_div=0),
+                         O.Bvh(pos, np.array(tri, np.uint32)).arrays())
+
+
+def test_refit_midstep_bit_exact_boxes(small):
+    s, o = pair(small)
+    tgt = scene.sphere_motion(small.obs_pos, 7)
+    s.UpdateObstacleAnimationFrame(tgt)
+    o.set_obstacle_target(tgt)
+    for step in range(3):
+        s.BvhRefitObstacle(step)
+        o.collision_pass(step)
+        g, c = s.bvh(), o.bvh()
+        np.testing.assert_array_equal(g["nodes"], c["nodes"])
+        # pred = x1 + tol*n1 goes through normals (different summation order): boxes to 1e-6
+        np.testing.assert_allclose(g["aabb"], c["aabb"], rtol=0, atol=2e-6)
+        np.testing.assert_allclose(s.debug("OBSTACLE_PRED", np.float32).reshape(-1, 9), c["pred"], rtol=0, atol=2e-6)
+    s.close()
+
+
+def _settle(s, o, frames):
+    for _ in range(frames):
+        s.SimulateSwift()
+        o.step_frame()
+
+
+def test_candidate_sets_and_contacts(small):
+    s, o = pair(small, enable_self_collision=0)
+    _settle(s, o, 2)
+    # same state on both sides, then one generation pass on each
+    x0, v = o.positions(), o.velocity()
+    s.SetClothState(x0, v)
+    s.PredictPositions()
+    o.predict()
+    np.testing.assert_array_equal(s.debug("PREDICTED", np.float32).reshape(-1, 3), o.predicted())
+    s.GenerateContacts()
+    o.generate_contacts()
+    oc = o.contacts()
+    vf, rt, ee = s.contacts()
+    for kind, key in ((0, "cnt_vf"), (1, "cnt_rt"), (2, "cnt_ee")):
+        off, items = s.candidates(kind)
+        np.testing.assert_array_equal(np.diff(off), oc[key])
+    # candidate lists in traversal order against the oracle's query
+    ob = O.Bvh(small.obs_pos, small.obs_tri)
+    off, items = s.candidates(0)
+    pred = o.predicted()
+    hit = np.nonzero(np.diff(off))[0]
+    assert len(hit) > 0
+    for i in hit[:200]:
+        np.testing.assert_array_equal(items[off[i]:off[i + 1]], ob.query(0, pred[i]))
+    off, items = s.candidates(2)
+    hit = np.nonzero(np.diff(off))[0]
+    for i in hit[:200]:
+        e = small.cloth_edges[i]
+        np.testing.assert_array_equal(items[off[i]:off[i + 1]], ob.query(1, pred[e[0]], pred[e[1]]))
+    np.testing.assert_array_equal(vf["index"], oc["vf_idx"])
+    np.testing.assert_allclose(vf["q"], oc["vf_q"], rtol=0, atol=1e-6)
+    np.testing.assert_array_equal(rt["index"], oc["rt_idx"])
+    np.testing.assert_allclose(rt["q"], oc["rt_q"], rtol=0, atol=1e-6)
+    live = oc["ee"][:, 0] < 1e6
+    np.testing.assert_array_equal(ee[:, 0] < 1e6, live)
+    np.testing.assert_allclose(ee[live], oc["ee"][live], rtol=0, atol=2e-6)
+    s.close()
+
+
+def test_neighbor_lists(small):
+    s, o = pair(small)
+    s.PredictPositions()
+    o.predict()
+    s.HashParticles()
+    o.hash()
+    gh = s.debug("PARTICLE_HASH", np.uint32)
+    oh, oi = o.particle_hash()
+    V = len(small.cloth_pos)
+    np.testing.assert_array_equal(gh[:V], oh)
+    np.testing.assert_array_equal(gh[V:], oi)
+    np.testing.assert_array_equal(s.debug("NEIGHBORS", np.uint32), o.neighbors())
+    s.close()
+
+
+@pytest.mark.parametrize("self_collision", [0, 1])
+def test_one_substep_positions(small, self_collision):
+    s, o = pair(small, num_substeps=1, enable_self_collision=self_collision)
+    s.SimulateSwift()
+    o.step_frame()
+    g, c = s.GetPositions(0), o.positions()
+    assert rel_rms(g, c) <= 1e-5, rel_rms(g, c)
+    # displacement parity too (positions are dominated by the rest pose)
+    d0 = small.cloth_pos.astype(np.float64)
+    assert rel_rms(g - d0, c - d0) <= 1e-3
+    s.close()
+
+
+def test_ten_frames_positions_moving_obstacle(small):
+    s, o = pair(small)
+    for f in range(10):
+        tgt = scene.sphere_motion(small.obs_pos, f + 1)
+        s.UpdateObstacleAnimationFrame(tgt)
+        o.set_obstacle_target(tgt)
+        s.SimulateSwift()
+        o.step_frame()
+    g, gn = s.GetPositions(0, normals=True)
+    assert np.isfinite(g).all()
+    assert rms(g, o.positions()) <= 1e-3, rms(g, o.positions())
+    np.testing.assert_allclose(s.GetPositions(1), scene.sphere_motion(small.obs_pos, 10), atol=1e-7)
+    st = s.stats()
+    assert st["stretch_rms"] < 0.05 and st["launches_per_frame"] > 0
+    s.close()
+
+
+def test_graph_replay_equals_eager_building_blocks(small):
+    """xrt_step_frame (CUDA graph) == the same frame driven call by call."""
+    s1, _ = pair(small, num_substeps=1, num_iterations=4, num_collision_passes=1, enable_self_collision=0)
+    s2, _ = pair(small, num_substeps=1, num_iterations=4, num_collision_passes=1, enable_self_collision=0)
+    s1.SimulateSwift()
+    s2.PredictPositions()
+    s2.GenerateContacts()
+    for it in range(4):
+        s2.SolveIteration(it)
+    s2.Finalize()
+    np.testing.assert_array_equal(s1.GetPositions(0), s2.GetPositions(0))
+    s1.close()
+    s2.close()
+
+
+def test_full_size_properties():
+    """C1 at full size (50k verts): properties that need no oracle run."""
+    sc = scene.drop_scene(224)
+    s = scene.make_solver(sc)
+    for _ in range(3):
+        s.SimulateSwift()
+    x = s.GetPositions(0)
+    assert np.isfinite(x).all()
+    b = s.bvh()
+    F = len(sc.obs_tri)
+    assert (np.diff(b["morton"].astype(np.int64)) >= 0).all()          # sortedness
+    assert sorted(b["object"].tolist()) == list(range(F))               # permutation
+    # every node's box contains its children's boxes
+    n, a = b["nodes"], b["aabb"]
+    for i in range(F - 1):
+        for ch in (n[i, 1], n[i, 2]):
+            assert (a[i, :3] <= a[ch, :3]).all() and (a[i, 3:] >= a[ch, 3:]).all()
+            assert n[ch, 0] == i
+    st = s.stats()
+    assert st["stretch_rms"] < 0.05
+    # cloth rests on / above the sphere
+    r = np.linalg.norm(x, axis=1)
+    assert r.min() > 0.29
+    s.close()
+
+
+def test_error_codes():
+    sc = scene.drop_scene(8, sphere=(4, 6))
+    s = X.ClothSolver()
+    with pytest.raises(X.XrtError) as e:
+        s.SimulateSwift()  # not finalized
+    assert e.value.code == 8100
+    with pytest.raises(X.XrtError) as e:
+        s.AddCloth(sc.cloth_pos, np.array([[0, 1, 999999]], np.uint32), sc.cloth_edges)
+    assert e.value.code == 8100
+    s.close()
