@@ -130,6 +130,8 @@ int xrt_sync(xrt_solver* s);
 int xrt_get_positions(xrt_solver* s, int which, float* xyz, float* nrm);
 /* Overwrite cloth state (x0 and v), for tests and batch seeding. */
 int xrt_set_cloth_state(xrt_solver* s, const float* xyz, const float* vel);
+/* Overwrite the predicted positions (Node::x) only, for parity tests. */
+int xrt_set_cloth_predicted(xrt_solver* s, const float* xyz);
 
 /* Building blocks exposed for parity tests; each one is the same device
  * code xrt_step_frame runs. */

@@ -5,7 +5,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libxrt_b200.so")
+# XRT_B200_LIB=fast selects the --use_fast_math build (A/B timing only)
+LIB_PATH = os.path.join(_HERE, "libxrt_b200_fast.so" if os.environ.get("XRT_B200_LIB") == "fast" else "libxrt_b200.so")
 
 
 class XrtError(RuntimeError):
@@ -48,7 +49,7 @@ SYMBOLS = [
     "xrt_default_params", "xrt_create", "xrt_destroy", "xrt_last_error", "xrt_add_cloth", "xrt_add_obstacle",
     "xrt_set_stretch", "xrt_set_bend", "xrt_add_geodesic", "xrt_set_colors", "xrt_finalize_setup",
     "xrt_set_obstacle_target", "xrt_step_frame", "xrt_step_frame_async", "xrt_sync", "xrt_get_positions",
-    "xrt_set_cloth_state", "xrt_bvh_build_obstacle", "xrt_bvh_refit_obstacle", "xrt_generate_contacts",
+    "xrt_set_cloth_state", "xrt_set_cloth_predicted", "xrt_bvh_build_obstacle", "xrt_bvh_refit_obstacle", "xrt_generate_contacts",
     "xrt_hash_particles", "xrt_predict", "xrt_solve_iteration", "xrt_finalize", "xrt_debug_get",
     "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone",
 ]
@@ -77,6 +78,7 @@ def _load():
         "xrt_sync": [vp],
         "xrt_get_positions": [vp, C.c_int, f32p, f32p],
         "xrt_set_cloth_state": [vp, f32p, f32p],
+        "xrt_set_cloth_predicted": [vp, f32p],
         "xrt_bvh_build_obstacle": [vp],
         "xrt_bvh_refit_obstacle": [vp, C.c_int],
         "xrt_generate_contacts": [vp],

@@ -720,6 +720,17 @@ extern "C" int xrt_set_cloth_state(xrt_solver* s, const float* xyz, const float*
   return XRT_OK;
 }
 
+extern "C" int xrt_set_cloth_predicted(xrt_solver* s, const float* xyz) {
+  XRT_READY();
+  XRT_REQUIRE(xyz, "set_cloth_predicted: null array");
+  const size_t V = s->c.V;
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  for (size_t i = 0; i < V; i++) s->stage[i] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], s->c_invm[i]);
+  XRT_CUDA_OK(cudaMemcpyAsync(s->c.x, s->stage, V * sizeof(float4), cudaMemcpyHostToDevice, s->st));
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  return XRT_OK;
+}
+
 // algorithmic bytes of one frame, SoA-ideal, SURVEY.md section 8(d) with the
 // exact counts of this scene (see DESIGN.md "Roofline accounting")
 static double frame_bytes(const xrt_solver* s, bool moved) {

@@ -31,11 +31,7 @@ __host__ __device__ __forceinline__ f3 cross3(f3 a, f3 b) {
 __host__ __device__ __forceinline__ float len3(f3 a) { return sqrtf(dot3(a, a)); }
 // glm::normalize = v * inversesqrt(dot(v,v))
 __host__ __device__ __forceinline__ f3 normalize3(f3 a) {
-#ifdef __CUDA_ARCH__
-  return a * rsqrtf(dot3(a, a));
-#else
   return a * (1.0f / sqrtf(dot3(a, a)));
-#endif
 }
 __host__ __device__ __forceinline__ float clampf(float x, float lo, float hi) { return fminf(fmaxf(x, lo), hi); }
 // MathFunctions::FaceNormal, math/MathFunctions.cu:14-20

@@ -158,6 +158,10 @@ class ClothSolver:
         v = _f32(vel).reshape(-1, 3) if vel is not None else None
         self._ck(lib.xrt_set_cloth_state(self._h, _pf(x), _pf(v)))
 
+    def SetClothPredicted(self, xyz):
+        x = _f32(xyz).reshape(-1, 3)
+        self._ck(lib.xrt_set_cloth_predicted(self._h, _pf(x)))
+
     # -- building blocks (parity tests) ------------------------------------
     def BvhBuildObstacle(self):
         self._ck(lib.xrt_bvh_build_obstacle(self._h))
