@@ -117,6 +117,13 @@ int xrt_finalize_setup(xrt_solver* s);
  * obstacle vertex positions of the coming frame (host pointer, 3*n floats). */
 int xrt_set_obstacle_target(xrt_solver* s, const float* xyz, size_t n_verts);
 
+/* Pre-stage a whole obstacle animation in device memory (n_frames x n_verts
+ * positions).  With a sequence set, every xrt_step_frame that has no explicit
+ * xrt_set_obstacle_target pending takes the next frame of the sequence
+ * (wrapping) with a device-to-device copy: the reference's SMPL pipeline keeps
+ * its pose sequence resident the same way (impl/smpl/ClothSolver.cpp:239-249). */
+int xrt_set_obstacle_sequence(xrt_solver* s, const float* xyz, size_t n_frames);
+
 /* ClothSolverBase::SimulateSwift (pipeline/base/ClothSolverBase.cpp:171-261).
  * solver_ms (may be NULL) receives the CUDA-event time of the frame, the
  * reference's "Solver_Total". */
@@ -124,6 +131,18 @@ int xrt_step_frame(xrt_solver* s, float* solver_ms);
 /* Same, but enqueue only (no sync, no timing); pair with xrt_sync. */
 int xrt_step_frame_async(xrt_solver* s);
 int xrt_sync(xrt_solver* s);
+
+/* Batch data generation: run `frames` frames on each of n independent
+ * handles (same device), all streams released by one start event and joined
+ * into one end event; *ms = device time between the two.  No host sync
+ * between frames. */
+int xrt_batch_run(xrt_solver** handles, int n, int frames, float* ms);
+
+/* Launch the named step kernel `reps` times on the handle's stream between
+ * two CUDA events; *avg_ms = mean duration of ONE launch, *bytes = its
+ * algorithmic bytes.  which: 0 bend colour pass, 1 stretch colour
+ * pass, 2 collide particles, 3 contact generation (vertex), 4 predict. */
+int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg_ms, double* bytes);
 
 /* SaveCache (impl/universal/ClothSolver.cpp:107-144): which 0 = cloth,
  * 1 = obstacle.  xyz / nrm: 3*n_verts floats each, either may be NULL. */

@@ -48,7 +48,7 @@ class XrtStats(C.Structure):
 SYMBOLS = [
     "xrt_default_params", "xrt_create", "xrt_destroy", "xrt_last_error", "xrt_add_cloth", "xrt_add_obstacle",
     "xrt_set_stretch", "xrt_set_bend", "xrt_add_geodesic", "xrt_set_colors", "xrt_finalize_setup",
-    "xrt_set_obstacle_target", "xrt_step_frame", "xrt_step_frame_async", "xrt_sync", "xrt_get_positions",
+    "xrt_set_obstacle_target", "xrt_set_obstacle_sequence", "xrt_batch_run", "xrt_profile_kernel", "xrt_step_frame", "xrt_step_frame_async", "xrt_sync", "xrt_get_positions",
     "xrt_set_cloth_state", "xrt_set_cloth_predicted", "xrt_bvh_build_obstacle", "xrt_bvh_refit_obstacle", "xrt_generate_contacts",
     "xrt_hash_particles", "xrt_predict", "xrt_solve_iteration", "xrt_finalize", "xrt_debug_get",
     "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone",
@@ -73,6 +73,9 @@ def _load():
         "xrt_set_colors": [vp, C.c_int, u32p, C.c_size_t],
         "xrt_finalize_setup": [vp],
         "xrt_set_obstacle_target": [vp, f32p, C.c_size_t],
+        "xrt_set_obstacle_sequence": [vp, f32p, C.c_size_t],
+        "xrt_batch_run": [C.POINTER(vp), C.c_int, C.c_int, f32p],
+        "xrt_profile_kernel": [vp, C.c_int, C.c_int, f32p, C.POINTER(C.c_double)],
         "xrt_step_frame": [vp, f32p],
         "xrt_step_frame_async": [vp],
         "xrt_sync": [vp],

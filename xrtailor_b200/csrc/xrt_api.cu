@@ -41,6 +41,9 @@ struct xrt_solver {
   float4* stage = nullptr;  // pinned host staging for obstacle targets / readback
   size_t stage_elems = 0;
   float4* d_stage = nullptr;
+  float4* d_seq = nullptr;  // pre-staged obstacle animation [seq_frames][Vo]
+  size_t seq_frames = 0, seq_cursor = 0;
+  cudaEvent_t ev_join = nullptr;
 };
 
 static void xrt_set_error(xrt_solver* s, const char* fmt, ...) {
@@ -593,8 +596,38 @@ extern "C" int xrt_set_obstacle_target(xrt_solver* s, const float* xyz, size_t n
   return XRT_OK;
 }
 
+extern "C" int xrt_set_obstacle_sequence(xrt_solver* s, const float* xyz, size_t n_frames) {
+  XRT_READY();
+  XRT_REQUIRE(s->o.V && xyz && n_frames, "set_obstacle_sequence: no obstacle or empty sequence");
+  const size_t Vo = s->o.V;
+  std::vector<float4> h(n_frames * Vo);
+  for (size_t f = 0; f < n_frames; f++)
+    for (size_t i = 0; i < Vo; i++) {
+      const float* p = xyz + 3 * (f * Vo + i);
+      h[f * Vo + i] = make_float4(p[0], p[1], p[2], s->o_invm[i]);
+    }
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  cudaFree(s->d_seq);
+  s->d_seq = nullptr;
+  XRT_CUDA_OK(dev_upload(&s->d_seq, h));
+  s->seq_frames = n_frames;
+  s->seq_cursor = 0;
+  return XRT_OK;
+}
+
+// next frame of the resident sequence -> obstacle target (device to device)
+static int take_sequence_frame(xrt_solver* s) {
+  if (s->target_pending || !s->seq_frames) return XRT_OK;
+  const float4* src = s->d_seq + (s->seq_cursor % s->seq_frames) * s->o.V;
+  XRT_CUDA_OK(cudaMemcpyAsync(s->o.x, src, s->o.V * sizeof(float4), cudaMemcpyDeviceToDevice, s->st));
+  s->seq_cursor++;
+  s->target_pending = true;
+  return XRT_OK;
+}
+
 extern "C" int xrt_step_frame_async(xrt_solver* s) {
   XRT_READY();
+  if (int rc0 = take_sequence_frame(s)) return rc0;
   const int moved = s->target_pending ? 1 : 0;
   int rc = ensure_graph(s, moved);
   if (rc) return rc;
@@ -611,6 +644,7 @@ extern "C" int xrt_sync(xrt_solver* s) {
 
 extern "C" int xrt_step_frame(xrt_solver* s, float* solver_ms) {
   XRT_READY();
+  if (int rc0 = take_sequence_frame(s)) return rc0;
   const int moved = s->target_pending ? 1 : 0;
   int rc = ensure_graph(s, moved);
   if (rc) return rc;
@@ -620,6 +654,87 @@ extern "C" int xrt_step_frame(xrt_solver* s, float* solver_ms) {
   s->target_pending = false;
   XRT_CUDA_OK(cudaStreamSynchronize(s->st));
   if (solver_ms) XRT_CUDA_OK(cudaEventElapsedTime(solver_ms, s->ev0, s->ev1));
+  return XRT_OK;
+}
+
+extern "C" int xrt_batch_run(xrt_solver** handles, int n, int frames, float* ms) {
+  if (!handles || n <= 0 || frames < 0) return XRT_ERR_INVALID;
+  xrt_solver* s = handles[0];
+  XRT_READY();
+  for (int i = 0; i < n; i++) {
+    if (!handles[i] || !handles[i]->finalized || handles[i]->p.device != s->p.device) {
+      xrt_set_error(s, "batch_run: handle %d is null, not finalized or on another device", i);
+      return XRT_ERR_INVALID;
+    }
+    if (!handles[i]->ev_join) XRT_CUDA_OK(cudaEventCreateWithFlags(&handles[i]->ev_join, cudaEventDisableTiming));
+  }
+  XRT_CUDA_OK(cudaEventRecord(s->ev0, s->st));
+  for (int i = 1; i < n; i++) XRT_CUDA_OK(cudaStreamWaitEvent(handles[i]->st, s->ev0, 0));
+  for (int f = 0; f < frames; f++)
+    for (int i = 0; i < n; i++) {
+      int rc = xrt_step_frame_async(handles[i]);
+      if (rc) {
+        if (i) xrt_set_error(s, "batch_run: handle %d: %s", i, handles[i]->err);
+        return rc;
+      }
+    }
+  for (int i = 1; i < n; i++) {
+    XRT_CUDA_OK(cudaEventRecord(handles[i]->ev_join, handles[i]->st));
+    XRT_CUDA_OK(cudaStreamWaitEvent(s->st, handles[i]->ev_join, 0));
+  }
+  XRT_CUDA_OK(cudaEventRecord(s->ev1, s->st));
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  if (ms) XRT_CUDA_OK(cudaEventElapsedTime(ms, s->ev0, s->ev1));
+  return XRT_OK;
+}
+
+extern "C" int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg_ms, double* bytes) {
+  XRT_READY();
+  XRT_REQUIRE(reps > 0 && avg_ms && bytes, "profile_kernel: bad argument");
+  const ClothDev& c = s->c;
+  int launches = 0;
+  double b = 0;
+  for (int pass = 0; pass < 2; pass++) {  // pass 0 warms up, pass 1 is timed
+    if (pass == 1) XRT_CUDA_OK(cudaEventRecord(s->ev0, s->st));
+    launches = 0;
+    for (int r = 0; r < (pass ? reps : 3); r++) {
+      switch (which) {
+        case 0:
+          for (uint32_t col = 0; col < c.n_bc; col++, launches++)
+            launch_bend_color(c, s->k, s->b_off[col], s->b_off[col + 1], s->atomic_b, s->st);
+          b = 160.0 * c.n_bend / std::max(1u, c.n_bc);
+          break;
+        case 1:
+          for (uint32_t col = 0; col < c.n_sc; col++, launches++)
+            launch_stretch_color(c, s->k, s->s_off[col], s->s_off[col + 1], 1, s->atomic_s, s->st);
+          b = 84.0 * c.n_stretch / std::max(1u, c.n_sc);
+          break;
+        case 2:
+          launch_collide_particles(c, s->k, s->st);
+          launches += 2;
+          b = ((4.0 * 8 + 16.0 * 8 + 36.0) * c.V + 52.0 * c.V) / 2;
+          break;
+        case 3:
+          XRT_REQUIRE(s->o.F, "no obstacle");
+          launch_generate_contacts(c, s->bvh, s->o.rtri, s->st);
+          launches += c.E ? 2 : 1;
+          b = (96.0 * c.V + 88.0 * c.E) / (c.E ? 2 : 1);
+          break;
+        case 4:
+          launch_predict(c, s->k, s->st);
+          launches++;
+          b = 64.0 * c.V;
+          break;
+        default: xrt_set_error(s, "profile_kernel: unknown kernel %d", which); return XRT_ERR_INVALID;
+      }
+    }
+  }
+  XRT_CUDA_OK(cudaEventRecord(s->ev1, s->st));
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  float ms = 0;
+  XRT_CUDA_OK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+  *avg_ms = ms / (float)std::max(1, launches);
+  *bytes = b;
   return XRT_OK;
 }
 
@@ -912,12 +1027,13 @@ extern "C" void xrt_destroy(xrt_solver* s) {
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
                   c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf,
                   c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
-                  s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage};
+                  s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq};
   for (void* p : ptrs) cudaFree(p);
   if (s->bvh.n_obj) bvh_free(&s->bvh, &s->bw);
   if (s->stage) cudaFreeHost(s->stage);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
+  if (s->ev_join) cudaEventDestroy(s->ev_join);
   if (s->st) cudaStreamDestroy(s->st);
   delete s;
 }

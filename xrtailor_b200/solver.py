@@ -129,6 +129,15 @@ class ClothSolver:
         t = _f32(target_xyz).reshape(-1, 3)
         self._ck(lib.xrt_set_obstacle_target(self._h, _pf(t), len(t)))
 
+    def SetObstacleSequence(self, frames_xyz):
+        t = _f32(frames_xyz).reshape(-1, self.n_obstacle_verts, 3)
+        self._ck(lib.xrt_set_obstacle_sequence(self._h, _pf(t), len(t)))
+
+    def ProfileKernel(self, which, reps=20):
+        ms, b = C.c_float(), C.c_double()
+        self._ck(lib.xrt_profile_kernel(self._h, int(which), int(reps), C.byref(ms), C.byref(b)))
+        return ms.value, b.value
+
     def SimulateSwift(self):
         ms = C.c_float()
         self._ck(lib.xrt_step_frame(self._h, C.byref(ms)))
@@ -220,6 +229,16 @@ class ClothSolver:
         cnt2 = C.c_size_t(cnt.value)
         self._ck(lib.xrt_debug_candidates(self._h, kind, _pu(off), _pu(items), C.byref(cnt2)))
         return off, items[:cnt.value]
+
+
+def batch_run(solvers, frames):
+    """Run `frames` frames on every solver concurrently; returns device ms."""
+    arr = (C.c_void_p * len(solvers))(*[s._h for s in solvers])
+    ms = C.c_float()
+    rc = lib.xrt_batch_run(arr, len(solvers), int(frames), C.byref(ms))
+    if rc:
+        raise XrtError(rc, lib.xrt_last_error(solvers[0]._h).decode(errors="replace"))
+    return ms.value
 
 
 def greedy_color(idx, n_verts):
