@@ -1,0 +1,293 @@
+#!/usr/bin/env python
+"""bench.py — simulated frames/s of the Swift-mode cloth hot path on B200.
+
+  python bench.py --gpus N --steps K --warmup W            (ours, CUDA through the C ABI)
+  python bench.py --impl reference --gpus N --steps K ...   (reference arm, see below)
+
+One "step" = one simulated frame (1/60 s = S substeps) of every instance on
+this GPU.  Workload C1m: 224x224 grid cloth (50,176 verts) draped
+on a moving UV sphere (8,066 verts, synthetic body motion), Swift S=4 N=10
+C=10, bending and self-collision on.  `value` = frames/s over all GPUs with the
+obstacle animation resident in HBM; `e2e` = the same through host buffers
+(H2D of each frame's obstacle target, D2H of positions + normals).  Multi-GPU is
+replica sharding (independent instances, no collective on the timed path).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "simulated_frames_per_sec"
+UNIT = "frames/s"
+SEED = 20261104
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+                for n, v in zip(names, r[2:6]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def build_scene(n):
+    from xrtailor_b200 import scene
+    return scene.drop_scene(n)
+
+
+def motion_sequence(sc, frames, phase=0.0, amp=0.05):
+    from xrtailor_b200 import scene
+    return np.stack([scene.sphere_motion(sc.obs_pos, f + 1 + phase, amp=amp) for f in range(frames)])
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import xrtailor_b200 as X
+    from xrtailor_b200 import scene
+
+    rank, local_rank, world = dist_env()
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    sc = build_scene(args.n)
+    V, E, Vo = len(sc.cloth_pos), len(sc.cloth_edges), len(sc.obs_pos)
+    M = args.instances
+    rng = np.random.default_rng(SEED + rank)
+    seq_len = 60
+    solvers, seqs = [], []
+    for i in range(M):
+        # seed-varied instances: jittered cloth, phase / amplitude of the body motion
+        sci = scene.Scene(sc.cloth_pos + rng.uniform(-1e-4, 1e-4, sc.cloth_pos.shape).astype(np.float32),
+                          sc.cloth_tri, sc.obs_pos, sc.obs_tri)
+        s = scene.make_solver(sci, device=local_rank, fused_iterations=args.fused)
+        seq = motion_sequence(sc, seq_len, phase=float(rng.uniform(0, 30)), amp=float(rng.uniform(0.03, 0.06)))
+        s.SetObstacleSequence(seq)
+        solvers.append(s)
+        seqs.append(seq)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident throughput -------------------------------------
+    X.batch_run(solvers, args.warmup)
+    barrier()
+    with ClockSampler(local_rank) as clk:
+        ms = X.batch_run(solvers, args.steps)
+    barrier()
+    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    frames_total = world * M * args.steps
+    value = frames_total / (ms_max * 1e-3)
+    st = solvers[0].stats()
+
+    # ---- single instance latency (ms / frame, ms / substep) --------------
+    lat = [solvers[0].SimulateSwift() for _ in range(max(5, args.steps))]
+    ms_frame_single = float(np.median(lat))
+
+    # ---- end to end through host buffers ---------------------------------
+    xyz = [np.empty((V, 3), np.float32) for _ in range(M)]
+    barrier()
+    t0 = time.perf_counter()
+    for f in range(args.steps):
+        for i, s in enumerate(solvers):
+            s.UpdateObstacleAnimationFrame(seqs[i][f % seq_len])   # H2D, pinned staging inside the library
+            s.SimulateSwiftAsync()
+        for i, s in enumerate(solvers):
+            xyz[i], _nrm = s.GetPositions(0, normals=True)         # D2H positions + normals (SaveCache)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = frames_total / float(t.item())
+    assert all(np.isfinite(a).all() for a in xyz)
+
+    # ---- roofline of the dominant kernel (bend colour pass) ---------------
+    peak, peak_src = peaks()
+    k_ms, k_bytes = solvers[0].ProfileKernel(0, reps=50)
+    achieved = k_bytes / (k_ms * 1e-3) / 1e9
+    traffic = None
+    tf = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tf):
+        try:
+            traffic = json.load(open(tf)).get("bend_color_kernel")
+        except Exception:
+            traffic = None
+    roofline = {"bound": "hbm", "kernel": "bend_color_kernel", "achieved": round(achieved, 2), "peak": peak,
+                "peak_source": peak_src, "unit": "GB/s", "frac": round(achieved / peak, 5), "traffic": traffic,
+                "bytes_per_launch": k_bytes, "us_per_launch": round(k_ms * 1e3, 3),
+                "frame_algorithmic_GBps": round(st["bytes_per_frame"] * M / (ms_max / args.steps * 1e-3) / 1e9, 2)}
+
+    out = None
+    if rank == 0:
+        cpu = cpu_baseline(args, sc) if (world == 1 and not args.no_cpu) else None
+        out = {
+            "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"C1m: {args.n}x{args.n} grid cloth ({V} verts, {E} edges) on moving UV sphere "
+                                   f"({Vo} verts), Swift S=4 N=10 C=10, bending+self-collision on",
+                       "instances_per_gpu": M, "parallelism": f"replicas x{world}",
+                       "l2_policy": "instances' working sets are cycled (M instances x ~25 MB each); inputs are "
+                                    "larger than one kernel's reuse window but a single instance fits L2",
+                       "single_instance_ms_per_frame": round(ms_frame_single, 4),
+                       "single_instance_ms_per_substep": round(ms_frame_single / 4, 4),
+                       "fused_iterations": args.fused, "colors": [st["n_stretch_colors"], st["n_bend_colors"]]},
+            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(M * Vo * 16),
+                    "d2h_bytes_per_step": int(M * V * 16 * 2)},
+            "gpu_launches": int(st["launches_per_frame"] * M * args.steps),
+            "clocks": clk.summary(), "roofline": roofline,
+        }
+        if cpu:
+            out["cpu_baseline"] = cpu
+        print(json.dumps(out), flush=True)
+    for s in solvers:
+        s.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return out
+
+
+def oracle_frames(sc, frames, n_threads=1):
+    """Time the CPU oracle (kind 'port') on `frames` frames of the workload."""
+    import xrtailor_b200 as X
+    from oracle import oracle as O
+    from xrtailor_b200 import scene
+    p = X.default_params()
+    p.particle_diameter = sc.particle_diameter()
+    cs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
+    cb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+    o = O.Scene(sc, p, (cs, cb))
+    t0 = time.perf_counter()
+    for f in range(frames):
+        o.set_obstacle_target(scene.sphere_motion(sc.obs_pos, f + 1))
+        o.step_frame()
+    return time.perf_counter() - t0
+
+
+def cpu_baseline(args, sc):
+    frames = args.cpu_frames
+    dt = oracle_frames(sc, frames)
+    return {"value": round(frames / dt, 4), "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": f"{frames} frames of the same workload on the CPU oracle (oracle/xrt_oracle.c, scalar C, 1 thread)"}
+
+
+def run_reference(args):
+    """Reference arm.  The reference has no CPU implementation of this path
+    (SURVEY.md F4); its own CUDA physics, built by oracle/ref_harness into
+    oracle/_ref, is timed when that build exists, else the CPU oracle port."""
+    rank, local_rank, world = dist_env()
+    if rank != 0:
+        return
+    sc = build_scene(args.n)
+    ref = None
+    try:
+        from oracle.ref_harness import ref as ref_mod
+        ref = ref_mod if ref_mod.available() else None
+    except Exception:
+        ref = None
+    if ref is not None:
+        res = ref.time_frames(sc, steps=args.steps, warmup=args.warmup, device=local_rank)
+        value, kind, cores = res["frames_per_s"], "reference", res.get("cores", 1)
+        sample = res["sample"]
+        ms_step = res["ms_per_frame"]
+    else:
+        frames = max(1, min(args.steps, args.cpu_frames))
+        dt = oracle_frames(sc, frames)
+        value, kind, cores = frames / dt, "port", 1
+        sample = f"{frames} frames on the CPU oracle port (the reference's CUDA harness is not built on this box)"
+        ms_step = dt / frames * 1e3
+    out = {"impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"C1m: {args.n}x{args.n} grid cloth on moving UV sphere, Swift S=4 N=10 C=10"},
+           "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+           "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=224, help="cloth grid size (224 -> 50,176 verts; 317 -> 100,489)")
+    ap.add_argument("--instances", type=int, default=8, help="independent simulations per GPU")
+    ap.add_argument("--fused", type=int, default=0)
+    ap.add_argument("--cpu-frames", type=int, default=8)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
