@@ -42,3 +42,11 @@ def assert_bvh_equal(g, o):
     np.testing.assert_array_equal(g["esc_int"], o["esc_int"])
     np.testing.assert_array_equal(g["esc_ext"], o["esc_ext"])
     np.testing.assert_array_equal(g["aabb"], o["aabb"])  # min/max only: bit exact
+
+
+def stretch_stats(sc, x):
+    """RMS / max of (|xi-xj|-rest)/rest, the statistic xrt_stats reports."""
+    x = np.asarray(x, np.float64)
+    d = np.linalg.norm(x[sc.stretch_idx[:, 0]] - x[sc.stretch_idx[:, 1]], axis=1)
+    e = (d - sc.stretch_rest) / sc.stretch_rest
+    return float(np.sqrt((e * e).mean())), float(np.abs(e).max())

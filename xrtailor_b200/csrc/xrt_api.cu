@@ -82,12 +82,12 @@ extern "C" int xrt_default_params(xrt_params* p) {
   p->max_num_neighbors = 64;     // Common.hpp:36
   p->gravity[0] = 0.f; p->gravity[1] = -9.8f; p->gravity[2] = 0.f;
   p->damping = 0.98f;
-  p->relaxation_factor = 0.25f;
-  p->long_range_stretchiness = 1.0f;
+  p->relaxation_factor = 0.9f;      // examples/smpl/simulation_conf_smpl.json FABRIC
+  p->long_range_stretchiness = 1.1f;
   p->sdf_friction = 0.1f;
   p->bvh_tolerance = 0.003f;     // config/Base.hpp:131 default (F10 in SURVEY.md)
   p->stretch_compliance = 0.0f;
-  p->bend_compliance = 10.0f;
+  p->bend_compliance = 100.0f;      // config/Base.hpp:40
   p->particle_diameter = 0.0f;   // 0: derive from the first edge like ClothObject.hpp:36-37
   p->hash_cell_size = 1.5f;
   p->inter_leaved_hash = 3;

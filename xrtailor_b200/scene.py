@@ -117,7 +117,7 @@ class Scene:
         self.obs_tri = None if obs_tri is None else np.ascontiguousarray(obs_tri, np.uint32)
         self.obs_edges = None if obs_tri is None else unique_edges(self.obs_tri)
 
-    def particle_diameter(self, scale=1.0):
+    def particle_diameter(self, scale=1.3):  # PARTICLE_DIAMETER of examples/smpl/simulation_conf_smpl.json
         # ClothObjectUniversal::Start, impl/universal/ClothObject.hpp:36-37
         t = self.cloth_tri[0]
         return float(np.linalg.norm(self.cloth_pos[t[0]] - self.cloth_pos[t[1]])) * scale
