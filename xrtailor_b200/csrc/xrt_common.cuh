@@ -55,7 +55,7 @@ struct VFContact {  // pbd_collision/Contact.cuh VFContact / RTContact
   int32_t index;
   float q[3];
 };
-struct EEContact {  // pbd_collision/Contact.cuh EEContact (56 bytes)
+struct EEContact {  // pbd_collision/Contact.cuh EEContact (48 bytes)
   float dist;
   float p2[3], q2[3];
   float s, t;

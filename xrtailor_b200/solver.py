@@ -217,7 +217,7 @@ class ClothSolver:
     def contacts(self):
         vf = self.debug("VF_CONTACTS", np.dtype([("index", np.int32), ("q", np.float32, 3)]))
         rt = self.debug("RT_CONTACTS", np.dtype([("index", np.int32), ("q", np.float32, 3)]))
-        ee = self.debug("EE_CONTACTS", np.float32).reshape(-1, 14)
+        ee = self.debug("EE_CONTACTS", np.float32).reshape(-1, 12)  # dist, p2, q2, s, t, fn
         return vf, rt, ee
 
     def candidates(self, kind):
