@@ -1,0 +1,220 @@
+"""The CPU oracle against known answers and brute-force restatements (numpy),
+so the checker itself is checked before the GPU parity tests trust it."""
+import numpy as np
+import pytest
+
+import xrtailor_b200 as X
+from oracle import oracle as O
+from xrtailor_b200 import scene
+
+
+def test_expand_bits_and_morton_known_answers():
+    # expand_bits inserts two zeros after each of the 10 input bits (BVH.cu:16-24)
+    assert O.L.oracle_expand_bits(0) == 0
+    assert O.L.oracle_expand_bits(1) == 1
+    assert O.L.oracle_expand_bits(0b11) == 0b1001
+    assert O.L.oracle_expand_bits(0x3FF) == 0x09249249
+    for v in (5, 77, 512, 1023):
+        ref = sum(((v >> b) & 1) << (3 * b) for b in range(10))
+        assert O.L.oracle_expand_bits(v) == ref
+    # morton = xx*4 + yy*2 + zz with 10-bit quantisation, clamped to [0, 1023]
+    assert O.L.oracle_morton_code(0.0, 0.0, 0.0) == 0
+    assert O.L.oracle_morton_code(1.0, 1.0, 1.0) == 0x3FFFFFFF
+    assert O.L.oracle_morton_code(2.0, -1.0, 0.5) == (0x09249249 << 2) + O.L.oracle_expand_bits(512)
+    assert O.L.oracle_morton_code(float("nan"), 0.0, 0.0) == 0
+    assert O.L.oracle_morton_code(1 / 1024, 0.0, 0.0) == 4
+
+
+def _brute_tree_checks(b, F):
+    n, aabb = b["nodes"], b["aabb"]
+    NI = F - 1
+    assert n[0, 0] == 0xFFFFFFFF
+    # every non-root node has exactly one parent that lists it as a child
+    for i in range(1, 2 * F - 1):
+        p = n[i, 0]
+        assert i in (n[p, 1], n[p, 2])
+    # leaves hold the sorted objects, boxes are the exact union of children
+    np.testing.assert_array_equal(n[NI:, 3], b["object"])
+    for i in range(NI):
+        l, r = n[i, 1], n[i, 2]
+        np.testing.assert_array_equal(aabb[i, :3], np.minimum(aabb[l, :3], aabb[r, :3]))
+        np.testing.assert_array_equal(aabb[i, 3:], np.maximum(aabb[l, 3:], aabb[r, 3:]))
+    assert (np.diff(b["morton"].astype(np.int64)) >= 0).all()
+
+
+def _dfs_escape(n, F):
+    """Escape links from a pre-order walk: the node visited after a subtree."""
+    NI = F - 1
+    order, stack = [], [0]
+    size = {}
+    def walk(i):
+        order.append(i)
+        if n[i, 3] != 0xFFFFFFFF:
+            size[i] = 1
+            return 1
+        s = 1 + walk(int(n[i, 1])) + walk(int(n[i, 2]))
+        size[i] = s
+        return s
+    import sys
+    sys.setrecursionlimit(10000)
+    walk(0)
+    pos = {v: k for k, v in enumerate(order)}
+    esc = {}
+    for v in order:
+        k = pos[v] + size[v]
+        esc[v] = order[k] if k < len(order) else -1
+    return esc
+
+
+@pytest.mark.parametrize("mesh", ["sphere", "grid", "dups"])
+def test_bvh_structure_and_escape_tables(mesh):
+    if mesh == "sphere":
+        pos, tri = scene.uv_sphere(0.3, 10, 16)
+    elif mesh == "grid":
+        pos, tri = scene.grid_cloth(12, jitter=1e-4)
+    else:
+        pos, tri = scene.grid_cloth(9, jitter=0.0)
+        tri = np.concatenate([tri, tri[:17]])
+    F = len(tri)
+    b = O.Bvh(pos, tri).arrays()
+    assert b["used64"] == (1 if mesh == "dups" else 0) or mesh == "grid"
+    _brute_tree_checks(b, F)
+    esc = _dfs_escape(b["nodes"], F)
+    NI = F - 1
+    assert [esc[i] for i in range(NI)] == b["esc_int"].tolist()
+    assert [esc[NI + i] for i in range(F)] == b["esc_ext"].tolist()
+    # the O(1) formula the CUDA build uses (xrt_bvh.cu escape_after) gives the same links
+    first = {}
+    def rng(i):
+        if b["nodes"][i, 3] != 0xFFFFFFFF:
+            k = i - NI
+            return k, k
+        l = rng(int(b["nodes"][i, 1])); r = rng(int(b["nodes"][i, 2]))
+        first[i] = (l[0], r[1])
+        return first[i]
+    rng(0)
+    def after(last):
+        if last >= F - 1:
+            return -1
+        k = last + 1
+        return k if (k <= F - 2 and first[k][0] == k) else NI + k
+    assert [after(first[i][1]) for i in range(NI)] == b["esc_int"].tolist()
+    assert [after(i) for i in range(F)] == b["esc_ext"].tolist()
+
+
+def test_stackless_queries_equal_brute_force():
+    pos, tri = scene.uv_sphere(0.3, 12, 20)
+    F = len(tri)
+    bv = O.Bvh(pos, tri)
+    b = bv.arrays()
+    leaf = b["aabb"][F - 1:]
+    obj = b["object"]
+    rng = np.random.default_rng(scene.SEED)
+    pts = rng.uniform(-0.35, 0.35, (300, 3)).astype(np.float32)
+    hits_total = 0
+    for p in pts:
+        inside = np.all((p > leaf[:, :3]) & (p < leaf[:, 3:]), axis=1)
+        got = bv.query(0, p)
+        np.testing.assert_array_equal(got, obj[inside])  # traversal order == leaf order
+        hits_total += len(got)
+    assert hits_total > 20
+    for _ in range(200):
+        p1 = rng.uniform(-0.4, 0.4, 3).astype(np.float32)
+        p2 = (p1 + rng.uniform(-0.05, 0.05, 3)).astype(np.float32)
+        brute = [obj[i] for i in range(F) if O.L.oracle_overlap_segment_f(O._pf(leaf[i].copy()), O._pf(p1), O._pf(p2))]
+        np.testing.assert_array_equal(bv.query(1, p1, p2), np.array(brute, np.uint32))
+
+
+def test_nearest_point_against_dense_sampling():
+    rng = np.random.default_rng(7)
+    for _ in range(100):
+        t = rng.normal(size=(3, 3)).astype(np.float32)
+        p = rng.normal(size=3).astype(np.float32) * 2
+        qs = np.zeros(3, np.float32)
+        d = O.L.oracle_nearest_point_f(O._pf(p), O._pf(t.ravel().copy()), O._pf(qs))
+        u, v = np.meshgrid(np.linspace(0, 1, 120), np.linspace(0, 1, 120))
+        m = u + v <= 1
+        cand = t[0] + u[m][:, None] * (t[1] - t[0]) + v[m][:, None] * (t[2] - t[0])
+        brute = np.linalg.norm(cand - p, axis=1).min()
+        assert d <= brute + 1e-5 and d >= brute - 0.03
+        assert abs(np.linalg.norm(p - qs) - d) < 1e-5
+
+
+def test_ray_and_segment_known_answers():
+    tri = np.array([0, 0, 0, 1, 0, 0, 0, 1, 0], np.float32)
+    o = np.array([0.25, 0.25, 1.0], np.float32)
+    d = np.array([0, 0, -1], np.float32)
+    assert abs(O.L.oracle_ray_intersect_f(O._pf(o), O._pf(d), 2.0, O._pf(tri)) - 1.0) < 1e-6
+    assert O.L.oracle_ray_intersect_f(O._pf(o), O._pf(d), 0.5, O._pf(tri)) == np.inf       # too short: "no hit"
+    o2 = np.array([2, 2, 1], np.float32)
+    assert O.L.oracle_ray_intersect_f(O._pf(o2), O._pf(d), 2.0, O._pf(tri)) == np.float32(3.4028235e38)  # outside
+    par = np.array([1, 0, 0], np.float32)
+    assert O.L.oracle_ray_intersect_f(O._pf(o), O._pf(par), 2.0, O._pf(tri)) == np.float32(3.4028235e38)  # parallel
+    # crossing segments at distance 1 (Ericson 5.1.9)
+    seg = np.array([-1, 0, 0, 1, 0, 0, 0, -1, 1, 0, 1, 1], np.float32)
+    st, cc = np.zeros(2, np.float32), np.zeros(6, np.float32)
+    dist = O.L.oracle_closest_seg_seg_f(O._pf(seg), O._pf(st), O._pf(cc))
+    assert abs(dist - 1) < 1e-6 and np.allclose(st, [0.5, 0.5]) and np.allclose(cc, [0, 0, 0, 0, 0, 1])
+    # both degenerate
+    seg = np.array([0, 0, 0, 0, 0, 0, 3, 4, 0, 3, 4, 0], np.float32)
+    assert abs(O.L.oracle_closest_seg_seg_f(O._pf(seg), O._pf(st), O._pf(cc)) - 5) < 1e-6
+
+
+def test_rtriangle_owns_every_edge_and_vertex_once():
+    pos, tri = scene.uv_sphere(0.3, 8, 12)
+    info = O.rtri(tri, len(pos))
+    verts = np.zeros(len(pos), int)
+    edges = {}
+    for f, t in enumerate(tri):
+        for i in range(3):
+            if (info[f] >> i) & 1:
+                verts[t[i]] += 1
+            if (info[f] >> (i + 3)) & 1:
+                e = tuple(sorted((int(t[i]), int(t[(i + 1) % 3]))))
+                edges[e] = edges.get(e, 0) + 1
+    assert (verts == 1).all()
+    assert len(edges) == len(scene.unique_edges(tri)) and set(edges.values()) == {1}
+
+
+def test_free_fall_and_rest_are_exact():
+    """No obstacle, no constraints violated: positions follow x += v dt with v += g dt (damped)."""
+    sc = scene.Scene(*scene.grid_cloth(6, jitter=0.0))
+    p = X.default_params()
+    p.particle_diameter = sc.particle_diameter()
+    p.enable_self_collision = 0
+    cs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
+    cb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+    o = O.Scene(sc, p, (cs, cb))
+    o.step_frame()
+    dt = np.float32(p.frame_dt / p.num_substeps)
+    y, v = np.float32(sc.cloth_pos[0, 1]), np.float32(0)
+    for _ in range(p.num_substeps):
+        v = np.float32(v + np.float32(-9.8) * dt)
+        yn = np.float32(y + v * dt)
+        v = np.float32(np.float32((yn - y) / dt) * np.float32(1 - np.float32(p.damping) * dt))
+        y = yn
+    # rigid translation: stretch keeps rest lengths to rounding, bend adds an in-plane push of ~1e-7
+    assert np.abs(o.positions()[:, 1] - y).max() < 2e-5
+    assert np.abs(o.velocity()[:, 1] - v).max() < 2e-3
+    # pinned cloth stays put
+    sc2 = scene.Scene(*scene.grid_cloth(6, jitter=0.0), fixed=range(36))
+    o2 = O.Scene(sc2, p, (cs, cb))
+    o2.step_frame()
+    np.testing.assert_array_equal(o2.positions(), sc2.cloth_pos)
+
+
+def test_contact_keeps_cloth_outside_sphere():
+    sc = scene.drop_scene(24, sphere=(12, 24))
+    p = X.default_params()
+    p.particle_diameter = sc.particle_diameter()
+    cs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
+    cb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+    o = O.Scene(sc, p, (cs, cb))
+    for _ in range(20):
+        o.step_frame()
+    x = o.positions()
+    assert np.isfinite(x).all()
+    r = np.linalg.norm(x, axis=1)
+    assert r.min() > 0.295          # nothing tunnels into the r = 0.3 sphere (faceted: ~0.297 at face centres)
+    c = o.contacts()
+    assert (c["vf_idx"] >= 0).sum() > 10 and (c["ee"][:, 0] < 1e6).sum() > 10
