@@ -1,0 +1,380 @@
+// GL-free harness around the reference's own CUDA physics translation units
+// (openxrlab/xrtailor @ 4eaf5c3, compiled in place from /root/reference by
+// oracle/ref_harness/Makefile).  TEST INFRASTRUCTURE ONLY: it is the oracle the
+// CUDA product is checked against on the GPU box and the reference arm of
+// bench.py.  This file contains no physics: it builds the reference's objects
+// (MemoryPool, PhysicsMesh, BVH, StretchSolver, ...) and restates the call
+// sequence of ClothSolverUniversal::Start
+// (src/pipeline/impl/universal/ClothSolver.cpp:46-93) and
+// ClothSolverBase::SimulateSwift (src/pipeline/base/ClothSolverBase.cpp:171-261)
+// call for call, with ClothSolverSMPL::UpdateObstacleAnimationFrame's BVH
+// rebuild (src/pipeline/impl/smpl/ClothSolver.cpp:257-261) for a moving obstacle.
+#include <map>
+#include <memory>
+#include <vector>
+
+#include <xrtailor/core/Global.hpp>
+#include <xrtailor/memory/MemoryPool.cuh>
+#include <xrtailor/physics/ClothSolverHelper.cuh>
+#include <xrtailor/physics/PhysicsMesh.cuh>
+#include <xrtailor/physics/broad_phase/lbvh/BVH.cuh>
+#include <xrtailor/physics/broad_phase/spatial_hash/SpatialHashGPU.cuh>
+#include <xrtailor/physics/dynamics/BasicSolver.cuh>
+#include <xrtailor/physics/dynamics/BindingConstraint.cuh>
+#include <xrtailor/physics/dynamics/LongRangeAttachments.cuh>
+#include <xrtailor/physics/pbd_collision/Constraint.cuh>
+#include <xrtailor/physics/representative_triangle/RTriangle.cuh>
+#include <xrtailor/utils/Timer.hpp>
+
+using namespace XRTailor;
+
+namespace {
+__global__ void SetTarget_Kernel(Node** nodes, const float* xyz, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  nodes[i]->x = Vector3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);  // UpdateObstaclePredicted_Kernel with identity matrices
+}
+__global__ void SetInvMass_Kernel(Node** nodes, const float* w, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  nodes[i]->inv_mass = w[i];
+  if (w[i] == 0.0f) nodes[i]->is_free = false;
+}
+__global__ void GetState_Kernel(Node** nodes, float* x0, float* x, float* v, float* nrm, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int k = 0; k < 3; k++) {
+    if (x0) x0[3 * i + k] = nodes[i]->x0[k];
+    if (x) x[3 * i + k] = nodes[i]->x[k];
+    if (v) v[3 * i + k] = nodes[i]->v[k];
+    if (nrm) nrm[3 * i + k] = nodes[i]->n[k];
+  }
+}
+__global__ void SetState_Kernel(Node** nodes, const float* x0, const float* x, const float* v, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int k = 0; k < 3; k++) {
+    if (x0) nodes[i]->x0[k] = x0[3 * i + k];
+    if (x) nodes[i]->x[k] = x[3 * i + k];
+    if (v) nodes[i]->v[k] = v[3 * i + k];
+  }
+}
+
+std::vector<uint> FaceEdgeIndices(const uint* tri, int F, const uint* edges, int E) {
+  std::map<std::pair<uint, uint>, uint> m;
+  for (int e = 0; e < E; e++) m[{std::min(edges[2 * e], edges[2 * e + 1]), std::max(edges[2 * e], edges[2 * e + 1])}] = e;
+  std::vector<uint> fe(3 * (size_t)F);
+  for (int f = 0; f < F; f++)
+    for (int j = 0; j < 3; j++) {
+      uint a = tri[3 * f + j], b = tri[3 * f + (j + 1) % 3];
+      fe[3 * f + j] = m[{std::min(a, b), std::max(a, b)}];
+    }
+  return fe;
+}
+
+struct RefSolver {
+  std::shared_ptr<MemoryPool> pool;
+  std::shared_ptr<PhysicsMesh> cloth, obstacle;
+  std::shared_ptr<BVH> obstacle_bvh;
+  std::shared_ptr<BasicConstraint::StretchSolver> stretch;
+  std::shared_ptr<BasicConstraint::BendSolver> bend;
+  std::shared_ptr<BindingConstraint> binding;
+  std::shared_ptr<PBDCollision::DCD::VFConstraint> vf_dcd;
+  std::shared_ptr<PBDCollision::CCD::RTConstraint> vf_ccd;
+  std::shared_ptr<PBDCollision::DCD::EEConstraint> ee_dcd;
+  std::shared_ptr<RTriangle> obstacle_rtri;
+  std::shared_ptr<SpatialHashGPU> hash;
+  int interleaved_hash = 3;
+  bool target_pending = false;
+  float* d_tmp = nullptr;
+  size_t tmp_floats = 0;
+};
+
+Timer* g_timer = nullptr;
+}  // namespace
+
+// Timer::CurrentTime() needs it (utils/Timer.hpp:64); no GLFW on this box
+extern "C" double glfwGetTime(void) {
+  static auto t0 = std::chrono::steady_clock::now();
+  return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+extern "C" {
+
+// ip: S, N, C, max_neighbors, interleaved_hash, self_collision, solve_bending, geodesic_lra, device, seed
+// fp: gx, gy, gz, damping, relaxation, lra_stretchiness, friction, bvh_tolerance, stretch_compliance,
+//     bend_compliance, particle_diameter, hash_cell_size
+void* ref_create(const int* ip, const float* fp, const float* cpos, const float* cinvm, int V, const uint* ctri, int F,
+                 const uint* cedge, int E, const uint* sidx, const float* srest, int ns, const uint* bidx,
+                 const float* btheta, int nb, const float* opos, int Vo, const uint* otri, int Fo, const uint* oedge,
+                 int Eo) {
+  cudaSetDevice(ip[8]);
+  if (!g_timer) g_timer = new Timer();
+  SimParams& sp = Global::sim_params;
+  sp = SimParams();
+  sp.num_substeps = ip[0]; sp.num_iterations = ip[1]; sp.num_collision_passes = ip[2];
+  sp.max_num_neighbors = ip[3];
+  sp.enable_self_collision = ip[5] != 0; sp.solve_bending = ip[6] != 0; sp.geodesic_LRA = ip[7] != 0;
+  sp.gravity = Vector3(fp[0], fp[1], fp[2]);
+  sp.damping = fp[3]; sp.relaxation_factor = fp[4]; sp.long_range_stretchiness = fp[5];
+  sp.sdf_friction = fp[6]; sp.bvh_tolerance = fp[7]; sp.particle_diameter = fp[10];
+  sp.solver_mode = 0;  // SWIFT
+  sp.num_particles = V; sp.num_edges = E; sp.num_faces = F; sp.num_overall_particles = V + Vo;
+  sp.num_obstacle_vertices = Vo; sp.num_obstacle_edges = Eo; sp.num_obstacle_faces = Fo;
+  sp.delta_time = Timer::FixedDeltaTime();
+
+  auto* s = new RefSolver();
+  s->interleaved_hash = ip[4] > 0 ? ip[4] : 1;
+  s->pool = std::make_shared<MemoryPool>();
+  s->cloth = std::make_shared<PhysicsMesh>(s->pool);
+  s->obstacle = std::make_shared<PhysicsMesh>(s->pool);
+  s->obstacle_bvh = std::make_shared<BVH>();
+  s->stretch = std::make_shared<BasicConstraint::StretchSolver>();
+  s->bend = std::make_shared<BasicConstraint::BendSolver>();
+  s->binding = std::make_shared<BindingConstraint>();
+
+  // --- AddCloth (impl/universal/ClothSolver.cpp:247-350) ---
+  std::vector<Vector3> cp(V);
+  for (int i = 0; i < V; i++) cp[i] = Vector3(cpos[3 * i], cpos[3 * i + 1], cpos[3 * i + 2]);
+  std::vector<uint> cidx(ctri, ctri + 3 * (size_t)F);
+  thrust::host_vector<uint> h_edges(cedge, cedge + 2 * (size_t)E);
+  std::vector<uint> fe = FaceEdgeIndices(ctri, F, cedge, E);
+  thrust::host_vector<uint> h_fe(fe.begin(), fe.end());
+  s->pool->SetupInitialPositions(cp);
+  s->cloth->RegisterNewMesh(cp, cidx, h_edges, h_fe, 0);
+  s->pool->SetupTmpPositions(V);
+  s->pool->SetupDeltas(V);
+  s->tmp_floats = 3 * (size_t)std::max(V, Vo) + 16;
+  cudaMalloc(&s->d_tmp, 4 * s->tmp_floats * sizeof(float));
+  cudaMemcpy(s->d_tmp, cinvm, V * sizeof(float), cudaMemcpyHostToDevice);
+  SetInvMass_Kernel<<<(V + 255) / 256, 256>>>(pointer(s->cloth->nodes), s->d_tmp, V);  // SetInvMass/SetFree per fixed index
+  cudaDeviceSynchronize();
+  std::vector<int> ev0(ns), ev1(ns);
+  std::vector<Scalar> len(srest, srest + ns);
+  for (int i = 0; i < ns; i++) { ev0[i] = sidx[2 * i]; ev1[i] = sidx[2 * i + 1]; }
+  s->stretch->AddCloth(ev0, ev1, len, fp[8]);
+  if (sp.solve_bending) {
+    std::vector<uint> bi(bidx, bidx + 4 * (size_t)nb);
+    std::vector<Scalar> ba(btheta, btheta + nb);
+    s->bend->AddCloth(bi, ba, fp[9]);
+  }
+  // --- AddObstacle (impl/universal/ClothSolver.cpp:189-245) ---
+  if (Vo) {
+    std::vector<Vector3> op(Vo);
+    for (int i = 0; i < Vo; i++) op[i] = Vector3(opos[3 * i], opos[3 * i + 1], opos[3 * i + 2]);
+    std::vector<uint> oidx(otri, otri + 3 * (size_t)Fo);
+    thrust::host_vector<uint> ho_edges(oedge, oedge + 2 * (size_t)Eo);
+    std::vector<uint> ofe = FaceEdgeIndices(otri, Fo, oedge, Eo);
+    thrust::host_vector<uint> ho_fe(ofe.begin(), ofe.end());
+    s->obstacle->SetPtrOffset(s->cloth->NumNodes(), s->cloth->NumEdges(), s->cloth->NumFaces());
+    s->obstacle->RegisterNewMesh(op, oidx, ho_edges, ho_fe, 0, false);
+    s->obstacle->PredictedToPositions();
+    s->obstacle->UpdateNodeGeometries();
+  }
+  // --- ClothSolverUniversal::Start (impl/universal/ClothSolver.cpp:46-93) ---
+  if (Vo) {
+    s->obstacle->UpdateNormals();
+    s->obstacle_bvh->UpdateData(pointer(s->obstacle->faces), 0.0f, false, s->obstacle->NumFaces());
+    s->obstacle_bvh->Construct();
+    // SetupRTriangle (pipeline/base/ClothSolverBase.cpp:487-500)
+    BuildVFAdjacency(s->obstacle, s->pool->obstacle_nb_vf, s->pool->obstacle_nb_vf_prefix);
+    s->obstacle_rtri = std::make_shared<RTriangle>();
+    s->obstacle_rtri->Init(s->obstacle->DeviceIndices(), s->pool->obstacle_nb_vf, s->pool->obstacle_nb_vf_prefix);
+  } else {
+    s->obstacle_rtri = std::make_shared<RTriangle>();
+  }
+  s->vf_dcd = std::make_shared<PBDCollision::DCD::VFConstraint>(V);
+  s->vf_ccd = std::make_shared<PBDCollision::CCD::RTConstraint>(V);
+  s->ee_dcd = std::make_shared<PBDCollision::DCD::EEConstraint>(E, s->obstacle_rtri);
+  s->hash = std::make_shared<SpatialHashGPU>(sp.particle_diameter, sp.num_particles, fp[11], sp.max_num_neighbors);
+  s->hash->SetInitialPositions(pointer(s->cloth->nodes), s->cloth->NumNodes());
+  // SetupInternalDynamics (pipeline/base/ClothSolverBase.cpp:453-468)
+  unsigned int seed = (unsigned int)ip[9];
+  s->stretch->SetupGraphColoring(pointer(s->cloth->edges), s->cloth->NumEdges(), seed);
+  if (sp.solve_bending) s->bend->SetupGraphColoring(seed);
+  cudaDeviceSynchronize();
+  return s;
+}
+
+void ref_set_obstacle_target(void* h, const float* xyz) {
+  auto* s = (RefSolver*)h;
+  int n = s->obstacle->NumNodes();
+  cudaMemcpy(s->d_tmp, xyz, 3 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice);
+  SetTarget_Kernel<<<(n + 255) / 256, 256>>>(pointer(s->obstacle->nodes), s->d_tmp, n);
+  s->target_pending = true;
+}
+
+// ClothSolverBase::SimulateSwift, pipeline/base/ClothSolverBase.cpp:171-261; returns Solver_Total in ms
+float ref_step_frame(void* h) {
+  auto* s = (RefSolver*)h;
+  SimParams& sp = Global::sim_params;
+  Timer::StartTimerGPU("Solver_Total");
+  Scalar substep_time = Timer::FixedDeltaTime() / sp.num_substeps;
+  SetSimulationParams(&sp);
+  bool b_obstacle_updated = false;
+  if (s->target_pending) {  // UpdateObstacleAnimationFrame, impl/smpl/ClothSolver.cpp:257-261
+    ScopedTimerGPU timer("Solver_UpdateBVH");
+    s->obstacle_bvh->UpdateData(pointer(s->obstacle->faces), 0.0f, false, s->obstacle->NumFaces());
+    s->obstacle_bvh->Construct();
+    b_obstacle_updated = true;
+    s->target_pending = false;
+  }
+  uint current_step = 0u;
+  uint frequency = (sp.num_substeps * sp.num_iterations) / sp.num_collision_passes;
+  uint cnt = 0;
+  for (int substep = 0; substep < sp.num_substeps; substep++) {
+    PredictPositions(pointer(s->cloth->nodes), substep_time, s->cloth->NumNodes());
+    if (sp.enable_self_collision) {
+      if (substep % s->interleaved_hash == 0) s->hash->Hash(pointer(s->cloth->nodes), s->cloth->NumNodes());
+    }
+    for (int iteration = 0; iteration < sp.num_iterations; iteration++) {
+      if (sp.enable_self_collision) {
+        CollideParticles(pointer(s->pool->deltas), pointer(s->pool->delta_counts), pointer(s->cloth->nodes),
+                         pointer(s->hash->neighbors));
+      }
+      current_step = substep * sp.num_iterations + iteration;
+      if (current_step % frequency == 0) {
+        if (b_obstacle_updated) {
+          s->obstacle->Interpolate(cnt, sp.num_collision_passes);
+          s->obstacle->UpdateMidstepNormals();
+          s->obstacle_bvh->RefitMidstep(pointer(s->obstacle->faces), sp.bvh_tolerance);
+        }
+        s->vf_dcd->Generate(pointer(s->cloth->nodes), s->obstacle_bvh);
+        s->vf_ccd->Generate(pointer(s->cloth->nodes), s->obstacle_bvh);
+        s->ee_dcd->Generate(pointer(s->cloth->nodes), pointer(s->cloth->edges), s->obstacle_bvh);
+        cnt++;
+      }
+      for (int c = 0; c < s->stretch->Coloring()->n_colors; c++)
+        s->stretch->Solve(pointer(s->cloth->nodes), pointer(s->pool->tmp_positions), c, substep_time, iteration);
+      if (sp.solve_bending)
+        for (int c = 0; c < s->bend->Coloring()->n_colors; c++)
+          s->bend->Solve(pointer(s->cloth->nodes), c, substep_time, iteration);
+      {  // SolveLongRangeAttachments, pipeline/base/ClothSolverBase.cpp:558-566
+        ScopedTimerGPU timer("Solver_SolveLRA");
+        if (sp.geodesic_LRA)
+          SolveGeodesicLRA(pointer(s->cloth->nodes), pointer(s->pool->geodesic_src_indices),
+                           pointer(s->pool->geodesic_tgt_indices), pointer(s->pool->geodesic_rest_length),
+                           s->pool->NumGeodesics(), sp.long_range_stretchiness);
+      }
+      s->vf_ccd->Solve(pointer(s->cloth->nodes), s->obstacle_bvh);
+      s->vf_dcd->Solve(pointer(s->cloth->nodes), s->obstacle_bvh);
+      s->ee_dcd->Solve(pointer(s->cloth->edges), pointer(s->pool->deltas), pointer(s->pool->delta_counts),
+                       s->obstacle_bvh);
+      ApplyDeltas(pointer(s->cloth->nodes), pointer(s->pool->deltas), pointer(s->pool->delta_counts));
+      s->binding->Solve(pointer(s->cloth->nodes), pointer(s->obstacle->nodes));
+    }
+    Finalize(pointer(s->cloth->nodes), substep_time);
+  }
+  s->obstacle->PredictedToPositions();
+  s->cloth->UpdateNormals();
+  s->obstacle->UpdateNormals();
+  Timer::EndTimerGPU("Solver_Total");
+  checkCudaErrors(cudaDeviceSynchronize());
+  Timer::NextFrame();  // GameInstance::MainLoop: timers of the previous frame are collected on the next Start
+  return (float)Timer::GetTimerGPU("Solver_Total");
+}
+
+// which: 0 cloth, 1 obstacle; any pointer may be null
+void ref_get_state(void* h, int which, float* x0, float* x, float* v, float* nrm) {
+  auto* s = (RefSolver*)h;
+  auto& mesh = which == 0 ? s->cloth : s->obstacle;
+  int n = mesh->NumNodes();
+  float* d = s->d_tmp;
+  size_t st = s->tmp_floats;
+  GetState_Kernel<<<(n + 255) / 256, 256>>>(pointer(mesh->nodes), d, d + st, d + 2 * st, d + 3 * st, n);
+  cudaDeviceSynchronize();
+  if (x0) cudaMemcpy(x0, d, 3 * (size_t)n * 4, cudaMemcpyDeviceToHost);
+  if (x) cudaMemcpy(x, d + st, 3 * (size_t)n * 4, cudaMemcpyDeviceToHost);
+  if (v) cudaMemcpy(v, d + 2 * st, 3 * (size_t)n * 4, cudaMemcpyDeviceToHost);
+  if (nrm) cudaMemcpy(nrm, d + 3 * st, 3 * (size_t)n * 4, cudaMemcpyDeviceToHost);
+}
+
+void ref_set_cloth_state(void* h, const float* x0, const float* x, const float* v) {
+  auto* s = (RefSolver*)h;
+  int n = s->cloth->NumNodes();
+  float* d = s->d_tmp;
+  size_t st = s->tmp_floats;
+  if (x0) cudaMemcpy(d, x0, 3 * (size_t)n * 4, cudaMemcpyHostToDevice);
+  if (x) cudaMemcpy(d + st, x, 3 * (size_t)n * 4, cudaMemcpyHostToDevice);
+  if (v) cudaMemcpy(d + 2 * st, v, 3 * (size_t)n * 4, cudaMemcpyHostToDevice);
+  SetState_Kernel<<<(n + 255) / 256, 256>>>(pointer(s->cloth->nodes), x0 ? d : nullptr, x ? d + st : nullptr,
+                                            v ? d + 2 * st : nullptr, n);
+  cudaDeviceSynchronize();
+}
+
+int ref_num_colors(void* h, int kind) {
+  auto* s = (RefSolver*)h;
+  return kind == 0 ? s->stretch->Coloring()->n_colors : s->bend->Coloring()->n_colors;
+}
+// GraphColoring::colors (graph_coloring/Base.cuh:36), for injection into the product (F9)
+void ref_get_colors(void* h, int kind, uint* out, int n) {
+  auto* s = (RefSolver*)h;
+  if (kind == 0) thrust::copy_n(s->stretch->Coloring()->colors.begin(), n, out);
+  else thrust::copy_n(s->bend->Coloring()->colors.begin(), n, out);
+}
+
+// the reference's own host accessors, BVH.cu:579-602
+void ref_get_bvh(void* h, uint* morton_unused, uint* nodes, float* aabbs, int* esc_int, int* esc_ext, float* pred9) {
+  auto* s = (RefSolver*)h;
+  (void)morton_unused;
+  auto hn = s->obstacle_bvh->NodesHost();
+  auto hb = s->obstacle_bvh->AABBsHost();
+  auto hi = s->obstacle_bvh->InternalEscapeIndexTableHost();
+  auto he = s->obstacle_bvh->ExternalEscapeIndexTableHost();
+  auto ho = s->obstacle_bvh->ObjectsHost();
+  const size_t F = ho.size();
+  for (size_t i = 0; i < hn.size(); i++) {
+    nodes[4 * i] = hn[i].parent_idx; nodes[4 * i + 1] = hn[i].left_idx;
+    nodes[4 * i + 2] = hn[i].right_idx; nodes[4 * i + 3] = hn[i].object_idx;
+    for (int k = 0; k < 3; k++) { aabbs[6 * i + k] = hb[i].lower[k]; aabbs[6 * i + 3 + k] = hb[i].upper[k]; }
+  }
+  for (size_t i = 0; i + 1 < F; i++) esc_int[i] = hi[i];
+  for (size_t i = 0; i < F; i++) {
+    esc_ext[i] = he[i];
+    if (pred9)
+      for (int k = 0; k < 3; k++) {
+        pred9[9 * i + k] = ho[i].pred1[k]; pred9[9 * i + 3 + k] = ho[i].pred2[k]; pred9[9 * i + 6 + k] = ho[i].pred3[k];
+      }
+  }
+}
+
+// contacts as the reference stores them (pbd_collision/Contact.cuh)
+void ref_get_contacts(void* h, int* vf_idx, float* vf_q, int* rt_idx, float* rt_q, float* ee12) {
+  auto* s = (RefSolver*)h;
+  thrust::host_vector<VFContact> a = s->vf_dcd->contacts;
+  thrust::host_vector<RTContact> b = s->vf_ccd->contacts;
+  thrust::host_vector<EEContact> c = s->ee_dcd->contacts;
+  for (size_t i = 0; i < a.size(); i++) {
+    vf_idx[i] = a[i].index; rt_idx[i] = b[i].index;
+    for (int k = 0; k < 3; k++) { vf_q[3 * i + k] = a[i].qs[k]; rt_q[3 * i + k] = b[i].qc[k]; }
+  }
+  for (size_t i = 0; i < c.size(); i++) {
+    float* o = ee12 + 12 * i;
+    o[0] = c[i].dist;
+    for (int k = 0; k < 3; k++) { o[1 + k] = c[i].p2[k]; o[4 + k] = c[i].q2[k]; o[9 + k] = c[i].fn[k]; }
+    o[7] = c[i].s; o[8] = c[i].t;
+  }
+}
+
+void ref_generate_contacts(void* h) {
+  auto* s = (RefSolver*)h;
+  SetSimulationParams(&Global::sim_params);
+  s->vf_dcd->Generate(pointer(s->cloth->nodes), s->obstacle_bvh);
+  s->vf_ccd->Generate(pointer(s->cloth->nodes), s->obstacle_bvh);
+  s->ee_dcd->Generate(pointer(s->cloth->nodes), pointer(s->cloth->edges), s->obstacle_bvh);
+  cudaDeviceSynchronize();
+}
+
+void ref_get_rtri(void* h, uint* out, int n) {
+  auto* s = (RefSolver*)h;
+  thrust::copy_n(s->obstacle_rtri->r_tris.begin(), n, out);
+}
+
+void ref_destroy(void* h) {
+  auto* s = (RefSolver*)h;
+  cudaFree(s->d_tmp);
+  s->cloth->Destroy();
+  s->obstacle->Destroy();
+  delete s;
+}
+}  // extern "C"
