@@ -118,7 +118,7 @@ void* ref_create(const int* ip, const float* fp, const float* cpos, const float*
   sp.gravity = Vector3(fp[0], fp[1], fp[2]);
   sp.damping = fp[3]; sp.relaxation_factor = fp[4]; sp.long_range_stretchiness = fp[5];
   sp.sdf_friction = fp[6]; sp.bvh_tolerance = fp[7]; sp.particle_diameter = fp[10];
-  sp.solver_mode = 0;  // SWIFT
+  sp.solver_mode = SOLVER_MODE::SWIFT;
   sp.num_particles = V; sp.num_edges = E; sp.num_faces = F; sp.num_overall_particles = V + Vo;
   sp.num_obstacle_vertices = Vo; sp.num_obstacle_edges = Eo; sp.num_obstacle_faces = Fo;
   sp.delta_time = Timer::FixedDeltaTime();

@@ -1,0 +1,166 @@
+"""ctypes wrapper of oracle/_ref/libxrt_ref.so — the reference's own CUDA
+physics (compiled from /root/reference by oracle/ref_harness/Makefile) behind a
+GL-free harness.  TEST INFRASTRUCTURE ONLY: used by tests/ as the oracle on the
+GPU box and by bench.py's reference arm.  Needs a GPU; nothing here reads
+/root/reference at run time."""
+import ctypes as C
+import os
+import time
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(_HERE, "..", "_ref", "libxrt_ref.so")
+_lib = None
+
+
+def available():
+    if not os.path.exists(SO):
+        return False
+    try:
+        import torch
+        return torch.cuda.is_available()
+    except Exception:
+        return False
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = C.CDLL(SO)
+        vp, f32p, u32p, i32p = C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_uint32), C.POINTER(C.c_int32)
+        L.ref_create.argtypes = [i32p, f32p, f32p, f32p, C.c_int, u32p, C.c_int, u32p, C.c_int, u32p, f32p, C.c_int,
+                                 u32p, f32p, C.c_int, f32p, C.c_int, u32p, C.c_int, u32p, C.c_int]
+        L.ref_create.restype = vp
+        L.ref_set_obstacle_target.argtypes = [vp, f32p]; L.ref_set_obstacle_target.restype = None
+        L.ref_step_frame.argtypes = [vp]; L.ref_step_frame.restype = C.c_float
+        L.ref_get_state.argtypes = [vp, C.c_int, f32p, f32p, f32p, f32p]; L.ref_get_state.restype = None
+        L.ref_set_cloth_state.argtypes = [vp, f32p, f32p, f32p]; L.ref_set_cloth_state.restype = None
+        L.ref_num_colors.argtypes = [vp, C.c_int]; L.ref_num_colors.restype = C.c_int
+        L.ref_get_colors.argtypes = [vp, C.c_int, u32p, C.c_int]; L.ref_get_colors.restype = None
+        L.ref_get_bvh.argtypes = [vp, u32p, u32p, f32p, i32p, i32p, f32p]; L.ref_get_bvh.restype = None
+        L.ref_get_contacts.argtypes = [vp, i32p, f32p, i32p, f32p, f32p]; L.ref_get_contacts.restype = None
+        L.ref_generate_contacts.argtypes = [vp]; L.ref_generate_contacts.restype = None
+        L.ref_get_rtri.argtypes = [vp, u32p, C.c_int]; L.ref_get_rtri.restype = None
+        L.ref_destroy.argtypes = [vp]; L.ref_destroy.restype = None
+        _lib = L
+    return _lib
+
+
+def _f(a):
+    return np.ascontiguousarray(a, np.float32)
+
+
+def _u(a):
+    return np.ascontiguousarray(a, np.uint32)
+
+
+def _pf(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float)) if a is not None else None
+
+
+def _pu(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint32)) if a is not None else None
+
+
+def _pi(a):
+    return a.ctypes.data_as(C.POINTER(C.c_int32)) if a is not None else None
+
+
+class RefSolver:
+    """The reference's Swift solver on a xrtailor_b200.scene.Scene with xrt_params p."""
+
+    def __init__(self, sc, p, seed=20261104, device=0):
+        L = lib()
+        ip = np.array([p.num_substeps, p.num_iterations, p.num_collision_passes, p.max_num_neighbors,
+                       p.inter_leaved_hash, p.enable_self_collision, p.solve_bending, p.geodesic_lra, device,
+                       seed & 0x7FFFFFFF], np.int32)
+        fp = np.array([p.gravity[0], p.gravity[1], p.gravity[2], p.damping, p.relaxation_factor,
+                       p.long_range_stretchiness, p.sdf_friction, p.bvh_tolerance, p.stretch_compliance,
+                       p.bend_compliance, p.particle_diameter, p.hash_cell_size], np.float32)
+        self.V, self.E, self.F = len(sc.cloth_pos), len(sc.cloth_edges), len(sc.cloth_tri)
+        self.Vo, self.Fo = len(sc.obs_pos), len(sc.obs_tri)
+        self.ns, self.nb = len(sc.stretch_rest), len(sc.bend_theta)
+        keep = [_f(sc.cloth_pos), _f(sc.inv_mass), _u(sc.cloth_tri), _u(sc.cloth_edges), _u(sc.stretch_idx),
+                _f(sc.stretch_rest), _u(sc.bend_idx), _f(sc.bend_theta), _f(sc.obs_pos), _u(sc.obs_tri),
+                _u(sc.obs_edges)]
+        self.h = L.ref_create(_pi(ip), _pf(fp), _pf(keep[0]), _pf(keep[1]), self.V, _pu(keep[2]), self.F,
+                              _pu(keep[3]), self.E, _pu(keep[4]), _pf(keep[5]), self.ns, _pu(keep[6]), _pf(keep[7]),
+                              self.nb, _pf(keep[8]), self.Vo, _pu(keep[9]), self.Fo, _pu(keep[10]),
+                              len(sc.obs_edges))
+
+    def colors(self):
+        cs, cb = np.zeros(self.ns, np.uint32), np.zeros(self.nb, np.uint32)
+        lib().ref_get_colors(self.h, 0, _pu(cs), self.ns)
+        lib().ref_get_colors(self.h, 1, _pu(cb), self.nb)
+        return cs, cb, lib().ref_num_colors(self.h, 0), lib().ref_num_colors(self.h, 1)
+
+    def set_obstacle_target(self, xyz):
+        lib().ref_set_obstacle_target(self.h, _pf(_f(xyz)))
+
+    def step_frame(self):
+        return lib().ref_step_frame(self.h)
+
+    def state(self, which=0):
+        n = self.V if which == 0 else self.Vo
+        out = [np.zeros((n, 3), np.float32) for _ in range(4)]
+        lib().ref_get_state(self.h, which, *[_pf(a) for a in out])
+        return dict(x0=out[0], x=out[1], v=out[2], n=out[3])
+
+    def set_cloth_state(self, x0=None, x=None, v=None):
+        a = [None if t is None else _f(t) for t in (x0, x, v)]
+        lib().ref_set_cloth_state(self.h, *[_pf(t) for t in a])
+
+    def bvh(self):
+        F = self.Fo
+        nodes, aabb = np.zeros((2 * F - 1, 4), np.uint32), np.zeros((2 * F - 1, 6), np.float32)
+        ei, ee, pred = np.zeros(F - 1, np.int32), np.zeros(F, np.int32), np.zeros((F, 9), np.float32)
+        lib().ref_get_bvh(self.h, None, _pu(nodes), _pf(aabb), _pi(ei), _pi(ee), _pf(pred))
+        return dict(nodes=nodes, aabb=aabb, esc_int=ei, esc_ext=ee, pred=pred, object=nodes[F - 1:, 3].copy())
+
+    def generate_contacts(self):
+        lib().ref_generate_contacts(self.h)
+
+    def contacts(self):
+        vi, ri = np.zeros(self.V, np.int32), np.zeros(self.V, np.int32)
+        vq, rq = np.zeros((self.V, 3), np.float32), np.zeros((self.V, 3), np.float32)
+        ee = np.zeros((self.E, 12), np.float32)
+        lib().ref_get_contacts(self.h, _pi(vi), _pf(vq), _pi(ri), _pf(rq), _pf(ee))
+        return dict(vf_idx=vi, vf_q=vq, rt_idx=ri, rt_q=rq, ee=ee)
+
+    def rtri(self):
+        out = np.zeros(self.Fo, np.uint32)
+        lib().ref_get_rtri(self.h, _pu(out), self.Fo)
+        return out
+
+    def close(self):
+        if self.h:
+            lib().ref_destroy(self.h)
+            self.h = None
+
+
+def time_frames(sc, steps, warmup, device=0, params=None):
+    """Reference arm of bench.py: the reference's own Solver_Total (CUDA events
+    around SimulateSwift) over `steps` frames after `warmup`, same workload."""
+    import xrtailor_b200 as X
+    from xrtailor_b200 import scene
+    p = params or X.default_params()
+    if p.particle_diameter <= 0:
+        p.particle_diameter = sc.particle_diameter()
+    r = RefSolver(sc, p, device=device)
+    ms = []
+    wall0 = None
+    for f in range(warmup + steps):
+        if f == warmup:
+            wall0 = time.perf_counter()
+        r.set_obstacle_target(scene.sphere_motion(sc.obs_pos, f + 1))
+        ms.append(r.step_frame())
+    wall = time.perf_counter() - wall0
+    ms = np.array(ms[warmup:])
+    cs, cb, nsc, nbc = r.colors()
+    r.close()
+    return {"frames_per_s": steps / (ms.sum() * 1e-3), "ms_per_frame": float(ms.mean()),
+            "ms_median": float(np.median(ms)), "wall_frames_per_s": steps / wall, "cores": 1,
+            "colors": [int(nsc), int(nbc)],
+            "sample": f"{steps} frames, reference CUDA physics (sm_100a, --use_fast_math) through the GL-free "
+                      f"harness, Solver_Total event time; {nsc}/{nbc} stretch/bend colours"}

@@ -1,0 +1,106 @@
+"""Parity against the REFERENCE'S OWN CUDA (oracle/_ref/libxrt_ref.so, built
+from /root/reference by oracle/ref_harness) on identical inputs, with the
+reference's constraint colours injected (its colouring seed is random, F9).
+Also pins the CPU oracle against the reference."""
+import numpy as np
+import pytest
+
+import xrtailor_b200 as X
+from oracle import oracle as O
+from oracle.ref_harness import ref as R
+from xrtailor_b200 import scene
+from tests.common import rel_rms, rms
+
+pytestmark = [pytest.mark.gpu, pytest.mark.skipif(not R.available(), reason="oracle/_ref/libxrt_ref.so not built")]
+
+
+@pytest.fixture(scope="module")
+def trio():
+    """(scene, reference solver, params, colours) — one reference solver per module (it owns process globals)."""
+    sc = scene.drop_scene(64, sphere=(24, 48))
+    p = X.default_params()
+    p.particle_diameter = sc.particle_diameter()
+    r = R.RefSolver(sc, p)
+    cs, cb, nsc, nbc = r.colors()
+    yield sc, r, p, (cs, cb)
+    r.close()
+
+
+def test_reference_colouring_is_usable(trio):
+    sc, r, p, (cs, cb) = trio
+    assert len(cs) == len(sc.stretch_rest) and len(cb) == len(sc.bend_theta)
+    assert cs.max() < 64 and cb.max() < 64
+
+
+def test_bvh_topology_boxes_escape_tables_bit_exact(trio):
+    sc, r, p, colors = trio
+    s = scene.make_solver(sc, colors=colors, morton_fast_div=1)   # div.approx like the reference build
+    g, ref = s.bvh(), r.bvh()
+    np.testing.assert_array_equal(g["object"], ref["object"])      # same sort order => same Morton ranks
+    np.testing.assert_array_equal(g["nodes"], ref["nodes"])
+    np.testing.assert_array_equal(g["esc_int"], ref["esc_int"])
+    np.testing.assert_array_equal(g["esc_ext"], ref["esc_ext"])
+    np.testing.assert_array_equal(g["aabb"], ref["aabb"])
+    np.testing.assert_array_equal(s.debug("RTRI", np.uint32), r.rtri())
+    # and the CPU oracle agrees with the reference too (pins the restatement)
+    o = O.Bvh(sc.obs_pos, sc.obs_tri).arrays()
+    np.testing.assert_array_equal(o["nodes"], ref["nodes"])
+    np.testing.assert_array_equal(o["aabb"], ref["aabb"])
+    np.testing.assert_array_equal(o["esc_int"], ref["esc_int"])
+    np.testing.assert_array_equal(o["esc_ext"], ref["esc_ext"])
+    s.close()
+
+
+def test_positions_after_frames_and_contacts(trio):
+    sc, r, p, colors = trio
+    s = scene.make_solver(sc, colors=colors, morton_fast_div=1)
+    o = O.Scene(sc, s.params, colors)
+    errs = []
+    for f in range(10):
+        tgt = scene.sphere_motion(sc.obs_pos, f + 1)
+        for obj in (s, ):
+            obj.UpdateObstacleAnimationFrame(tgt)
+        r.set_obstacle_target(tgt)
+        o.set_obstacle_target(tgt)
+        s.SimulateSwift()
+        r.step_frame()
+        o.step_frame()
+        errs.append(rms(s.GetPositions(0), r.state(0)["x0"]))
+    ref = r.state(0)
+    g = s.GetPositions(0)
+    print("rms vs reference per frame:", ["%.2e" % e for e in errs])
+    assert rel_rms(g, ref["x0"]) <= 1e-3
+    assert errs[0] <= 1e-5 * np.sqrt((ref["x0"].astype(np.float64) ** 2).sum(1).mean()) * 10  # first frame (4 substeps)
+    assert errs[-1] <= 1e-3                                                                     # 10 frames: 1e-3 m RMS
+    assert rms(o.positions(), ref["x0"]) <= 1e-3                                                # oracle pinned too
+    np.testing.assert_allclose(s.GetPositions(1), r.state(1)["x0"], atol=1e-6)
+    # BVH after a moving-obstacle frame (rebuild + refits): topology equal, boxes to rounding of pred
+    gb, rb = s.bvh(), r.bvh()
+    np.testing.assert_array_equal(gb["nodes"], rb["nodes"])
+    np.testing.assert_allclose(gb["aabb"], rb["aabb"], atol=5e-6)
+    # contact statistics on the final state
+    rc = r.contacts()
+    vf, rt, ee = s.contacts()
+    n_ref, n_got = (rc["vf_idx"] >= 0).sum(), (vf["index"] >= 0).sum()
+    assert abs(int(n_ref) - int(n_got)) <= max(3, 0.02 * n_ref)
+    s.close()
+
+
+def test_one_substep_from_identical_state(trio):
+    """Load the reference's current state into the product, advance both by one frame of one substep."""
+    sc, r, p, colors = trio
+    st = r.state(0)
+    ob = r.state(1)["x0"]
+    sc2 = scene.Scene(st["x0"], sc.cloth_tri, ob, sc.obs_tri)
+    # same constraints as the original garment (rest lengths come from the rest pose, not the current state)
+    sc2.stretch_idx, sc2.stretch_rest, sc2.bend_idx, sc2.bend_theta = sc.stretch_idx, sc.stretch_rest, sc.bend_idx, sc.bend_theta
+    s = scene.make_solver(sc2, colors=colors, morton_fast_div=1, particle_diameter=p.particle_diameter)
+    s.SetClothState(st["x0"], st["v"])
+    # one full frame on both (the reference cannot run a single substep without changing its globals)
+    s.SimulateSwift()
+    r.step_frame()
+    a, b = s.GetPositions(0), r.state(0)["x0"]
+    disp = np.sqrt(((b - st["x0"]) ** 2).sum(1).mean())
+    print("one frame from identical state: rel rms %.3e, displacement rms %.3e" % (rel_rms(a, b), disp))
+    assert rel_rms(a, b) <= 1e-5 * 4   # 4 substeps per frame
+    s.close()
