@@ -86,21 +86,29 @@ def test_positions_after_frames_and_contacts(trio):
     s.close()
 
 
-def test_one_substep_from_identical_state(trio):
-    """Load the reference's current state into the product, advance both by one frame of one substep."""
-    sc, r, p, colors = trio
-    st = r.state(0)
-    ob = r.state(1)["x0"]
-    sc2 = scene.Scene(st["x0"], sc.cloth_tri, ob, sc.obs_tri)
-    # same constraints as the original garment (rest lengths come from the rest pose, not the current state)
-    sc2.stretch_idx, sc2.stretch_rest, sc2.bend_idx, sc2.bend_theta = sc.stretch_idx, sc.stretch_rest, sc.bend_idx, sc.bend_theta
-    s = scene.make_solver(sc2, colors=colors, morton_fast_div=1, particle_diameter=p.particle_diameter)
+def test_one_frame_from_identical_state(trio):
+    """Static obstacle: settle the reference for a few frames, load its state
+    (x0, v) into the product, advance both by one frame, compare."""
+    sc, _, p, _ = trio
+    r2 = R.RefSolver(sc, p, seed=7)
+    cs, cb, _, _ = r2.colors()
+    for _ in range(8):
+        r2.step_frame()
+    st = r2.state(0)
+    s = scene.make_solver(sc, colors=(cs, cb), morton_fast_div=1)
     s.SetClothState(st["x0"], st["v"])
-    # one full frame on both (the reference cannot run a single substep without changing its globals)
     s.SimulateSwift()
-    r.step_frame()
-    a, b = s.GetPositions(0), r.state(0)["x0"]
+    r2.step_frame()
+    a, b = s.GetPositions(0), r2.state(0)["x0"]
     disp = np.sqrt(((b - st["x0"]) ** 2).sum(1).mean())
-    print("one frame from identical state: rel rms %.3e, displacement rms %.3e" % (rel_rms(a, b), disp))
-    assert rel_rms(a, b) <= 1e-5 * 4   # 4 substeps per frame
+    err = rms(a, b)
+    print("one frame from identical state: rms %.3e m, rel rms %.3e, displacement rms %.3e" % (err, rel_rms(a, b), disp))
+    assert rel_rms(a, b) <= 4e-5          # 4 substeps, 1e-5 relative RMS each
+    assert err <= 1e-2 * disp             # and small against what the frame actually moved
+    # same vertices in contact, same faces (ties between equally near faces excepted)
+    rc = r2.contacts()
+    vf, rt, ee = s.contacts()
+    same = (vf["index"] == rc["vf_idx"]).mean()
+    assert same > 0.98, same
     s.close()
+    r2.close()
