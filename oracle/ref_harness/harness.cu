@@ -188,6 +188,9 @@ void* ref_create(const int* ip, const float* fp, const float* cpos, const float*
   s->ee_dcd = std::make_shared<PBDCollision::DCD::EEConstraint>(E, s->obstacle_rtri);
   s->hash = std::make_shared<SpatialHashGPU>(sp.particle_diameter, sp.num_particles, fp[11], sp.max_num_neighbors);
   s->hash->SetInitialPositions(pointer(s->cloth->nodes), s->cloth->NumNodes());
+  // SetupBinding (pipeline/base/ClothSolverBase.cpp:448-451, called by the SMPL pipeline's Start): sets
+  // n_bindings = 0; without it BindingConstraint::n_bindings is uninitialised (BindingConstraint.cu:4)
+  s->binding->Generate(pointer(s->cloth->nodes), pointer(s->obstacle->nodes), pointer(s->pool->skin_params));
   // SetupInternalDynamics (pipeline/base/ClothSolverBase.cpp:453-468)
   unsigned int seed = (unsigned int)ip[9];
   s->stretch->SetupGraphColoring(pointer(s->cloth->edges), s->cloth->NumEdges(), seed);
