@@ -316,6 +316,20 @@ void ref_get_colors(void* h, int kind, uint* out, int n) {
   else thrust::copy_n(s->bend->Coloring()->colors.begin(), n, out);
 }
 
+// overwrite GraphColoring::colors / n_colors (public members, graph_coloring/Base.cuh:36) so that both
+// implementations can be driven with the same PROPER colouring (the reference's own randomized colouring
+// leaves vertex conflicts inside colours, which makes its result depend on atomic timing)
+void ref_set_colors(void* h, int kind, const uint* colors, int n, int n_colors) {
+  auto* s = (RefSolver*)h;
+  if (kind == 0) {
+    thrust::copy_n(colors, n, s->stretch->Coloring()->colors.begin());
+    s->stretch->Coloring()->n_colors = n_colors;
+  } else {
+    thrust::copy_n(colors, n, s->bend->Coloring()->colors.begin());
+    s->bend->Coloring()->n_colors = n_colors;
+  }
+}
+
 // the reference's own host accessors, BVH.cu:579-602
 void ref_get_bvh(void* h, uint* morton_unused, uint* nodes, float* aabbs, int* esc_int, int* esc_ext, float* pred9) {
   auto* s = (RefSolver*)h;

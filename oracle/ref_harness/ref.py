@@ -38,6 +38,7 @@ def lib():
         L.ref_set_cloth_state.argtypes = [vp, f32p, f32p, f32p]; L.ref_set_cloth_state.restype = None
         L.ref_num_colors.argtypes = [vp, C.c_int]; L.ref_num_colors.restype = C.c_int
         L.ref_get_colors.argtypes = [vp, C.c_int, u32p, C.c_int]; L.ref_get_colors.restype = None
+        L.ref_set_colors.argtypes = [vp, C.c_int, u32p, C.c_int, C.c_int]; L.ref_set_colors.restype = None
         L.ref_get_bvh.argtypes = [vp, u32p, u32p, f32p, i32p, i32p, f32p]; L.ref_get_bvh.restype = None
         L.ref_get_contacts.argtypes = [vp, i32p, f32p, i32p, f32p, f32p]; L.ref_get_contacts.restype = None
         L.ref_generate_contacts.argtypes = [vp]; L.ref_generate_contacts.restype = None
@@ -94,6 +95,11 @@ class RefSolver:
         lib().ref_get_colors(self.h, 0, _pu(cs), self.ns)
         lib().ref_get_colors(self.h, 1, _pu(cb), self.nb)
         return cs, cb, lib().ref_num_colors(self.h, 0), lib().ref_num_colors(self.h, 1)
+
+    def set_colors(self, cs, cb):
+        cs, cb = _u(cs), _u(cb)
+        lib().ref_set_colors(self.h, 0, _pu(cs), len(cs), int(cs.max()) + 1)
+        lib().ref_set_colors(self.h, 1, _pu(cb), len(cb), int(cb.max()) + 1)
 
     def set_obstacle_target(self, xyz):
         lib().ref_set_obstacle_target(self.h, _pf(_f(xyz)))

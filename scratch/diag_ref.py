@@ -27,5 +27,25 @@ out.append("rms %.3e rel %.3e disp %.3e max %.3e n>1e-5: %d n>1e-6: %d" % (rms(a
 out.append("vf contacts ref %d ours %d same idx %.4f; rt ref %d ours %d same %.4f; ee live ref %d ours %d" % ((rc["vf_idx"] >= 0).sum(), (vf["index"] >= 0).sum(), (vf["index"] == rc["vf_idx"]).mean(), (rc["rt_idx"] >= 0).sum(), (rt["index"] >= 0).sum(), (rt["index"] == rc["rt_idx"]).mean(), (rc["ee"][:, 0] < 1e6).sum(), (ee[:, 0] < 1e6).sum()))
 bad = np.argsort(-d)[:8]
 out.append("worst verts %s err %s vf ref %s ours %s" % (bad.tolist(), ["%.1e" % e for e in d[bad]], rc["vf_idx"][bad].tolist(), vf["index"][bad].tolist()))
-# is the reference deterministic? run a second reference from the same state
+# (1) the reference against itself from the same state: its own run-to-run spread
+r3 = R.RefSolver(sc, p, seed=7)
+c3 = r3.colors()
+r3.set_cloth_state(st["x0"], st["x0"], st["v"])
+r3.step_frame()
+b3 = r3.state(0)["x0"]
+out.append("REF vs REF (same colours: %s): rms %.3e rel %.3e max %.3e" % (bool((c3[0] == cs).all() and (c3[1] == cb).all()), rms(b3, b), rel_rms(b3, b), np.sqrt(((b3 - b) ** 2).sum(1)).max()))
+# (2) both with OUR proper colouring
+gs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos)); gb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+r3.set_colors(gs, gb)
+r3.set_cloth_state(st["x0"], st["x0"], st["v"])
+r3.step_frame()
+s2 = scene.make_solver(sc, colors=(gs, gb), morton_fast_div=1, num_substeps=S, enable_self_collision=selfc)
+s2.SetClothState(st["x0"], st["v"]); s2.SimulateSwift()
+a2, b2 = s2.GetPositions(0), r3.state(0)["x0"]
+d2 = np.sqrt(((a2 - b2) ** 2).sum(1))
+out.append("PROPER colouring: rms %.3e rel %.3e max %.3e n>1e-5: %d n>1e-6: %d" % (rms(a2, b2), rel_rms(a2, b2), d2.max(), (d2 > 1e-5).sum(), (d2 > 1e-6).sum()))
+bad = np.argsort(-d2)[:6]
+rc = r3.contacts(); vf, rt, ee = s2.contacts()
+out.append("PROPER worst %s err %s vf ref %s ours %s" % (bad.tolist(), ["%.1e" % e for e in d2[bad]], rc["vf_idx"][bad].tolist(), vf["index"][bad].tolist()))
+# run a second reference from the same state
 print("\nDIAG " + "\nDIAG ".join(out), flush=True)
