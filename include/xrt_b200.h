@@ -57,9 +57,13 @@ typedef struct xrt_params {
    * for bit); 1: div.approx like the reference's --use_fast_math build
    * (CMakeLists.txt:217), for bit parity against the reference's CUDA. */
   int32_t morton_fast_div;
-  /* 0: one launch per colour (CUDA-graph replayed); 1: fused cooperative
-   * kernels with grid barriers between colours. */
-  int32_t fused_iterations;
+  /* Launch shape of the substep.  0: one launch per stage and colour,
+   * replayed as a CUDA graph.  C >= 1: one persistent kernel per substep on a
+   * thread-block cluster of C CTAs (1, 2, 4, 8 or 16; one CTA per SM) with
+   * hardware cluster barriers between the phases; 148 / C garments run
+   * concurrently on a B200.  -1: the largest cluster the device schedules.
+   * Both shapes call the same device bodies and give identical results. */
+  int32_t persist_cluster;
   int32_t device;                /* CUDA device ordinal                */
 } xrt_params;
 
@@ -138,11 +142,23 @@ int xrt_sync(xrt_solver* s);
  * between frames. */
 int xrt_batch_run(xrt_solver** handles, int n, int frames, float* ms);
 
+/* Persistent launch shape on the current device: *max_cluster = largest
+ * cluster (CTAs) the device co-schedules, *resident = how many clusters of
+ * `cluster` CTAs fit at once (= garments that step concurrently).  Either
+ * out pointer may be NULL.  Fails with XRT_ERR_CUDA without a device. */
+int xrt_persist_info(int cluster, int* max_cluster, int* resident);
+
 /* Launch the named step kernel `reps` times on the handle's stream between
  * two CUDA events; *avg_ms = mean duration of ONE launch, *bytes = its
  * algorithmic bytes.  which: 0 bend colour pass, 1 stretch colour
- * pass, 2 collide particles, 3 contact generation (vertex), 4 predict. */
+ * pass, 2 collide particles, 3 contact generation (vertex), 4 predict, 5 the persistent substep kernel
+ * (advances the state by one substep per launch). */
 int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg_ms, double* bytes);
+/* The persistent substep kernel as it runs in batch mode: every handle
+ * launches it `reps` times on its own stream between one start and one end
+ * event.  *avg_ms = duration of one round (n launches running side by side on
+ * disjoint clusters), *bytes = algorithmic bytes of those n launches. */
+int xrt_batch_profile_substep(xrt_solver** handles, int n, int reps, float* avg_ms, double* bytes);
 
 /* SaveCache (impl/universal/ClothSolver.cpp:107-144): which 0 = cloth,
  * 1 = obstacle.  xyz / nrm: 3*n_verts floats each, either may be NULL. */
@@ -186,7 +202,12 @@ enum xrt_debug_what {
   XRT_DBG_PARTICLE_HASH = 17,/* uint32[V] sorted hash; then uint32[V] index    */
   XRT_DBG_VF_CAND_COUNT = 18,/* uint32[V] #leaf hits of the VF point query     */
   XRT_DBG_RT_CAND_COUNT = 19,/* uint32[V] #leaf hits of the vertex-ray query   */
-  XRT_DBG_EE_CAND_COUNT = 20 /* uint32[E] #leaf hits of the edge query         */
+  XRT_DBG_EE_CAND_COUNT = 20,/* uint32[E] #leaf hits of the edge query         */
+  /* uint64[16] ns per phase kind of the persistent kernel since setup (empty
+   * unless XRT_PERSIST_PROF=1 was set at xrt_finalize_setup): 0 predict,
+   * 1 collide, 2 apply, 3 interpolate+normals, 4 refit, 5 generate, 6 stretch,
+   * 7 bend, 8 LRA, 9 vertex solve, 10 edge solve, 11 apply, 12 finalize */
+  XRT_DBG_PERSIST_PROF = 21
 };
 int xrt_debug_get(xrt_solver* s, int what, void* dst, size_t* bytes);
 

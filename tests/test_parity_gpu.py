@@ -169,7 +169,8 @@ def test_ten_frames_positions_moving_obstacle(small):
 
 def test_graph_replay_equals_eager_building_blocks(small):
     """xrt_step_frame (CUDA graph) == the same frame driven call by call."""
-    s1, _ = pair(small, num_substeps=1, num_iterations=4, num_collision_passes=1, enable_self_collision=0)
+    s1, _ = pair(small, num_substeps=1, num_iterations=4, num_collision_passes=1, enable_self_collision=0,
+                 persist_cluster=0)
     s2, _ = pair(small, num_substeps=1, num_iterations=4, num_collision_passes=1, enable_self_collision=0)
     s1.SimulateSwift()
     s2.PredictPositions()
@@ -218,4 +219,63 @@ def test_error_codes():
     with pytest.raises(X.XrtError) as e:
         s.AddCloth(sc.cloth_pos, np.array([[0, 1, 999999]], np.uint32), sc.cloth_edges)
     assert e.value.code == 8100
+    s.close()
+
+
+# ---- persistent cluster kernel (xrt_persist.cu) vs the per-stage launch shape ----
+
+def _run_frames(sc, frames, **kw):
+    s, _ = pair(sc, **kw)
+    for f in range(frames):
+        s.UpdateObstacleAnimationFrame(scene.sphere_motion(sc.obs_pos, f + 1))
+        s.SimulateSwift()
+    x = s.GetPositions(0)
+    st = s.stats()
+    vf = s.contacts()[0]["index"].copy()
+    s.close()
+    return x, st, vf
+
+
+@pytest.mark.parametrize("cluster", [1, 2, 8, 16])
+def test_persistent_bit_equal_before_contact(cluster):
+    """Same device bodies, same phase order: with a proper colouring and no EE
+    contact (whose Jacobi sum uses float atomics) the two launch shapes agree
+    bit for bit, refit + contact generation + self-collision included."""
+    sc = scene.drop_scene(48, sphere=(16, 32), y=0.6)
+    x0, st0, vf0 = _run_frames(sc, 3, persist_cluster=0)
+    x1, st1, vf1 = _run_frames(sc, 3, persist_cluster=cluster)
+    np.testing.assert_array_equal(x0, x1)
+    np.testing.assert_array_equal(vf0, vf1)
+    assert st1["launches_per_frame"] < st0["launches_per_frame"] / 10
+
+
+@pytest.mark.parametrize("cluster", [1, 8, -1])
+def test_persistent_in_contact_vs_oracle(small, cluster):
+    s, o = pair(small, persist_cluster=cluster)
+    for f in range(6):
+        tgt = scene.sphere_motion(small.obs_pos, f + 1)
+        s.UpdateObstacleAnimationFrame(tgt)
+        o.set_obstacle_target(tgt)
+        s.SimulateSwift()
+        o.step_frame()
+    g = s.GetPositions(0)
+    assert np.isfinite(g).all()
+    assert rms(g, o.positions()) <= 1e-3, rms(g, o.positions())
+    assert_bvh_equal(s.bvh(), o.bvh())   # refit inside the persistent kernel: boxes bit exact
+    s.close()
+
+
+def test_persistent_one_substep_positions(small):
+    s, o = pair(small, num_substeps=1, persist_cluster=8)
+    s.SimulateSwift()
+    o.step_frame()
+    assert rel_rms(s.GetPositions(0), o.positions()) <= 1e-5
+    s.close()
+
+
+def test_per_stage_shape_still_matches_oracle(small):
+    s, o = pair(small, num_substeps=1, persist_cluster=0)
+    s.SimulateSwift()
+    o.step_frame()
+    assert rel_rms(s.GetPositions(0), o.positions()) <= 1e-5
     s.close()

@@ -3,12 +3,13 @@
 // (xrtailor/src/pipeline/base/ClothSolverBase.cpp:171-261) as one CUDA graph
 // per frame.  No CPU fallback lives here: without a CUDA device xrt_create fails.
 #include "../../include/xrt_b200.h"
-#include "xrt_solver.cuh"
+#include "xrt_persist.cuh"
 
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -44,6 +45,8 @@ struct xrt_solver {
   float4* d_seq = nullptr;  // pre-staged obstacle animation [seq_frames][Vo]
   size_t seq_frames = 0, seq_cursor = 0;
   cudaEvent_t ev_join = nullptr;
+  int cluster = 0;  // resolved persist_cluster (0: per-stage launches)
+  unsigned long long* d_prof = nullptr;  // [16] per-phase-kind ns of the persistent kernel (XRT_PERSIST_PROF=1)
 };
 
 static void xrt_set_error(xrt_solver* s, const char* fmt, ...) {
@@ -96,7 +99,7 @@ extern "C" int xrt_default_params(xrt_params* p) {
   p->geodesic_lra = 1;
   p->frame_dt = 1.0f / 60.0f;
   p->morton_fast_div = 1;
-  p->fused_iterations = 0;
+  p->persist_cluster = 8;
   p->device = 0;
   return XRT_OK;
 }
@@ -462,6 +465,19 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
       return XRT_ERR_CUDA;
     }
   }
+  // launch shape (xrt_params.persist_cluster)
+  {
+    int cl = s->p.persist_cluster;
+    const int mx = persist_max_cluster();
+    if (cl < 0 || cl > mx) cl = mx;
+    XRT_REQUIRE(cl == 0 || (cl & (cl - 1)) == 0, "persist_cluster must be 0, -1 or a power of two up to 16");
+    s->cluster = cl;
+    const char* pe = getenv("XRT_PERSIST_PROF");
+    if (cl > 0 && pe && pe[0] == '1') {
+      XRT_CUDA_OK(dev_alloc(&s->d_prof, 32));
+      XRT_CUDA_OK(cudaMemset(s->d_prof, 0, 32 * sizeof(unsigned long long)));
+    }
+  }
   const size_t stage = std::max<size_t>(std::max(c.V, o.V), 1);
   XRT_CUDA_OK(cudaMallocHost((void**)&s->stage, stage * sizeof(float4)));
   XRT_CUDA_OK(dev_alloc(&s->d_stage, stage));
@@ -521,6 +537,27 @@ static void enqueue_collision_pass(xrt_solver* s, bool moved, int cnt, uint32_t*
   (*launches) += s->c.E ? 2 : 1;
 }
 
+// arguments of the persistent kernel for one substep of the frame
+static PersistArgs make_persist_args(const xrt_solver* s, int substep, bool moved, bool do_predict) {
+  const xrt_params& p = s->p;
+  uint32_t frequency = (uint32_t)(p.num_substeps * p.num_iterations) / (uint32_t)p.num_collision_passes;
+  if (frequency == 0) frequency = 1;
+  PersistArgs a{};
+  a.c = s->c; a.o = s->o; a.bvh = s->bvh; a.k = s->k;
+  a.s_off = s->d_s_off; a.b_off = s->d_b_off;
+  a.refit_flags = s->bw.flags;
+  a.tol = p.bvh_tolerance;
+  a.substep = substep;
+  a.n_iter = p.num_iterations; a.n_passes = p.num_collision_passes;
+  a.frequency = frequency;
+  a.do_predict = do_predict ? 1 : 0; a.do_finalize = 1;
+  a.self_collision = p.enable_self_collision; a.solve_bending = p.solve_bending;
+  a.lra = p.geodesic_lra; a.moved = moved ? 1 : 0;
+  a.atomic_s = s->atomic_s ? 1 : 0; a.atomic_b = s->atomic_b ? 1 : 0;
+  a.prof = s->d_prof;
+  return a;
+}
+
 // SimulateSwift, ClothSolverBase.cpp:171-247
 static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
   const xrt_params& p = s->p;
@@ -537,9 +574,22 @@ static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
   if (frequency == 0) frequency = 1;  // the reference divides by zero here
   int cnt = 0;
   for (int substep = 0; substep < p.num_substeps; substep++) {
+    const bool hash = p.enable_self_collision && substep % std::max(1, p.inter_leaved_hash) == 0;
+    if (s->cluster > 0) {
+      // persistent shape: [predict + hash when due] + ONE kernel for the rest of the substep
+      if (hash) {
+        launch_predict(c, s->k, st);
+        launch_hash(c, s->k, st);
+        launches += 6;
+      }
+      const PersistArgs a = make_persist_args(s, substep, moved, !hash);
+      launch_swift_substep(a, s->cluster, st);
+      launches++;
+      continue;
+    }
     launch_predict(c, s->k, st);
     launches++;
-    if (p.enable_self_collision && substep % std::max(1, p.inter_leaved_hash) == 0) {
+    if (hash) {
       launch_hash(c, s->k, st);
       launches += 5;
     }
@@ -688,6 +738,25 @@ extern "C" int xrt_batch_run(xrt_solver** handles, int n, int frames, float* ms)
   return XRT_OK;
 }
 
+static double frame_bytes(const xrt_solver* s, bool moved);
+static double bvh_build_bytes(const xrt_solver* s) {
+  const double Fo = s->o.F;
+  return 84.0 * Fo + 24.0 * Fo + 8.0 * Fo * 8.0 + 40.0 * (2 * Fo - 1) + 8.0 * Fo;
+}
+
+extern "C" int xrt_persist_info(int cluster, int* max_cluster, int* resident) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+    (void)cudaGetLastError();
+    return XRT_ERR_CUDA;
+  }
+  const int mx = persist_max_cluster();
+  if (max_cluster) *max_cluster = mx;
+  if (cluster < 0 || cluster > mx) cluster = mx;
+  if (resident) *resident = persist_active_clusters(cluster < 1 ? 1 : cluster);
+  return XRT_OK;
+}
+
 extern "C" int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg_ms, double* bytes) {
   XRT_READY();
   XRT_REQUIRE(reps > 0 && avg_ms && bytes, "profile_kernel: bad argument");
@@ -725,6 +794,16 @@ extern "C" int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg
           launches++;
           b = 64.0 * c.V;
           break;
+        case 5: {
+          // the persistent substep kernel (substep 1: predict inside, no hash before it);
+          // algorithmic bytes = the frame's minus the BVH build, per substep
+          XRT_REQUIRE(s->cluster > 0, "profile_kernel: persistent shape is off (persist_cluster = 0)");
+          const PersistArgs a = make_persist_args(s, 1 % s->p.num_substeps, s->o.F != 0, true);
+          XRT_CUDA_OK(launch_swift_substep(a, s->cluster, s->st));
+          launches++;
+          b = (frame_bytes(s, s->o.F != 0) - (s->o.F ? bvh_build_bytes(s) : 0.0)) / s->p.num_substeps;
+          break;
+        }
         default: xrt_set_error(s, "profile_kernel: unknown kernel %d", which); return XRT_ERR_INVALID;
       }
     }
@@ -734,6 +813,42 @@ extern "C" int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg
   float ms = 0;
   XRT_CUDA_OK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
   *avg_ms = ms / (float)std::max(1, launches);
+  *bytes = b;
+  return XRT_OK;
+}
+
+extern "C" int xrt_batch_profile_substep(xrt_solver** handles, int n, int reps, float* avg_ms, double* bytes) {
+  if (!handles || n <= 0 || reps <= 0 || !avg_ms || !bytes) return XRT_ERR_INVALID;
+  xrt_solver* s = handles[0];
+  XRT_READY();
+  for (int i = 0; i < n; i++) {
+    if (!handles[i] || !handles[i]->finalized || handles[i]->p.device != s->p.device || handles[i]->cluster <= 0) {
+      xrt_set_error(s, "batch_profile_substep: handle %d is null, not finalized, on another device or per-stage", i);
+      return XRT_ERR_INVALID;
+    }
+    if (!handles[i]->ev_join) XRT_CUDA_OK(cudaEventCreateWithFlags(&handles[i]->ev_join, cudaEventDisableTiming));
+  }
+  double b = 0;
+  for (int pass = 0; pass < 2; pass++) {  // pass 0 warms up
+    XRT_CUDA_OK(cudaEventRecord(s->ev0, s->st));
+    for (int i = 1; i < n; i++) XRT_CUDA_OK(cudaStreamWaitEvent(handles[i]->st, s->ev0, 0));
+    b = 0;
+    for (int i = 0; i < n; i++) {
+      xrt_solver* h = handles[i];
+      const PersistArgs a = make_persist_args(h, 1 % h->p.num_substeps, h->o.F != 0, true);
+      for (int r = 0; r < (pass ? reps : 2); r++) XRT_CUDA_OK(launch_swift_substep(a, h->cluster, h->st));
+      b += (frame_bytes(h, h->o.F != 0) - (h->o.F ? bvh_build_bytes(h) : 0.0)) / h->p.num_substeps;
+    }
+    for (int i = 1; i < n; i++) {
+      XRT_CUDA_OK(cudaEventRecord(handles[i]->ev_join, handles[i]->st));
+      XRT_CUDA_OK(cudaStreamWaitEvent(s->st, handles[i]->ev_join, 0));
+    }
+    XRT_CUDA_OK(cudaEventRecord(s->ev1, s->st));
+    XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  }
+  float ms = 0;
+  XRT_CUDA_OK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+  *avg_ms = ms / (float)reps;
   *bytes = b;
   return XRT_OK;
 }
@@ -858,7 +973,7 @@ static double frame_bytes(const xrt_solver* s, bool moved) {
   double b = S * N * per_iter + S * (64.0 + 64.0) * V;              // + predict + finalize
   if (Fo) b += C * (48.0 * V + 48.0 * V + 88.0 * E);                // contact generation, compulsory traffic only
   if (moved && Fo) {
-    b += 84.0 * Fo + 24.0 * Fo + 8.0 * Fo * 8.0 + 40.0 * (2 * Fo - 1) + 8.0 * Fo;  // BVH build
+    b += bvh_build_bytes(s);  // BVH build
     b += C * (36.0 * Fo + 24.0 * (2 * Fo - 1) + 32.0 * Vo);                          // refit + interpolate
   }
   if (p.enable_self_collision) {
@@ -892,6 +1007,7 @@ extern "C" int xrt_debug_get(xrt_solver* s, int what, void* dst, size_t* bytes) 
     case XRT_DBG_VF_CAND_COUNT: src = s->c.cnt_vf; need = V * 4; break;
     case XRT_DBG_RT_CAND_COUNT: src = s->c.cnt_rt; need = V * 4; break;
     case XRT_DBG_EE_CAND_COUNT: src = s->c.cnt_ee; need = E * 4; break;
+    case XRT_DBG_PERSIST_PROF: src = s->d_prof; need = s->d_prof ? 32 * sizeof(unsigned long long) : 0; break;
     case XRT_DBG_COLORS_STRETCH: need = s->s_color.size() * 4; break;
     case XRT_DBG_COLORS_BEND: need = s->b_color.size() * 4; break;
     case XRT_DBG_AABBS: need = F ? (2 * F - 1) * 6 * sizeof(float) : 0; break;

@@ -6,9 +6,11 @@
 // (morton), :57-210 (determine_range / find_split), :212-264 (escape tables),
 // :423-462 (leaf boxes), :618-722 (Construct), :770-818 (RefitMidstep).
 #include "xrt_bvh.cuh"
+#include "xrt_dev_bvh.cuh"
 #include <cub/device/device_radix_sort.cuh>
 
 namespace {
+using namespace xrtdev;
 
 // order-preserving float <-> int map so atomicMin/Max work on floats
 __device__ __forceinline__ int f2ord(float f) {
@@ -159,40 +161,6 @@ __global__ void karras_kernel(const uint32_t* __restrict__ morton, const uint32_
   ranges[idx] = make_int2(first, last);
 }
 
-__device__ __forceinline__ void tnode_store_box(TNode* t, const float lo[3], const float hi[3]) {
-  // box lives in the first 24 bytes: one float4 + one float2 store
-  reinterpret_cast<float4*>(t)[0] = make_float4(lo[0], lo[1], lo[2], hi[0]);
-  reinterpret_cast<float2*>(t)[2] = make_float2(hi[1], hi[2]);
-}
-__device__ __forceinline__ void tnode_load_box(const TNode* t, float lo[3], float hi[3]) {
-  // L2 loads: sibling boxes written by other SMs must not come from a stale L1 line
-  float4 a = __ldcg(reinterpret_cast<const float4*>(t));
-  float2 b = __ldcg(reinterpret_cast<const float2*>(t) + 2);
-  lo[0] = a.x; lo[1] = a.y; lo[2] = a.z;
-  hi[0] = a.w; hi[1] = b.x; hi[2] = b.y;
-}
-
-// Bottom-up boxes in one pass (replaces AssignAABBAtomic_Kernel's
-// O(F log F) CAS walk, BVH.cu:540-556; min/max are exact so boxes are
-// identical).  The second thread to arrive at a parent merges its children.
-__device__ __forceinline__ void walk_up(TNode* tn, const BVNode* nodes, int* flags, uint32_t leaf_node) {
-  uint32_t parent = nodes[leaf_node].parent;
-  while (parent != 0xFFFFFFFFu) {
-    __threadfence();
-    if (atomicAdd(flags + parent, 1) == 0) return;
-    float la[3], ha[3], lb[3], hb[3];
-    tnode_load_box(tn + nodes[parent].left, la, ha);
-    tnode_load_box(tn + nodes[parent].right, lb, hb);
-#pragma unroll
-    for (int k = 0; k < 3; k++) {
-      la[k] = fminf(la[k], lb[k]);
-      ha[k] = fmaxf(ha[k], hb[k]);
-    }
-    tnode_store_box(tn + parent, la, ha);
-    parent = nodes[parent].parent;
-  }
-}
-
 __global__ void build_boxes_kernel(TNode* tn, const BVNode* __restrict__ nodes,
                                    const float* __restrict__ leaf_box,
                                    const uint32_t* __restrict__ obj, int* flags, uint32_t F) {
@@ -201,7 +169,7 @@ __global__ void build_boxes_kernel(TNode* tn, const BVNode* __restrict__ nodes,
   const float* b = leaf_box + 6 * (size_t)obj[i];
   float lo[3] = {b[0], b[1], b[2]}, hi[3] = {b[3], b[4], b[5]};
   tnode_store_box(tn + F - 1 + i, lo, hi);
-  walk_up(tn, nodes, flags, F - 1 + i);
+  walk_up<false>(tn, nodes, flags, F - 1 + i);
 }
 
 // Escape links in O(1) from the Karras ranges: the subtree that follows a
@@ -234,29 +202,12 @@ __global__ void link_kernel(TNode* tn, const BVNode* __restrict__ nodes, const i
   }
 }
 
-// Interpolated obstacle -> primitive pred + grow-only leaf boxes + exact
-// internal merge (RefitExternalNodeMidstep_Kernel + AssignAABBCAS_Kernel,
-// BVH.cu:770-793,515-538), one kernel.
+// RefitMidstep, one kernel (body in xrt_dev_bvh.cuh)
 __global__ void refit_kernel(TNode* tn, const BVNode* __restrict__ nodes, float4* __restrict__ pred,
                              const float4* __restrict__ x1, const float4* __restrict__ n1,
                              const uint32_t* __restrict__ tri, float tol, int* flags, uint32_t F) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= F) return;
-  const uint32_t node = F - 1 + i;
-  const uint32_t o = nodes[node].object;
-  float lo[3], hi[3];
-  tnode_load_box(tn + node, lo, hi);
-#pragma unroll
-  for (int k = 0; k < 3; k++) {
-    const uint32_t v = tri[3 * o + k];
-    const float4 p = x1[v], nn = n1[v];
-    const float4 q = make_float4(p.x + tol * nn.x, p.y + tol * nn.y, p.z + tol * nn.z, 0.f);
-    pred[3 * o + k] = q;
-    lo[0] = fminf(lo[0], q.x); lo[1] = fminf(lo[1], q.y); lo[2] = fminf(lo[2], q.z);
-    hi[0] = fmaxf(hi[0], q.x); hi[1] = fmaxf(hi[1], q.y); hi[2] = fmaxf(hi[2], q.z);
-  }
-  tnode_store_box(tn + node, lo, hi);
-  walk_up(tn, nodes, flags, node);
+  if (i < F) refit_item<false>(tn, nodes, pred, x1, n1, tri, tol, flags, F, i);
 }
 
 }  // namespace

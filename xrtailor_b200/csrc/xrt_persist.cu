@@ -1,0 +1,233 @@
+// One Swift substep as ONE persistent kernel on a thread-block cluster.
+//
+// The per-stage launch shape (xrt_api.cu: enqueue_frame with persist == 0)
+// replays ~270 dependent 3-5 us kernels per substep; each touches ~1.7 MB that
+// lives in L2, so the step is bound by launch + drain latency, not by HBM
+// (profiles/r01b_launches_percolour_summary.csv).  Here a cluster of C CTAs
+// (C x 1024 threads, one CTA per SM) owns one garment for the whole substep and
+// separates the ~270 phases with the hardware cluster barrier
+// (barrier.cluster, ~0.2 us) instead of a kernel boundary.  Independent
+// garments run on other clusters at the same time (one stream per handle), so
+// a B200 carries 148 / C garments concurrently.
+//
+// Phase order is exactly ClothSolverBase::SimulateSwift's inner loop
+// (pipeline/base/ClothSolverBase.cpp:189-243); the bodies are the same device
+// functions the per-stage kernels call, so results are bit-identical to that
+// path whenever the colouring is proper (no float atomics in the projection).
+#include "xrt_dev_bvh.cuh"
+#include "xrt_dev_contact.cuh"
+#include "xrt_dev_dynamics.cuh"
+#include "xrt_dev_hash.cuh"
+#include "xrt_persist.cuh"
+
+namespace {
+using namespace xrtdev;
+
+constexpr int PT = XRT_PERSIST_THREADS;
+
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ uint32_t cluster_nctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r));
+  return r;
+}
+
+// Barrier between two phases.  Release/acquire at cluster scope orders the
+// global-memory writes of every CTA of the cluster before the reads that
+// follow (ptxas emits the L1 invalidate with the acquire).  A one-CTA cluster
+// shares one L1, so bar.sync is enough.
+template <bool MULTI>
+__device__ __forceinline__ void phase_sync() {
+  if (MULTI) {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  } else {
+    __syncthreads();
+  }
+}
+
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// optional per-phase-kind wall time (ns, barrier included), thread 0 of CTA 0 only
+struct PhaseClock {
+  unsigned long long* acc;
+  unsigned long long t;
+  __device__ __forceinline__ void start(unsigned long long* a, uint32_t tid) {
+    acc = tid == 0 ? a : nullptr;
+    if (acc) t = gtimer();
+  }
+  __device__ __forceinline__ void lap(int kind) {
+    if (acc) {
+      const unsigned long long n = gtimer();
+      acc[kind] += n - t;
+      t = n;
+    }
+  }
+};
+
+template <bool MULTI>
+__global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_constant__ PersistArgs a) {
+  const uint32_t nth = (MULTI ? cluster_nctarank() : 1u) * PT;
+  const uint32_t tid = (MULTI ? cluster_ctarank() : 0u) * PT + threadIdx.x;
+  const ClothDev& c = a.c;
+  const ObstacleDev& o = a.o;
+  const StepConst& k = a.k;
+  const uint32_t V = c.V, E = c.E;
+  const float alpha_s = k.stretch_compliance / (k.dt * k.dt);
+  const float xpbd_b = k.bend_compliance / k.dt / k.dt;
+  PhaseClock pc;
+  pc.start(a.prof, tid);
+
+  if (a.do_predict) {
+    for (uint32_t i = tid; i < V; i += nth) predict_item(c.x0, c.x, c.v, k, i);
+    phase_sync<MULTI>();
+    pc.lap(0);
+  }
+  for (int it = 0; it < a.n_iter; it++) {
+    if (a.self_collision) {
+      for (uint32_t i = tid; i < V; i += nth) collide_item(c.delta, c.x, c.x0, c.neighbors, k, V, i);
+      phase_sync<MULTI>();
+    pc.lap(1);
+      for (uint32_t i = tid; i < V; i += nth) apply_delta_item(c.x, c.delta, k.relaxation, i);
+      phase_sync<MULTI>();
+    pc.lap(2);
+    }
+    const uint32_t step = (uint32_t)(a.substep * a.n_iter + it);
+    if (o.F && step % a.frequency == 0) {
+      if (a.moved) {
+        const int cnt = (int)(step / a.frequency);
+        const float alpha = ((float)cnt + 1.0f) / (float)a.n_passes;
+        for (uint32_t i = tid; i < o.V; i += nth) interpolate_item(o.x0, o.x, o.x1, alpha, i);
+        phase_sync<MULTI>();
+        for (uint32_t i = tid; i < o.V; i += nth) normals_item(o.x1, o.n1, o.tri, o.vf_off, o.vf_idx, i);
+        phase_sync<MULTI>();
+    pc.lap(3);
+        for (uint32_t i = tid; i < o.F; i += nth)
+          refit_item<true>(a.bvh.tnodes, a.bvh.nodes, a.bvh.pred, o.x1, o.n1, o.tri, a.tol, a.refit_flags, o.F, i);
+        phase_sync<MULTI>();
+    pc.lap(4);
+      }
+      for (uint32_t i = tid; i < V; i += nth)
+        gen_vertex_item<false>(a.bvh.tnodes, a.bvh.pred, c.x0, c.x, c.vf, c.rt, c.cnt_vf, c.cnt_rt, i);
+      for (uint32_t i = tid; i < E; i += nth)
+        gen_edge_item<false>(a.bvh.tnodes, a.bvh.pred, o.rtri, c.x, c.edge, c.ee, c.cnt_ee, i);
+      phase_sync<MULTI>();
+    pc.lap(5);
+    }
+    for (uint32_t col = 0; col < c.n_sc; col++) {
+      const uint32_t end = a.s_off[col + 1];
+      for (uint32_t i = a.s_off[col] + tid; i < end; i += nth)
+        stretch_one(c.x, c.s_idx, c.s_rest, c.s_lambda, i, alpha_s, it, a.atomic_s != 0);
+      phase_sync<MULTI>();
+    pc.lap(6);
+    }
+    if (a.solve_bending)
+      for (uint32_t col = 0; col < c.n_bc; col++) {
+        const uint32_t end = a.b_off[col + 1];
+        for (uint32_t i = a.b_off[col] + tid; i < end; i += nth)
+          bend_one(c.x, c.b_idx, c.b_theta, i, xpbd_b, a.atomic_b != 0);
+        phase_sync<MULTI>();
+    pc.lap(7);
+      }
+    if (a.lra && c.n_lra) {
+      for (uint32_t i = tid; i < c.n_lra; i += nth) lra_item(c.x, c.l_src, c.l_tgt, c.l_rest, k.lra_stretchiness, i);
+      phase_sync<MULTI>();
+    pc.lap(8);
+    }
+    if (o.F) {
+      for (uint32_t i = tid; i < V; i += nth) solve_vertex_item(a.bvh.pred, c.x, c.vf, c.rt, i);
+      phase_sync<MULTI>();
+    pc.lap(9);
+      if (E) {
+        for (uint32_t i = tid; i < E; i += nth) solve_edge_item(c.x, c.edge, c.ee, c.delta, i);
+        phase_sync<MULTI>();
+    pc.lap(10);
+      }
+      for (uint32_t i = tid; i < V; i += nth) apply_delta_item(c.x, c.delta, k.relaxation, i);
+      phase_sync<MULTI>();
+    pc.lap(11);
+    }
+  }
+  if (a.do_finalize)
+    for (uint32_t i = tid; i < V; i += nth) finalize_item(c.x0, c.x, c.v, k, i);
+  pc.lap(12);
+}
+
+}  // namespace
+
+int persist_max_cluster() {
+  static int cached = -1;
+  if (cached >= 0) return cached;
+  // clusters above 8 CTAs need the non-portable opt-in
+  cudaFuncSetAttribute(swift_substep_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  int best = 1;
+  for (int cs = 2; cs <= 16; cs *= 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(cs);
+    cfg.blockDim = dim3(PT);
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cs;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, swift_substep_kernel<true>, &cfg) == cudaSuccess && n > 0) best = cs;
+  }
+  (void)cudaGetLastError();
+  cached = best;
+  return cached;
+}
+
+int persist_active_clusters(int cluster) {
+  if (cluster <= 1) {
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;
+  }
+  persist_max_cluster();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cluster);
+  cfg.blockDim = dim3(PT);
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cluster;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, swift_substep_kernel<true>, &cfg) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t st) {
+  if (cluster <= 1) {
+    swift_substep_kernel<false><<<1, PT, 0, st>>>(a);
+    return cudaGetLastError();
+  }
+  persist_max_cluster();  // sets the non-portable attribute once
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(cluster);
+  cfg.blockDim = dim3(PT);
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cluster;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, swift_substep_kernel<true>, a);
+}

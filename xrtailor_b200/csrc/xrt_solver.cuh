@@ -77,12 +77,6 @@ void launch_apply_deltas(const ClothDev& c, const StepConst& k, cudaStream_t st)
 void launch_normals(const float4* x, float4* n, const uint32_t* tri, const uint32_t* vf_off,
                     const uint32_t* vf_idx, uint32_t V, cudaStream_t st);
 void launch_interpolate(const ObstacleDev& o, int step, int num_steps, cudaStream_t st);
-// fused: every colour of stretch+bend, LRA, contact solves, delta apply for one
-// iteration in ONE cooperative kernel with grid barriers between colours
-int launch_fused_iteration(const ClothDev& c, const DevBVH& bvh, const StepConst& k, const uint32_t* s_off,
-                           const uint32_t* b_off, int iter, bool solve_bend, bool lra, bool contacts,
-                           bool atomic, cudaStream_t st);
-
 // ---- contacts (xrt_contact.cu) ----
 void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, cudaStream_t st);
 void launch_solve_contacts(const ClothDev& c, const DevBVH& bvh, const StepConst& k, cudaStream_t st);

@@ -15,7 +15,7 @@ from ._abi import XrtError, XrtMeshDesc, XrtParams, XrtStats, default_params, li
 
 DBG = dict(MORTON=0, SORTED_OBJECT=1, NODES=2, AABBS=3, ESCAPE_INT=4, ESCAPE_EXT=5, VF_CONTACTS=6, RT_CONTACTS=7,
            EE_CONTACTS=8, PREDICTED=9, VELOCITY=10, COLORS_STRETCH=11, COLORS_BEND=12, NEIGHBORS=13, RTRI=14,
-           OBSTACLE_PRED=15, STATS=16, PARTICLE_HASH=17, VF_CAND_COUNT=18, RT_CAND_COUNT=19, EE_CAND_COUNT=20)
+           OBSTACLE_PRED=15, STATS=16, PARTICLE_HASH=17, VF_CAND_COUNT=18, RT_CAND_COUNT=19, EE_CAND_COUNT=20, PERSIST_PROF=21)
 
 _f32p = C.POINTER(C.c_float)
 _u32p = C.POINTER(C.c_uint32)
@@ -239,6 +239,25 @@ def batch_run(solvers, frames):
     if rc:
         raise XrtError(rc, lib.xrt_last_error(solvers[0]._h).decode(errors="replace"))
     return ms.value
+
+
+def batch_profile_substep(solvers, reps=20):
+    """(ms of one round of the persistent substep kernel on every solver side by side, bytes of that round)."""
+    arr = (C.c_void_p * len(solvers))(*[s._h for s in solvers])
+    ms, b = C.c_float(), C.c_double()
+    rc = lib.xrt_batch_profile_substep(arr, len(solvers), int(reps), C.byref(ms), C.byref(b))
+    if rc:
+        raise XrtError(rc, lib.xrt_last_error(solvers[0]._h).decode(errors="replace"))
+    return ms.value, b.value
+
+
+def persist_info(cluster=-1):
+    """(largest cluster the device schedules, clusters of `cluster` CTAs resident at once)."""
+    mx, res = C.c_int32(), C.c_int32()
+    rc = lib.xrt_persist_info(int(cluster), C.byref(mx), C.byref(res))
+    if rc:
+        raise XrtError(rc, "xrt_persist_info failed (no CUDA device)")
+    return mx.value, res.value
 
 
 def greedy_color(idx, n_verts):
