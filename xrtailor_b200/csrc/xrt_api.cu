@@ -46,6 +46,7 @@ struct xrt_solver {
   size_t seq_frames = 0, seq_cursor = 0;
   cudaEvent_t ev_join = nullptr;
   int cluster = 0;  // resolved persist_cluster (0: per-stage launches)
+  uint32_t *d_gen_list = nullptr, *d_gen_count = nullptr;  // compaction scratch of the persistent kernel
   unsigned long long* d_prof = nullptr;  // [16] per-phase-kind ns of the persistent kernel (XRT_PERSIST_PROF=1)
 };
 
@@ -435,6 +436,10 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
     for (auto& e : e0) { memset(&e, 0, sizeof(e)); e.dist = XRT_SCALAR_MAX; }
     if (c.E) XRT_CUDA_OK(cudaMemcpy(c.ee, e0.data(), c.E * sizeof(EEContact), cudaMemcpyHostToDevice));
   }
+  XRT_CUDA_OK(dev_alloc(&c.v_active, (c.V + 31) / 32));
+  XRT_CUDA_OK(cudaMemset(c.v_active, 0, std::max<size_t>((c.V + 31) / 32, 1) * 4));
+  XRT_CUDA_OK(dev_alloc(&c.e_active, (c.E + 31) / 32));
+  XRT_CUDA_OK(cudaMemset(c.e_active, 0, std::max<size_t>((c.E + 31) / 32, 1) * 4));
   XRT_CUDA_OK(dev_alloc(&c.cnt_vf, c.V));
   XRT_CUDA_OK(dev_alloc(&c.cnt_rt, c.V));
   XRT_CUDA_OK(dev_alloc(&c.cnt_ee, c.E));
@@ -472,6 +477,11 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
     if (cl < 0 || cl > mx) cl = mx;
     XRT_REQUIRE(cl == 0 || (cl & (cl - 1)) == 0, "persist_cluster must be 0, -1 or a power of two up to 16");
     s->cluster = cl;
+    if (cl > 0) {
+      XRT_CUDA_OK(dev_alloc(&s->d_gen_list, (size_t)c.V + c.E));
+      XRT_CUDA_OK(dev_alloc(&s->d_gen_count, 2));
+      XRT_CUDA_OK(cudaMemset(s->d_gen_count, 0, 2 * sizeof(uint32_t)));
+    }
     const char* pe = getenv("XRT_PERSIST_PROF");
     if (cl > 0 && pe && pe[0] == '1') {
       XRT_CUDA_OK(dev_alloc(&s->d_prof, 32));
@@ -533,7 +543,7 @@ static void enqueue_collision_pass(xrt_solver* s, bool moved, int cnt, uint32_t*
     bvh_refit_midstep(s->bvh, s->bw, s->o.x1, s->o.n1, s->o.tri, s->p.bvh_tolerance, st);
     (*launches) += 2 + bvh_refit_launches();
   }
-  launch_generate_contacts(s->c, s->bvh, s->o.rtri, st);
+  launch_generate_contacts(s->c, s->bvh, s->o.rtri, false, st);
   (*launches) += s->c.E ? 2 : 1;
 }
 
@@ -555,6 +565,8 @@ static PersistArgs make_persist_args(const xrt_solver* s, int substep, bool move
   a.lra = p.geodesic_lra; a.moved = moved ? 1 : 0;
   a.atomic_s = s->atomic_s ? 1 : 0; a.atomic_b = s->atomic_b ? 1 : 0;
   a.prof = s->d_prof;
+  a.gen_list = s->d_gen_list;
+  a.gen_count = s->d_gen_count;
   return a;
 }
 
@@ -785,7 +797,7 @@ extern "C" int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg
           break;
         case 3:
           XRT_REQUIRE(s->o.F, "no obstacle");
-          launch_generate_contacts(c, s->bvh, s->o.rtri, s->st);
+          launch_generate_contacts(c, s->bvh, s->o.rtri, false, s->st);
           launches += c.E ? 2 : 1;
           b = (96.0 * c.V + 88.0 * c.E) / (c.E ? 2 : 1);
           break;
@@ -873,7 +885,7 @@ extern "C" int xrt_bvh_refit_obstacle(xrt_solver* s, int step) {
 extern "C" int xrt_generate_contacts(xrt_solver* s) {
   XRT_READY();
   XRT_REQUIRE(s->o.F, "no obstacle");
-  launch_generate_contacts(s->c, s->bvh, s->o.rtri, s->st);
+  launch_generate_contacts(s->c, s->bvh, s->o.rtri, true, s->st);
   XRT_CUDA_OK(cudaStreamSynchronize(s->st));
   return XRT_OK;
 }
@@ -1001,7 +1013,7 @@ extern "C" int xrt_debug_get(xrt_solver* s, int what, void* dst, size_t* bytes) 
     case XRT_DBG_ESCAPE_EXT: src = s->bvh.esc_ext; need = F * 4; break;
     case XRT_DBG_VF_CONTACTS: src = s->c.vf; need = V * sizeof(VFContact); break;
     case XRT_DBG_RT_CONTACTS: src = s->c.rt; need = V * sizeof(VFContact); break;
-    case XRT_DBG_EE_CONTACTS: src = s->c.ee; need = E * sizeof(EEContact); break;
+    case XRT_DBG_EE_CONTACTS: need = E * sizeof(EEContact); break;
     case XRT_DBG_NEIGHBORS: src = s->c.neighbors; need = V * (size_t)s->p.max_num_neighbors * 4; break;
     case XRT_DBG_RTRI: src = s->o.rtri; need = (size_t)s->o.F * 4; break;
     case XRT_DBG_VF_CAND_COUNT: src = s->c.cnt_vf; need = V * 4; break;
@@ -1026,6 +1038,20 @@ extern "C" int xrt_debug_get(xrt_solver* s, int what, void* dst, size_t* bytes) 
     return XRT_OK;
   }
   switch (what) {
+    case XRT_DBG_EE_CONTACTS: {
+      // records exist only where the active bit is set; the rest reads as "no contact"
+      // like the reference's initial value (dist = SCALAR_MAX, PBDCollision.cu:105)
+      std::vector<uint32_t> bits((E + 31) / 32);
+      if (need) XRT_CUDA_OK(cudaMemcpy(dst, s->c.ee, need, cudaMemcpyDeviceToHost));
+      if (E) XRT_CUDA_OK(cudaMemcpy(bits.data(), s->c.e_active, bits.size() * 4, cudaMemcpyDeviceToHost));
+      EEContact* e = (EEContact*)dst;
+      for (size_t i = 0; i < E; i++)
+        if (!((bits[i >> 5] >> (i & 31)) & 1u)) {
+          memset(&e[i], 0, sizeof(EEContact));
+          e[i].dist = XRT_SCALAR_MAX;
+        }
+      break;
+    }
     case XRT_DBG_COLORS_STRETCH: memcpy(dst, s->s_color.data(), need); break;
     case XRT_DBG_COLORS_BEND: memcpy(dst, s->b_color.data(), need); break;
     case XRT_DBG_AABBS: {
@@ -1141,7 +1167,7 @@ extern "C" void xrt_destroy(xrt_solver* s) {
   ClothDev& c = s->c;
   void* ptrs[] = {c.x0, c.x, c.v, c.n, c.rest, c.tri, c.edge, c.vf_off, c.vf_idx, c.s_idx, c.s_rest, c.s_lambda,
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
-                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf,
+                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof, s->d_gen_list, s->d_gen_count,
                   c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
                   s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq};
   for (void* p : ptrs) cudaFree(p);

@@ -37,6 +37,41 @@ __host__ __device__ __forceinline__ float clampf(float x, float lo, float hi) { 
 // MathFunctions::FaceNormal, math/MathFunctions.cu:14-20
 __host__ __device__ __forceinline__ f3 face_normal(f3 a, f3 b, f3 c) { return normalize3(cross3(b - a, c - a)); }
 
+// Approximate single-precision helpers of the projection math (stretch, bend,
+// self-contact, contact solves).  These are the instructions the reference's
+// own build selects with --use_fast_math (CMakeLists.txt:217): MUFU rcp / rsq /
+// sqrt and fused multiply-add.  Discrete decisions (Morton bucket, box tests,
+// closest feature, hash cell) stay in IEEE arithmetic so candidate sets and
+// contact indices are bit-identical to the oracle; only float-valued position
+// updates go through here (gate: 1e-5 relative RMS after one substep).
+#ifdef __CUDACC__
+__device__ __forceinline__ float xf_div(float a, float b) { return __fdividef(a, b); }
+__device__ __forceinline__ float xf_rcp(float a) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+}
+__device__ __forceinline__ float xf_rsqrt(float a) {
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+}
+__device__ __forceinline__ float xf_sqrt(float a) {
+  float r;
+  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+  return r;
+}
+__device__ __forceinline__ float xf_dot(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ f3 xf_cross(f3 a, f3 b) {
+  return f3{fmaf(a.y, b.z, -(b.y * a.z)), fmaf(a.z, b.x, -(b.z * a.x)), fmaf(a.x, b.y, -(b.x * a.y))};
+}
+__device__ __forceinline__ float xf_len(f3 a) { return xf_sqrt(xf_dot(a, a)); }
+__device__ __forceinline__ f3 xf_normalize(f3 a) { return a * xf_rsqrt(xf_dot(a, a)); }
+__device__ __forceinline__ f3 xf_face_normal(f3 a, f3 b, f3 c) { return xf_normalize(xf_cross(b - a, c - a)); }
+// a + s*b
+__device__ __forceinline__ f3 xf_axpy(float s, f3 b, f3 a) { return f3{fmaf(s, b.x, a.x), fmaf(s, b.y, a.y), fmaf(s, b.z, a.z)}; }
+#endif
+
 // One BVH node packed for traversal: 32 bytes = one DRAM sector.
 //   lo.xyz, hi.xyz : box
 //   link_hit       : internal: left child index; leaf: ~object_idx (negative)

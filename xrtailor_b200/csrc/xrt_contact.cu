@@ -8,27 +8,35 @@ __global__ void generate_vertex_contacts_kernel(const TNode* __restrict__ t, con
                                                 const float4* __restrict__ x0, const float4* __restrict__ x,
                                                 VFContact* __restrict__ vf, VFContact* __restrict__ rt,
                                                 uint32_t* __restrict__ cnt_vf, uint32_t* __restrict__ cnt_rt,
-                                                uint32_t V) {
+                                                uint32_t* __restrict__ active, uint32_t V) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < V) gen_vertex_item<true>(t, pred, x0, x, vf, rt, cnt_vf, cnt_rt, i);
+  __shared__ uint32_t hits[XRT_HIT_CAP * XRT_BLOCK];
+  bool live = false;
+  if (i < V) live = gen_vertex_item<true, XRT_BLOCK>(t, pred, x0, x, vf, rt, cnt_vf, cnt_rt, hits + threadIdx.x, i);
+  store_active_bits(active, i, V, live);
 }
 __global__ void generate_edge_contacts_kernel(const TNode* __restrict__ t, const float4* __restrict__ pred,
                                               const uint32_t* __restrict__ rtri, const float4* __restrict__ x,
                                               const uint2* __restrict__ edge, EEContact* __restrict__ ee,
-                                              uint32_t* __restrict__ cnt_ee, uint32_t E) {
+                                              uint32_t* __restrict__ cnt_ee, uint32_t* __restrict__ active,
+                                              uint32_t E) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < E) gen_edge_item<true>(t, pred, rtri, x, edge, ee, cnt_ee, i);
+  __shared__ uint32_t hits[XRT_HIT_CAP * XRT_BLOCK];
+  bool live = false;
+  if (i < E) live = gen_edge_item<true, XRT_BLOCK>(t, pred, rtri, x, edge, ee, cnt_ee, hits + threadIdx.x, i);
+  store_active_bits(active, i, E, live);
 }
 __global__ void solve_vertex_contacts_kernel(const float4* __restrict__ pred, float4* __restrict__ x,
                                              const VFContact* __restrict__ vf, const VFContact* __restrict__ rt,
-                                             uint32_t V) {
+                                             const uint32_t* __restrict__ active, uint32_t V) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < V) solve_vertex_item(pred, x, vf, rt, i);
+  if (i < V && load_active_bit(active, i)) solve_vertex_item(pred, x, vf, rt, i);
 }
 __global__ void solve_edge_contacts_kernel(const float4* __restrict__ x, const uint2* __restrict__ edge,
-                                           const EEContact* __restrict__ ee, float4* delta, uint32_t E) {
+                                           const EEContact* __restrict__ ee, const uint32_t* __restrict__ active,
+                                           float4* delta, uint32_t E) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < E) solve_edge_item(x, edge, ee, delta, i);
+  if (i < E && load_active_bit(active, i)) solve_edge_item(x, edge, ee, delta, i);
 }
 
 // candidate lists in traversal order for the parity tests
@@ -61,19 +69,22 @@ __global__ void candidates_kernel(const TNode* __restrict__ t, const float4* __r
 
 }  // namespace
 
-void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, cudaStream_t st) {
+void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, bool counts,
+                              cudaStream_t st) {
   if (!bvh.n_obj) return;
-  generate_vertex_contacts_kernel<<<xrt_grid(c.V), XRT_BLOCK, 0, st>>>(bvh.tnodes, bvh.pred, c.x0, c.x, c.vf, c.rt,
-                                                                       c.cnt_vf, c.cnt_rt, c.V);
+  generate_vertex_contacts_kernel<<<xrt_grid(c.V), XRT_BLOCK, 0, st>>>(
+      bvh.tnodes, bvh.pred, c.x0, c.x, c.vf, c.rt, counts ? c.cnt_vf : nullptr, counts ? c.cnt_rt : nullptr,
+      c.v_active, c.V);
   if (c.E)
-    generate_edge_contacts_kernel<<<xrt_grid(c.E), XRT_BLOCK, 0, st>>>(bvh.tnodes, bvh.pred, rtri, c.x, c.edge,
-                                                                       c.ee, c.cnt_ee, c.E);
+    generate_edge_contacts_kernel<<<xrt_grid(c.E), XRT_BLOCK, 0, st>>>(
+        bvh.tnodes, bvh.pred, rtri, c.x, c.edge, c.ee, counts ? c.cnt_ee : nullptr, c.e_active, c.E);
 }
 
 void launch_solve_contacts(const ClothDev& c, const DevBVH& bvh, const StepConst& k, cudaStream_t st) {
   if (!bvh.n_obj) return;
-  solve_vertex_contacts_kernel<<<xrt_grid(c.V), XRT_BLOCK, 0, st>>>(bvh.pred, c.x, c.vf, c.rt, c.V);
-  if (c.E) solve_edge_contacts_kernel<<<xrt_grid(c.E), XRT_BLOCK, 0, st>>>(c.x, c.edge, c.ee, c.delta, c.E);
+  solve_vertex_contacts_kernel<<<xrt_grid(c.V), XRT_BLOCK, 0, st>>>(bvh.pred, c.x, c.vf, c.rt, c.v_active, c.V);
+  if (c.E)
+    solve_edge_contacts_kernel<<<xrt_grid(c.E), XRT_BLOCK, 0, st>>>(c.x, c.edge, c.ee, c.e_active, c.delta, c.E);
 }
 
 void launch_candidates(const ClothDev& c, const DevBVH& bvh, int kind, const uint32_t* offsets, uint32_t* items,

@@ -182,29 +182,57 @@ __device__ __forceinline__ float closest_seg_seg(f3 p1, f3 q1, f3 p2, f3 q2, flo
   return len3(c1 - c2);
 }
 
+// Leaf hits are staged in a small per-thread shared-memory buffer and the
+// narrow phase runs over the buffer after the traversal (or when it fills), so
+// the lanes of a warp execute the expensive primitive tests together instead of
+// one lane at a time as each reaches a leaf.  Hits are consumed in traversal
+// order, so "first minimum wins" is unchanged.  hb = this thread's slot 0;
+// consecutive slots are BS words apart (bank-conflict free).
+#define XRT_HIT_CAP 8
+template <int BS, class Narrow>
+struct HitStage {
+  uint32_t* hb;
+  int n;
+  Narrow& narrow;
+  __device__ __forceinline__ HitStage(uint32_t* b, Narrow& f) : hb(b), n(0), narrow(f) {}
+  __device__ __forceinline__ void flush() {
+    for (int h = 0; h < n; h++) narrow(hb[h * BS]);
+    n = 0;
+  }
+  __device__ __forceinline__ void push(uint32_t o) {
+    hb[n * BS] = o;
+    if (++n == XRT_HIT_CAP) flush();
+  }
+};
+
 // GenerateVF_DCD_Kernel + GenerateVFCCD_Kernel (PBDCollision.cu:17-47,236-268):
 // both per-vertex queries for one vertex (x and x0 are loaded once).
-template <bool NC>
-__device__ __forceinline__ void gen_vertex_item(const TNode* t, const float4* pred, const float4* x0, const float4* x,
+// Returns whether the vertex has any contact (either query).
+template <bool NC, int BS>
+__device__ __forceinline__ bool gen_vertex_item(const TNode* t, const float4* pred, const float4* x0, const float4* x,
                                                 VFContact* vf, VFContact* rt, uint32_t* cnt_vf, uint32_t* cnt_rt,
-                                                uint32_t i) {
+                                                uint32_t* hb, uint32_t i) {
   const f3 p = mk3(x[i]);
+  bool live_vf;
   {
     float best = XRT_SCALAR_MAX;
     int best_idx = -1;
     f3 best_q = mk3(0, 0, 0);
-    uint32_t nf = traverse<NC>(
-        t, [&](const Box& b) { return overlap_point(b, p); },
-        [&](uint32_t o) {
-          f3 qs;
-          const float d = nearest_point(p, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]), qs);
-          if (d < best) {
-            best = d;
-            best_q = qs;
-            best_idx = (int)o;
-          }
-        });
+    auto narrow = [&](uint32_t o) {
+      f3 qs;
+      const float d = nearest_point(p, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]), qs);
+      if (d < best) {
+        best = d;
+        best_q = qs;
+        best_idx = (int)o;
+      }
+    };
+    HitStage<BS, decltype(narrow)> st(hb, narrow);
+    const uint32_t nf = traverse<NC>(
+        t, [&](const Box& b) { return overlap_point(b, p); }, [&](uint32_t o) { st.push(o); });
+    st.flush();
     vf[i] = VFContact{best_idx, {best_q.x, best_q.y, best_q.z}};
+    live_vf = best_idx != -1;
     if (cnt_vf) cnt_vf[i] = nf;
   }
   {
@@ -216,57 +244,70 @@ __device__ __forceinline__ void gen_vertex_item(const TNode* t, const float4* pr
     if (!(length < XRT_EPS)) {
       d = d / length;
       float best = XRT_SCALAR_MAX;
+      auto narrow = [&](uint32_t o) {
+        const float dist = ray_intersect(p1, d, length, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]));
+        if (dist < best) {
+          const f3 qc = p1 + dist * d;
+          out = VFContact{(int)o, {qc.x, qc.y, qc.z}};
+          best = dist;
+        }
+      };
+      HitStage<BS, decltype(narrow)> st(hb, narrow);
       nf = traverse<NC>(
-          t, [&](const Box& b) { return overlap_segment(b, p1, p); },
-          [&](uint32_t o) {
-            const float dist = ray_intersect(p1, d, length, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]));
-            if (dist < best) {
-              const f3 qc = p1 + dist * d;
-              out = VFContact{(int)o, {qc.x, qc.y, qc.z}};
-              best = dist;
-            }
-          });
+          t, [&](const Box& b) { return overlap_segment(b, p1, p); }, [&](uint32_t o) { st.push(o); });
+      st.flush();
     }
     rt[i] = out;
     if (cnt_rt) cnt_rt[i] = nf;
+    return live_vf || out.index != -1;
   }
 }
 
 // GenerateEE_DCD_Kernel, PBDCollision.cu:100-153
-template <bool NC>
-__device__ __forceinline__ void gen_edge_item(const TNode* t, const float4* pred, const uint32_t* rtri,
+// Returns whether a contact was found; only then is ee[i] written (the active
+// bit, not the record, says "no contact").
+template <bool NC, int BS>
+__device__ __forceinline__ bool gen_edge_item(const TNode* t, const float4* pred, const uint32_t* rtri,
                                               const float4* x, const uint2* edge, EEContact* ee, uint32_t* cnt_ee,
-                                              uint32_t i) {
+                                              uint32_t* hb, uint32_t i) {
   const uint2 e = edge[i];
   const f3 pc = mk3(x[e.x]), qc = mk3(x[e.y]);
   float s = 0.f, tt = 0.f, min_dist = XRT_SCALAR_MAX;
-  f3 p2 = mk3(0, 0, 0), q2 = mk3(0, 0, 0), fn = mk3(0, 0, 0);
-  uint32_t nf = traverse<NC>(
-      t, [&](const Box& b) { return overlap_segment(b, pc, qc); },
-      [&](uint32_t o) {
-        const uint32_t info = rtri[o];
-        const f3 ov[3] = {mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2])};
+  f3 p2 = mk3(0, 0, 0), q2 = mk3(0, 0, 0);
+  uint32_t best_o = 0xFFFFFFFFu;
+  auto narrow = [&](uint32_t o) {
+    const uint32_t info = rtri[o] >> 3;  // RTriEdge bits
+    if (!info) return;
+    const f3 ov[3] = {mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2])};
 #pragma unroll
-        for (uint32_t k = 0; k < 3; k++) {
-          if ((info >> (k + 3u)) & 1u) {  // RTriEdge
-            float _s, _t;
-            f3 c1, c2;
-            const uint32_t j = (k + 1u) % 3u;
-            // the reference tests the returned distance as a bool: non-zero distance only
-            if (closest_seg_seg(pc, qc, ov[k], ov[j], _s, _t, c1, c2) != 0.f) {
-              const float dist = len3(c1 - c2);
-              if (dist < min_dist) {
-                min_dist = dist;
-                p2 = ov[k];
-                q2 = ov[j];
-                s = _s;
-                tt = _t;
-                fn = face_normal(ov[0], ov[1], ov[2]);
-              }
-            }
+    for (uint32_t k = 0; k < 3; k++) {
+      if ((info >> k) & 1u) {
+        float _s, _t;
+        f3 c1, c2;
+        const uint32_t j = (k + 1u) % 3u;
+        // the reference tests the returned distance as a bool: non-zero distance only
+        if (closest_seg_seg(pc, qc, ov[k], ov[j], _s, _t, c1, c2) != 0.f) {
+          const float dist = len3(c1 - c2);
+          if (dist < min_dist) {
+            min_dist = dist;
+            p2 = ov[k];
+            q2 = ov[j];
+            s = _s;
+            tt = _t;
+            best_o = o;
           }
         }
-      });
+      }
+    }
+  };
+  HitStage<BS, decltype(narrow)> st(hb, narrow);
+  const uint32_t nf = traverse<NC>(
+      t, [&](const Box& b) { return overlap_segment(b, pc, qc); }, [&](uint32_t o) { st.push(o); });
+  st.flush();
+  if (cnt_ee) cnt_ee[i] = nf;
+  if (!(min_dist < 1e6f)) return false;
+  // the winning face's normal, once (the reference recomputes it on every improvement)
+  const f3 fn = face_normal(mk3(pred[3 * best_o]), mk3(pred[3 * best_o + 1]), mk3(pred[3 * best_o + 2]));
   EEContact c;
   c.dist = min_dist;
   c.p2[0] = p2.x; c.p2[1] = p2.y; c.p2[2] = p2.z;
@@ -274,7 +315,7 @@ __device__ __forceinline__ void gen_edge_item(const TNode* t, const float4* pred
   c.s = s; c.t = tt;
   c.fn[0] = fn.x; c.fn[1] = fn.y; c.fn[2] = fn.z;
   ee[i] = c;
-  if (cnt_ee) cnt_ee[i] = nf;
+  return true;
 }
 
 // SolveVFCCD_Kernel then SolveVFDCD_Kernel (PBDCollision.cu:279-297,57-75) on
@@ -286,16 +327,16 @@ __device__ __forceinline__ void solve_vertex_item(const float4* pred, float4* x,
   float4 p = x[i];
   bool dirty = false;
   if (c.index != -1) {
-    const f3 nc = face_normal(mk3(pred[3 * c.index]), mk3(pred[3 * c.index + 1]), mk3(pred[3 * c.index + 2]));
-    const float lambda = dot3(nc, mk3(p) - mk3(c.q[0], c.q[1], c.q[2]));
+    const f3 nc = xf_face_normal(mk3(pred[3 * c.index]), mk3(pred[3 * c.index + 1]), mk3(pred[3 * c.index + 2]));
+    const float lambda = xf_dot(nc, mk3(p) - mk3(c.q[0], c.q[1], c.q[2]));
     if (lambda < 0) {
       p.x += -lambda * nc.x; p.y += -lambda * nc.y; p.z += -lambda * nc.z;
       dirty = true;
     }
   }
   if (d.index != -1) {
-    const f3 ns = face_normal(mk3(pred[3 * d.index]), mk3(pred[3 * d.index + 1]), mk3(pred[3 * d.index + 2]));
-    const float lambda = dot3(ns, mk3(p) - mk3(d.q[0], d.q[1], d.q[2])) - 1e-3f;
+    const f3 ns = xf_face_normal(mk3(pred[3 * d.index]), mk3(pred[3 * d.index + 1]), mk3(pred[3 * d.index + 2]));
+    const float lambda = xf_dot(ns, mk3(p) - mk3(d.q[0], d.q[1], d.q[2])) - 1e-3f;
     if (lambda < 0) {
       p.x += -lambda * ns.x; p.y += -lambda * ns.y; p.z += -lambda * ns.z;
       dirty = true;
@@ -304,11 +345,11 @@ __device__ __forceinline__ void solve_vertex_item(const float4* pred, float4* x,
   if (dirty) x[i] = p;
 }
 
-// SolveEEDCD_Kernel, PBDCollision.cu:163-207
+// SolveEEDCD_Kernel, PBDCollision.cu:163-207.  `active` is the bit the
+// generation pass recorded for this edge (dist < 1e6); inactive records are
+// not stored, so they must not be read.
 __device__ __forceinline__ void solve_edge_item(const float4* x, const uint2* edge, const EEContact* ee,
                                                 float4* delta, uint32_t i) {
-  const float dist = ee[i].dist;
-  if (dist > 1e6f) return;
   const EEContact c = ee[i];
   const uint2 e = edge[i];
   const f3 p1 = mk3(x[e.x]), q1 = mk3(x[e.y]);
@@ -317,14 +358,28 @@ __device__ __forceinline__ void solve_edge_item(const float4* x, const uint2* ed
   const f3 c1 = (1 - c.s) * p1 + c.s * q1;
   const f3 c2 = (1 - c.t) * p2 + c.t * q2;
   const f3 d = c1 - c2;
-  if (len3(d) < XRT_EPS) return;
-  const float lambda = dot3(d, fn) - 1e-3f;
+  if (xf_len(d) < XRT_EPS) return;
+  const float lambda = xf_dot(d, fn) - 1e-3f;
   if (lambda > 0) return;
   const f3 k1 = (-(1 - c.s) * lambda) * fn, k2 = (-(c.s) * lambda) * fn;
   atomicAdd(&delta[e.x].x, k1.x); atomicAdd(&delta[e.x].y, k1.y); atomicAdd(&delta[e.x].z, k1.z);
   atomicAdd(&delta[e.x].w, 1.0f);
   atomicAdd(&delta[e.y].x, k2.x); atomicAdd(&delta[e.y].y, k2.y); atomicAdd(&delta[e.y].z, k2.z);
   atomicAdd(&delta[e.y].w, 1.0f);
+}
+
+// Bit i of these masks = "item i has a live contact"; one word per 32
+// consecutive items, written by lane 0 from a warp ballot in the generation
+// pass (callers keep 32-item groups warp-aligned).  The solves read one
+// broadcast word per warp instead of a 48-byte record per edge.
+// Must be called by all 32 lanes of the warp (lanes past the end pass live = false);
+// i = this lane's item, a multiple of 32 on lane 0.
+__device__ __forceinline__ void store_active_bits(uint32_t* mask, uint32_t i, uint32_t n, bool live) {
+  const uint32_t b = __ballot_sync(0xFFFFFFFFu, live);
+  if ((threadIdx.x & 31u) == 0 && i < n) mask[i >> 5] = b;
+}
+__device__ __forceinline__ bool load_active_bit(const uint32_t* mask, uint32_t i) {
+  return (mask[i >> 5] >> (i & 31u)) & 1u;
 }
 
 }  // namespace xrtdev

@@ -18,14 +18,14 @@ __device__ __forceinline__ void predict_item(const float4* x0, float4* x, float4
     vel.z += k.gz * k.dt;
     v[i] = vel;
   }
-  x[i] = make_float4(p.x + vel.x * k.dt, p.y + vel.y * k.dt, p.z + vel.z * k.dt, p.w);
+  x[i] = make_float4(fmaf(vel.x, k.dt, p.x), fmaf(vel.y, k.dt, p.y), fmaf(vel.z, k.dt, p.z), p.w);
 }
 
 // Finalize_Kernel, ClothSolverHelper.cu:222-229
 __device__ __forceinline__ void finalize_item(float4* x0, const float4* x, float4* v, const StepConst& k, uint32_t i) {
   float4 p = x[i], q = x0[i];
-  const float s = 1.0f - k.damping * k.dt;
-  v[i] = make_float4((p.x - q.x) / k.dt * s, (p.y - q.y) / k.dt * s, (p.z - q.z) / k.dt * s, 0.f);
+  const float s = xf_rcp(k.dt) * (1.0f - k.damping * k.dt);
+  v[i] = make_float4((p.x - q.x) * s, (p.y - q.y) * s, (p.z - q.z) * s, 0.f);
   x0[i] = p;
 }
 
@@ -43,58 +43,71 @@ __device__ __forceinline__ void add_pos(float4* x, uint32_t i, f3 c, bool atomic
 
 // SolveStretch_Kernel, BasicSolverHelper.cu:80-127.  The record (ij, rest) is
 // passed in so a caller can fetch it ahead of a barrier.
+// `lambda` is the multiplier carried from the previous iteration (0 at iteration 0).
 __device__ __forceinline__ void stretch_rec(float4* x, float* s_lambda, uint32_t id, uint2 ij, float rest,
-                                            float alpha_tilde, int iter, bool atomic) {
-  float lambda = iter == 0 ? 0.f : s_lambda[id];
+                                            float lambda, float alpha_tilde, bool atomic) {
   const float4 a = x[ij.x], b = x[ij.y];
   const f3 diff = mk3(a) - mk3(b);
-  const float dist = len3(diff);
+  const float dist = xf_len(diff);
   const float w1 = a.w, w2 = b.w;
   if (dist != rest && w1 + w2 > 0.f) {
-    const f3 grad = diff / (dist + XRT_EPS);
+    const f3 grad = diff * xf_rcp(dist + XRT_EPS);
     const float C = dist - rest;
-    const float dl = (-C - alpha_tilde * lambda) / (w1 + w2 + alpha_tilde);
+    const float dl = xf_div(-C - alpha_tilde * lambda, w1 + w2 + alpha_tilde);
     const f3 corr = dl * grad;
     lambda += dl;
     if (atomic) {
       add_pos(x, ij.x, corr * w1, true);
       add_pos(x, ij.y, (-corr) * w2, true);
     } else {
-      x[ij.x] = make_float4(a.x + corr.x * w1, a.y + corr.y * w1, a.z + corr.z * w1, a.w);
-      x[ij.y] = make_float4(b.x - corr.x * w2, b.y - corr.y * w2, b.z - corr.z * w2, b.w);
+      x[ij.x] = make_float4(fmaf(corr.x, w1, a.x), fmaf(corr.y, w1, a.y), fmaf(corr.z, w1, a.z), a.w);
+      x[ij.y] = make_float4(fmaf(-corr.x, w2, b.x), fmaf(-corr.y, w2, b.y), fmaf(-corr.z, w2, b.z), b.w);
     }
   }
   s_lambda[id] = lambda;
 }
 __device__ __forceinline__ void stretch_one(float4* x, const uint2* s_idx, const float* s_rest, float* s_lambda,
                                             uint32_t id, float alpha_tilde, int iter, bool atomic) {
-  stretch_rec(x, s_lambda, id, s_idx[id], s_rest[id], alpha_tilde, iter, atomic);
+  stretch_rec(x, s_lambda, id, s_idx[id], s_rest[id], iter == 0 ? 0.f : s_lambda[id], alpha_tilde, atomic);
 }
 
-// SolveBend_Kernel, BasicSolverHelper.cu:8-66
+// SolveBend_Kernel, BasicSolverHelper.cu:8-66.  Without atomics the four
+// positions gathered at the top are the ones updated at the bottom (a proper
+// colouring gives this thread exclusive ownership), so x is read once.
 __device__ __forceinline__ void bend_rec(float4* x, uint4 q, float theta0, float xpbd_bend, bool atomic) {
   const float4 a1 = x[q.x], a2 = x[q.y], a3 = x[q.z], a4 = x[q.w];
   const float w1 = a1.w, w2 = a2.w, w3 = a3.w, w4 = a4.w;
   const f3 p1 = mk3(a1);
   const f3 p2 = mk3(a2) - p1, p3 = mk3(a3) - p1, p4 = mk3(a4) - p1;
-  const f3 c23 = cross3(p2, p3), c24 = cross3(p2, p4);
-  const f3 n1 = normalize3(c23), n2 = normalize3(c24);
-  const float dd = dot3(n1, n2);
+  const f3 c23 = xf_cross(p2, p3), c24 = xf_cross(p2, p4);
+  const float s23 = xf_dot(c23, c23), s24 = xf_dot(c24, c24);
+  const f3 n1 = c23 * xf_rsqrt(s23), n2 = c24 * xf_rsqrt(s24);
+  const float dd = xf_dot(n1, n2);
   const float d = dd < 0.f ? 0.f : (dd > 1.f ? 1.f : dd);  // MathFunctions::Clamp
   const float angle = acosf(d);
   if (angle < XRT_EPS || isnan(d)) return;
-  const float l23 = len3(c23) + XRT_EPS, l24 = len3(c24) + XRT_EPS;
-  const f3 q3 = (cross3(p2, n2) + cross3(n1, p2) * d) / l23;
-  const f3 q4 = (cross3(p2, n1) + cross3(n2, p2) * d) / l24;
-  const f3 q2 = -((cross3(p3, n2) + cross3(n1, p3) * d) / l23) - (cross3(p4, n1) + cross3(n2, p4) * d) / l24;
+  const float i23 = xf_rcp(xf_sqrt(s23) + XRT_EPS), i24 = xf_rcp(xf_sqrt(s24) + XRT_EPS);
+  const f3 q3 = xf_axpy(d, xf_cross(n1, p2), xf_cross(p2, n2)) * i23;
+  const f3 q4 = xf_axpy(d, xf_cross(n2, p2), xf_cross(p2, n1)) * i24;
+  const f3 q2 = -(xf_axpy(d, xf_cross(n1, p3), xf_cross(p3, n2)) * i23) -
+                xf_axpy(d, xf_cross(n2, p4), xf_cross(p4, n1)) * i24;
   const f3 q1 = -q2 - q3 - q4;
-  const float denom = xpbd_bend + (w1 * dot3(q1, q1) + w2 * dot3(q2, q2) + w3 * dot3(q3, q3) + w4 * dot3(q4, q4));
+  const float denom = xpbd_bend + fmaf(w1, xf_dot(q1, q1), fmaf(w2, xf_dot(q2, q2), fmaf(w3, xf_dot(q3, q3), w4 * xf_dot(q4, q4))));
   if (denom < XRT_EPS) return;
-  const float lambda = sqrtf(1.0f - d * d) * (angle - theta0) / denom;
-  add_pos(x, q.x, (w1 * lambda) * q1, atomic);
-  add_pos(x, q.y, (w2 * lambda) * q2, atomic);
-  add_pos(x, q.z, (w3 * lambda) * q3, atomic);
-  add_pos(x, q.w, (w4 * lambda) * q4, atomic);
+  const float lambda = xf_div(xf_sqrt(fmaf(-d, d, 1.0f)) * (angle - theta0), denom);
+  if (atomic) {
+    add_pos(x, q.x, (w1 * lambda) * q1, true);
+    add_pos(x, q.y, (w2 * lambda) * q2, true);
+    add_pos(x, q.z, (w3 * lambda) * q3, true);
+    add_pos(x, q.w, (w4 * lambda) * q4, true);
+  } else {
+    const f3 r1 = xf_axpy(w1 * lambda, q1, p1), r2 = xf_axpy(w2 * lambda, q2, mk3(a2));
+    const f3 r3 = xf_axpy(w3 * lambda, q3, mk3(a3)), r4 = xf_axpy(w4 * lambda, q4, mk3(a4));
+    x[q.x] = make_float4(r1.x, r1.y, r1.z, w1);
+    x[q.y] = make_float4(r2.x, r2.y, r2.z, w2);
+    x[q.z] = make_float4(r3.x, r3.y, r3.z, w3);
+    x[q.w] = make_float4(r4.x, r4.y, r4.z, w4);
+  }
 }
 __device__ __forceinline__ void bend_one(float4* x, const uint4* b_idx, const float* b_theta, uint32_t id,
                                          float xpbd_bend, bool atomic) {
@@ -110,9 +123,9 @@ __device__ __forceinline__ void lra_item(float4* x, const uint32_t* src, const u
   float4 pt = x[t];
   if (pt.w < XRT_EPS && target > 0.f) return;
   const f3 diff = mk3(pt) - mk3(x[s]);
-  const float dist = len3(diff);
+  const float dist = xf_len(diff);
   if (dist > target) {
-    const f3 c = -diff + diff / dist * target;
+    const f3 c = -diff + diff * (xf_rcp(dist) * target);
     pt.x += c.x; pt.y += c.y; pt.z += c.z;
     x[t] = pt;
   }
@@ -123,9 +136,10 @@ __device__ __forceinline__ void apply_delta_item(float4* x, float4* delta, float
   const float4 d = delta[i];
   if (d.w > 0.f) {
     float4 p = x[i];
-    p.x += d.x / d.w * relaxation;
-    p.y += d.y / d.w * relaxation;
-    p.z += d.z / d.w * relaxation;
+    const float sc = xf_rcp(d.w) * relaxation;
+    p.x = fmaf(d.x, sc, p.x);
+    p.y = fmaf(d.y, sc, p.y);
+    p.z = fmaf(d.z, sc, p.z);
     x[i] = p;
     delta[i] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
@@ -138,11 +152,30 @@ __device__ __forceinline__ void normals_item(const float4* x, float4* n, const u
                                              const uint32_t* vf_idx, uint32_t i) {
   const f3 p = mk3(x[i]);
   f3 acc = mk3(0.f, 0.f, 0.f);
-  for (uint32_t k = vf_off[i]; k < vf_off[i + 1]; k++) {
-    const uint32_t fc = vf_idx[k], f = fc >> 2, j = fc & 3u;
-    const f3 e0 = mk3(x[tri[3 * f + (j + 1) % 3]]) - p;
-    const f3 e1 = mk3(x[tri[3 * f + (j + 2) % 3]]) - p;
-    acc = acc + cross3(e0, e1) / (dot3(e0, e0) * dot3(e1, e1));
+  // incident faces in batches of 4: the index -> corner -> position chains of a
+  // batch are issued together (same summation order as one face at a time)
+  const uint32_t kb = vf_off[i], ke = vf_off[i + 1];
+  for (uint32_t k0 = kb; k0 < ke; k0 += 4) {
+    uint32_t ia[4], ib[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      const uint32_t fc = k0 + u < ke ? vf_idx[k0 + u] : 0xFFFFFFFFu;
+      const uint32_t f = fc >> 2, j = fc & 3u;
+      ia[u] = fc != 0xFFFFFFFFu ? tri[3 * f + (j + 1) % 3] : 0xFFFFFFFFu;
+      ib[u] = fc != 0xFFFFFFFFu ? tri[3 * f + (j + 2) % 3] : 0xFFFFFFFFu;
+    }
+    float4 pa[4], pb[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      pa[u] = ia[u] != 0xFFFFFFFFu ? x[ia[u]] : make_float4(0.f, 0.f, 0.f, 0.f);
+      pb[u] = ib[u] != 0xFFFFFFFFu ? x[ib[u]] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (ia[u] != 0xFFFFFFFFu) {
+        const f3 e0 = mk3(pa[u]) - p, e1 = mk3(pb[u]) - p;
+        acc = acc + cross3(e0, e1) / (dot3(e0, e0) * dot3(e1, e1));
+      }
   }
   const f3 r = normalize3(acc);
   n[i] = make_float4(r.x, r.y, r.z, 0.f);

@@ -10,36 +10,43 @@ __device__ __forceinline__ void collide_item(float4* delta, const float4* x, con
                                              const uint32_t* neighbors, const StepConst& k, uint32_t V, uint32_t id) {
   const float4 pi4 = x[id];
   const f3 pi = mk3(pi4);
-  const f3 vi = pi - mk3(x0[id]);
   const float wi = pi4.w;
   f3 acc = mk3(0, 0, 0);
   int count = 0;
-  for (int s = 0; s < k.max_neighbors; s++) {
-    const uint32_t j = neighbors[(size_t)s * V + id];
-    if (j > V) break;
+  f3 vi = mk3(0, 0, 0);
+  bool have_vi = false;
+  uint32_t j = neighbors[id];
+  for (int s = 0; s < k.max_neighbors && j <= V; s++) {
+    // next slot's index is fetched while this neighbour is processed
+    const uint32_t jn = s + 1 < k.max_neighbors ? neighbors[(size_t)(s + 1) * V + id] : 0xFFFFFFFFu;
     const float4 pj4 = x[j];
     const float denom = wi + pj4.w;
-    if (denom <= 0) continue;
     const f3 pj = mk3(pj4);
     const f3 diff = pi - pj;
-    const float dist = len3(diff);
-    if (dist >= k.particle_diameter) continue;
-    const f3 grad = diff / (dist + XRT_EPS);
-    const float lambda = (dist - k.particle_diameter) / denom;
-    const f3 common = lambda * grad;
-    count++;
-    acc = acc - wi * common;
-    const f3 rel = vi - (pj - mk3(x0[j]));
-    // ComputeFriction(common, rel)
-    const float cl = len3(common);
-    if (k.friction > 0.f && cl > 0.f) {
-      const f3 nrm = common / cl;
-      const f3 tan = rel - nrm * dot3(rel, nrm);
-      const float tl = len3(tan);
-      const float r = (cl * k.friction) / tl;
-      const f3 fr = -tan * (r < 1.0f ? r : 1.0f);
-      acc = acc + wi * fr;
+    const float dist = xf_len(diff);
+    if (denom > 0 && dist < k.particle_diameter) {
+      const f3 grad = diff * xf_rcp(dist + XRT_EPS);
+      const float lambda = xf_div(dist - k.particle_diameter, denom);
+      const f3 common = lambda * grad;
+      count++;
+      acc = acc - wi * common;
+      if (!have_vi) {
+        vi = pi - mk3(x0[id]);
+        have_vi = true;
+      }
+      const f3 rel = vi - (pj - mk3(x0[j]));
+      // ComputeFriction(common, rel)
+      const float cl = xf_len(common);
+      if (k.friction > 0.f && cl > 0.f) {
+        const f3 nrm = common * xf_rcp(cl);
+        const f3 tan = rel - nrm * xf_dot(rel, nrm);
+        const float tl = xf_len(tan);
+        const float r = xf_div(cl * k.friction, tl);
+        const f3 fr = -tan * (r < 1.0f ? r : 1.0f);
+        acc = acc + wi * fr;
+      }
     }
+    j = jn;
   }
   delta[id] = make_float4(acc.x, acc.y, acc.z, (float)count);
 }

@@ -71,6 +71,36 @@ struct PhaseClock {
   }
 };
 
+// first item of colour phase `ph` for this thread (stretch colours, then bend colours)
+struct ColorRec {
+  uint4 q;
+  float f, lambda;
+};
+__device__ __forceinline__ ColorRec fetch_color_rec(const PersistArgs& a, uint32_t ph, uint32_t n_sc, uint32_t n_ph,
+                                                    uint32_t tid, int it) {
+  ColorRec r;
+  r.q = make_uint4(0, 0, 0, 0);
+  r.f = 0.f;
+  r.lambda = 0.f;
+  if (ph < n_sc) {
+    const uint32_t i = a.s_off[ph] + tid;
+    if (i < a.s_off[ph + 1]) {
+      const uint2 ij = a.c.s_idx[i];
+      r.q.x = ij.x;
+      r.q.y = ij.y;
+      r.f = a.c.s_rest[i];
+      if (it != 0) r.lambda = a.c.s_lambda[i];
+    }
+  } else if (ph < n_ph) {
+    const uint32_t col = ph - n_sc, i = a.b_off[col] + tid;
+    if (i < a.b_off[col + 1]) {
+      r.q = a.c.b_idx[i];
+      r.f = a.c.b_theta[i];
+    }
+  }
+  return r;
+}
+
 template <bool MULTI>
 __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_constant__ PersistArgs a) {
   const uint32_t nth = (MULTI ? cluster_nctarank() : 1u) * PT;
@@ -81,6 +111,7 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
   const uint32_t V = c.V, E = c.E;
   const float alpha_s = k.stretch_compliance / (k.dt * k.dt);
   const float xpbd_b = k.bend_compliance / k.dt / k.dt;
+  __shared__ uint32_t hits[XRT_HIT_CAP * PT];  // staged leaf hits of the contact queries
   PhaseClock pc;
   pc.start(a.prof, tid);
 
@@ -113,39 +144,116 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
         phase_sync<MULTI>();
     pc.lap(4);
       }
-      for (uint32_t i = tid; i < V; i += nth)
-        gen_vertex_item<false>(a.bvh.tnodes, a.bvh.pred, c.x0, c.x, c.vf, c.rt, c.cnt_vf, c.cnt_rt, i);
-      for (uint32_t i = tid; i < E; i += nth)
-        gen_edge_item<false>(a.bvh.tnodes, a.bvh.pred, o.rtri, c.x, c.edge, c.ee, c.cnt_ee, i);
-      phase_sync<MULTI>();
-    pc.lap(5);
-    }
-    for (uint32_t col = 0; col < c.n_sc; col++) {
-      const uint32_t end = a.s_off[col + 1];
-      for (uint32_t i = a.s_off[col] + tid; i < end; i += nth)
-        stretch_one(c.x, c.s_idx, c.s_rest, c.s_lambda, i, alpha_s, it, a.atomic_s != 0);
-      phase_sync<MULTI>();
-    pc.lap(6);
-    }
-    if (a.solve_bending)
-      for (uint32_t col = 0; col < c.n_bc; col++) {
-        const uint32_t end = a.b_off[col + 1];
-        for (uint32_t i = a.b_off[col] + tid; i < end; i += nth)
-          bend_one(c.x, c.b_idx, c.b_theta, i, xpbd_b, a.atomic_b != 0);
+      // Compacted generation (the reference traverses from every vertex and edge).
+      // Stage 1: test every item against the root box only; items that miss get
+      // their "no contact" result at once, the others are appended to a compact
+      // list (one atomic per warp).  Stage 2: full traversal + narrow phase over the
+      // list, so warps are dense and the load is even whatever the mesh order.
+      {
+        const NodeView root = load_node<false>(a.bvh.tnodes, 0);
+        const uint32_t lane = threadIdx.x & 31u;
+        uint32_t* list_v = a.gen_list;
+        uint32_t* list_e = a.gen_list + V;
+        for (uint32_t i = tid; (i & ~31u) < V; i += nth) {
+          bool act = false;
+          if (i < V) {
+            const f3 p = mk3(c.x[i]), p1 = mk3(c.x0[i]);
+            act = overlap_point(root.b, p) || (!(len3(p - p1) < XRT_EPS) && overlap_segment(root.b, p1, p));
+            if (!act) {
+              c.vf[i] = VFContact{-1, {0.f, 0.f, 0.f}};
+              c.rt[i] = VFContact{-1, {0.f, 0.f, 0.f}};
+            }
+          }
+          const uint32_t m = __ballot_sync(0xFFFFFFFFu, act);
+          uint32_t base = 0;
+          if (lane == 0) {
+            if (i < V) c.v_active[i >> 5] = 0u;
+            if (m) base = atomicAdd(a.gen_count, (uint32_t)__popc(m));
+          }
+          base = __shfl_sync(0xFFFFFFFFu, base, 0);
+          if (act) list_v[base + __popc(m & ((1u << lane) - 1u))] = i;
+        }
+        for (uint32_t i = tid; (i & ~31u) < E; i += nth) {
+          bool act = false;
+          if (i < E) {
+            const uint2 e = c.edge[i];
+            act = overlap_segment(root.b, mk3(c.x[e.x]), mk3(c.x[e.y]));
+          }
+          const uint32_t m = __ballot_sync(0xFFFFFFFFu, act);
+          uint32_t base = 0;
+          if (lane == 0) {
+            if (i < E) c.e_active[i >> 5] = 0u;
+            if (m) base = atomicAdd(a.gen_count + 1, (uint32_t)__popc(m));
+          }
+          base = __shfl_sync(0xFFFFFFFFu, base, 0);
+          if (act) list_e[base + __popc(m & ((1u << lane) - 1u))] = i;
+        }
         phase_sync<MULTI>();
-    pc.lap(7);
+        pc.lap(13);
+        const uint32_t nv = a.gen_count[0], ne = a.gen_count[1];
+        if (pc.acc) { pc.acc[16] += nv; pc.acc[17] += ne; pc.acc[18] += 1; }
+        for (uint32_t k2 = tid; k2 < nv; k2 += nth) {
+          const uint32_t i = list_v[k2];
+          if (gen_vertex_item<false, PT>(a.bvh.tnodes, a.bvh.pred, c.x0, c.x, c.vf, c.rt, nullptr, nullptr,
+                                         hits + threadIdx.x, i))
+            atomicOr(c.v_active + (i >> 5), 1u << (i & 31u));
+        }
+        pc.lap(14);
+        for (uint32_t k2 = tid; k2 < ne; k2 += nth) {
+          const uint32_t i = list_e[k2];
+          if (gen_edge_item<false, PT>(a.bvh.tnodes, a.bvh.pred, o.rtri, c.x, c.edge, c.ee, nullptr, hits + threadIdx.x, i))
+            atomicOr(c.e_active + (i >> 5), 1u << (i & 31u));
+        }
+        phase_sync<MULTI>();
+        // every thread has read the counts; clear them for the next pass (next use is barriers away)
+        if (tid == 0) {
+          a.gen_count[0] = 0u;
+          a.gen_count[1] = 0u;
+        }
       }
+      pc.lap(5);
+    }
+    // Colour phases of stretch then bend.  The record of this thread's first
+    // item of the NEXT phase is static data, so it is fetched before the barrier
+    // and its latency overlaps the store drain + barrier.
+    {
+      const uint32_t n_sc = c.n_sc, n_ph = c.n_sc + (a.solve_bending ? c.n_bc : 0u);
+      ColorRec cur = fetch_color_rec(a, 0, n_sc, n_ph, tid, it);
+      for (uint32_t ph = 0; ph < n_ph; ph++) {
+        if (ph < n_sc) {
+          const uint32_t end = a.s_off[ph + 1];
+          uint32_t i = a.s_off[ph] + tid;
+          if (i < end) {
+            stretch_rec(c.x, c.s_lambda, i, make_uint2(cur.q.x, cur.q.y), cur.f, cur.lambda, alpha_s, a.atomic_s != 0);
+            for (i += nth; i < end; i += nth)
+              stretch_one(c.x, c.s_idx, c.s_rest, c.s_lambda, i, alpha_s, it, a.atomic_s != 0);
+          }
+        } else {
+          const uint32_t col = ph - n_sc, end = a.b_off[col + 1];
+          uint32_t i = a.b_off[col] + tid;
+          if (i < end) {
+            bend_rec(c.x, cur.q, cur.f, xpbd_b, a.atomic_b != 0);
+            for (i += nth; i < end; i += nth) bend_one(c.x, c.b_idx, c.b_theta, i, xpbd_b, a.atomic_b != 0);
+          }
+        }
+        cur = fetch_color_rec(a, ph + 1, n_sc, n_ph, tid, it);
+        phase_sync<MULTI>();
+        pc.lap(ph < n_sc ? 6 : 7);
+      }
+    }
     if (a.lra && c.n_lra) {
       for (uint32_t i = tid; i < c.n_lra; i += nth) lra_item(c.x, c.l_src, c.l_tgt, c.l_rest, k.lra_stretchiness, i);
       phase_sync<MULTI>();
     pc.lap(8);
     }
     if (o.F) {
-      for (uint32_t i = tid; i < V; i += nth) solve_vertex_item(a.bvh.pred, c.x, c.vf, c.rt, i);
+      for (uint32_t i = tid; i < V; i += nth)
+        if (load_active_bit(c.v_active, i)) solve_vertex_item(a.bvh.pred, c.x, c.vf, c.rt, i);
       phase_sync<MULTI>();
     pc.lap(9);
       if (E) {
-        for (uint32_t i = tid; i < E; i += nth) solve_edge_item(c.x, c.edge, c.ee, c.delta, i);
+        for (uint32_t i = tid; i < E; i += nth)
+          if (load_active_bit(c.e_active, i)) solve_edge_item(c.x, c.edge, c.ee, c.delta, i);
         phase_sync<MULTI>();
     pc.lap(10);
       }

@@ -33,7 +33,9 @@ struct ClothDev {
   // contacts
   VFContact* vf = nullptr;  // [V]
   VFContact* rt = nullptr;  // [V]
-  EEContact* ee = nullptr;  // [E]
+  EEContact* ee = nullptr;  // [E]  (record valid only where the e_active bit is set)
+  uint32_t* v_active = nullptr;  // [ceil(V/32)] bit i: vertex i has a VF or RT contact
+  uint32_t* e_active = nullptr;  // [ceil(E/32)] bit i: edge i has an EE contact
   // spatial hash (SpatialHashGPU members)
   uint32_t *p_hash = nullptr, *p_index = nullptr, *p_hash_b = nullptr, *p_index_b = nullptr;
   uint32_t *cell_start = nullptr, *cell_end = nullptr, *neighbors = nullptr;
@@ -78,7 +80,8 @@ void launch_normals(const float4* x, float4* n, const uint32_t* tri, const uint3
                     const uint32_t* vf_idx, uint32_t V, cudaStream_t st);
 void launch_interpolate(const ObstacleDev& o, int step, int num_steps, cudaStream_t st);
 // ---- contacts (xrt_contact.cu) ----
-void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, cudaStream_t st);
+// counts: also record the per-query leaf-hit counts (debug getters); the frame path passes false
+void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, bool counts, cudaStream_t st);
 void launch_solve_contacts(const ClothDev& c, const DevBVH& bvh, const StepConst& k, cudaStream_t st);
 void launch_candidates(const ClothDev& c, const DevBVH& bvh, int kind, const uint32_t* offsets,
                        uint32_t* items, uint32_t* counts, cudaStream_t st);
