@@ -21,10 +21,6 @@ for cl in [int(a) for a in sys.argv[2:]] or [8, 16]:
         s.UpdateObstacleAnimationFrame(scene.sphere_motion(sc.obs_pos, f + 1)); ms.append(s.SimulateSwift())
     p = (s.debug("PERSIST_PROF", np.uint64) - p0).astype(np.float64) / frames / 1e3
     print(f"cluster {cl}: frame {np.median(ms):.3f} ms; per-phase-kind us/frame (sum {p[:13].sum():.0f}):")
-    raw = (s.debug("PERSIST_PROF", np.uint64) - p0).astype(np.float64)
-    if raw[18] > 0:
-        print(f"   generate: stage1 {p[13]:.1f} us/frame, stage2 vertex (thread 0 only) {p[14]:.1f}; root-pass per pass: "
-              f"{raw[16]/raw[18]:.0f} verts, {raw[17]/raw[18]:.0f} edges")
     for nm, v in zip(NAMES, p[:13]):
         print(f"   {nm:16s} {v:9.1f}")
     s.close()

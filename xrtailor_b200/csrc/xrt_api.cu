@@ -46,7 +46,6 @@ struct xrt_solver {
   size_t seq_frames = 0, seq_cursor = 0;
   cudaEvent_t ev_join = nullptr;
   int cluster = 0;  // resolved persist_cluster (0: per-stage launches)
-  uint32_t *d_gen_list = nullptr, *d_gen_count = nullptr;  // compaction scratch of the persistent kernel
   unsigned long long* d_prof = nullptr;  // [16] per-phase-kind ns of the persistent kernel (XRT_PERSIST_PROF=1)
 };
 
@@ -477,11 +476,6 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
     if (cl < 0 || cl > mx) cl = mx;
     XRT_REQUIRE(cl == 0 || (cl & (cl - 1)) == 0, "persist_cluster must be 0, -1 or a power of two up to 16");
     s->cluster = cl;
-    if (cl > 0) {
-      XRT_CUDA_OK(dev_alloc(&s->d_gen_list, (size_t)c.V + c.E));
-      XRT_CUDA_OK(dev_alloc(&s->d_gen_count, 2));
-      XRT_CUDA_OK(cudaMemset(s->d_gen_count, 0, 2 * sizeof(uint32_t)));
-    }
     const char* pe = getenv("XRT_PERSIST_PROF");
     if (cl > 0 && pe && pe[0] == '1') {
       XRT_CUDA_OK(dev_alloc(&s->d_prof, 32));
@@ -565,8 +559,6 @@ static PersistArgs make_persist_args(const xrt_solver* s, int substep, bool move
   a.lra = p.geodesic_lra; a.moved = moved ? 1 : 0;
   a.atomic_s = s->atomic_s ? 1 : 0; a.atomic_b = s->atomic_b ? 1 : 0;
   a.prof = s->d_prof;
-  a.gen_list = s->d_gen_list;
-  a.gen_count = s->d_gen_count;
   return a;
 }
 
@@ -748,6 +740,22 @@ extern "C" int xrt_batch_run(xrt_solver** handles, int n, int frames, float* ms)
   XRT_CUDA_OK(cudaStreamSynchronize(s->st));
   if (ms) XRT_CUDA_OK(cudaEventElapsedTime(ms, s->ev0, s->ev1));
   return XRT_OK;
+}
+
+// boxes in the reference's node numbering (BVH::AABBsHost) from the sibling-pair slots
+static cudaError_t download_aabbs(const DevBVH& b, size_t F, float* o) {
+  if (!F) return cudaSuccess;
+  std::vector<TNode> t(2 * F);
+  std::vector<BVNode> nd(2 * F - 1);
+  cudaError_t e = cudaMemcpy(t.data(), b.tnodes, t.size() * sizeof(TNode), cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(nd.data(), b.nodes, nd.size() * sizeof(BVNode), cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) return e;
+  for (size_t i = 0; i < nd.size(); i++) {
+    const TNode& n = t[tnode_slot(nd.data(), (uint32_t)i)];
+    o[6 * i] = n.lx; o[6 * i + 1] = n.ly; o[6 * i + 2] = n.lz;
+    o[6 * i + 3] = n.ux; o[6 * i + 4] = n.uy; o[6 * i + 5] = n.uz;
+  }
+  return cudaSuccess;
 }
 
 static double frame_bytes(const xrt_solver* s, bool moved);
@@ -1054,16 +1062,7 @@ extern "C" int xrt_debug_get(xrt_solver* s, int what, void* dst, size_t* bytes) 
     }
     case XRT_DBG_COLORS_STRETCH: memcpy(dst, s->s_color.data(), need); break;
     case XRT_DBG_COLORS_BEND: memcpy(dst, s->b_color.data(), need); break;
-    case XRT_DBG_AABBS: {
-      std::vector<TNode> t(2 * F - 1);
-      XRT_CUDA_OK(cudaMemcpy(t.data(), s->bvh.tnodes, t.size() * sizeof(TNode), cudaMemcpyDeviceToHost));
-      float* o = (float*)dst;
-      for (size_t i = 0; i < t.size(); i++) {
-        o[6 * i] = t[i].lx; o[6 * i + 1] = t[i].ly; o[6 * i + 2] = t[i].lz;
-        o[6 * i + 3] = t[i].ux; o[6 * i + 4] = t[i].uy; o[6 * i + 5] = t[i].uz;
-      }
-      break;
-    }
+    case XRT_DBG_AABBS: XRT_CUDA_OK(download_aabbs(s->bvh, F, (float*)dst)); break;
     case XRT_DBG_PREDICTED: return download_xyz(s, s->c.x, V, (float*)dst);
     case XRT_DBG_VELOCITY: return download_xyz(s, s->c.v, V, (float*)dst);
     case XRT_DBG_OBSTACLE_PRED: {
@@ -1167,7 +1166,7 @@ extern "C" void xrt_destroy(xrt_solver* s) {
   ClothDev& c = s->c;
   void* ptrs[] = {c.x0, c.x, c.v, c.n, c.rest, c.tri, c.edge, c.vf_off, c.vf_idx, c.s_idx, c.s_rest, c.s_lambda,
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
-                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof, s->d_gen_list, s->d_gen_count,
+                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof,
                   c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
                   s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq};
   for (void* p : ptrs) cudaFree(p);
@@ -1220,14 +1219,7 @@ extern "C" int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts
     if (nodes) cudaMemcpy(nodes, b.nodes, (2 * F - 1) * sizeof(BVNode), cudaMemcpyDeviceToHost);
     if (esc_int && F > 1) cudaMemcpy(esc_int, b.esc_int, (F - 1) * 4, cudaMemcpyDeviceToHost);
     if (esc_ext) cudaMemcpy(esc_ext, b.esc_ext, F * 4, cudaMemcpyDeviceToHost);
-    if (aabbs) {
-      std::vector<TNode> t(2 * F - 1);
-      cudaMemcpy(t.data(), b.tnodes, t.size() * sizeof(TNode), cudaMemcpyDeviceToHost);
-      for (size_t i = 0; i < t.size(); i++) {
-        aabbs[6 * i] = t[i].lx; aabbs[6 * i + 1] = t[i].ly; aabbs[6 * i + 2] = t[i].lz;
-        aabbs[6 * i + 3] = t[i].ux; aabbs[6 * i + 4] = t[i].uy; aabbs[6 * i + 5] = t[i].uz;
-      }
-    }
+    if (aabbs && download_aabbs(b, F, aabbs) != cudaSuccess) rc = XRT_ERR_CUDA;
     if (cudaGetLastError() != cudaSuccess) rc = XRT_ERR_CUDA;
   }
   cudaFree(dx);

@@ -168,7 +168,7 @@ __global__ void build_boxes_kernel(TNode* tn, const BVNode* __restrict__ nodes,
   if (i >= F) return;
   const float* b = leaf_box + 6 * (size_t)obj[i];
   float lo[3] = {b[0], b[1], b[2]}, hi[3] = {b[3], b[4], b[5]};
-  tnode_store_box(tn + F - 1 + i, lo, hi);
+  tnode_store_box(tn + tnode_slot(nodes, F - 1 + i), lo, hi);
   walk_up<false>(tn, nodes, flags, F - 1 + i);
 }
 
@@ -188,17 +188,18 @@ __global__ void link_kernel(TNode* tn, const BVNode* __restrict__ nodes, const i
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   const int n = (int)F;
   if (i >= 2 * F - 1) return;
+  TNode* me = tn + tnode_slot(nodes, i);
   if (i < F - 1) {
     int e = escape_after(ranges[i].y, ranges, n);
     esc_int[i] = e;
-    tn[i].link_hit = (int)nodes[i].left;
-    tn[i].link_miss = e;
+    me->link_hit = (int)tnode_child_slot(i, false);
+    me->link_miss = e < 0 ? -1 : (int)tnode_slot(nodes, (uint32_t)e);
   } else {
     int leaf = (int)(i - (F - 1));
     int e = escape_after(leaf, ranges, n);
     esc_ext[leaf] = e;
-    tn[i].link_hit = ~(int)nodes[i].object;
-    tn[i].link_miss = e;
+    me->link_hit = ~(int)nodes[i].object;
+    me->link_miss = e < 0 ? -1 : (int)tnode_slot(nodes, (uint32_t)e);
   }
 }
 
@@ -220,7 +221,7 @@ int bvh_alloc(DevBVH* b, BvhWork* w, uint32_t F) {
   auto A = [&](void** p, size_t bytes) {
     if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16);
   };
-  A((void**)&b->tnodes, nn * sizeof(TNode));
+  A((void**)&b->tnodes, (nn + 1) * sizeof(TNode));  // 2F sibling-pair slots
   A((void**)&b->nodes, nn * sizeof(BVNode));
   A((void**)&b->esc_int, F * sizeof(int32_t));
   A((void**)&b->esc_ext, F * sizeof(int32_t));

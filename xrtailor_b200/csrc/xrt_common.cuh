@@ -86,6 +86,19 @@ struct BVNode {  // broad_phase/lbvh/BVH.cuh:27-32
   uint32_t parent, left, right, object;
 };
 
+// Where node c lives in the traversal array: the root at slot 0, the two
+// children of internal node p at slots 2p+2 and 2p+3 (slot 1 unused, 2F slots).
+// Siblings are one aligned 64-byte pair, so the load of a left child brings its
+// right sibling -- which the stackless traversal always visits next after the
+// left subtree -- into the same L1 line.  links in TNode are slots.
+__host__ __device__ __forceinline__ uint32_t tnode_child_slot(uint32_t parent, bool right) {
+  return 2u + 2u * parent + (right ? 1u : 0u);
+}
+__host__ __device__ __forceinline__ uint32_t tnode_slot(const BVNode* nodes, uint32_t c) {
+  const uint32_t p = nodes[c].parent;
+  return p == 0xFFFFFFFFu ? 0u : tnode_child_slot(p, nodes[p].right == c);
+}
+
 struct VFContact {  // pbd_collision/Contact.cuh VFContact / RTContact
   int32_t index;
   float q[3];
@@ -99,7 +112,7 @@ struct EEContact {  // pbd_collision/Contact.cuh EEContact (48 bytes)
 
 struct DevBVH {
   uint32_t n_obj;       // F
-  TNode* tnodes;        // [2F-1]
+  TNode* tnodes;        // [2F] traversal nodes in sibling-pair slots (tnode_slot)
   BVNode* nodes;        // [2F-1]
   float* aabbs;         // [6*(2F-1)]
   int32_t* esc_int;     // [F-1]

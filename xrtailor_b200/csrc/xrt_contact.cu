@@ -10,9 +10,8 @@ __global__ void generate_vertex_contacts_kernel(const TNode* __restrict__ t, con
                                                 uint32_t* __restrict__ cnt_vf, uint32_t* __restrict__ cnt_rt,
                                                 uint32_t* __restrict__ active, uint32_t V) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  __shared__ uint32_t hits[XRT_HIT_CAP * XRT_BLOCK];
   bool live = false;
-  if (i < V) live = gen_vertex_item<true, XRT_BLOCK>(t, pred, x0, x, vf, rt, cnt_vf, cnt_rt, hits + threadIdx.x, i);
+  if (i < V) live = gen_vertex_item<true>(t, pred, x0, x, vf, rt, cnt_vf, cnt_rt, i);
   store_active_bits(active, i, V, live);
 }
 __global__ void generate_edge_contacts_kernel(const TNode* __restrict__ t, const float4* __restrict__ pred,
@@ -21,9 +20,8 @@ __global__ void generate_edge_contacts_kernel(const TNode* __restrict__ t, const
                                               uint32_t* __restrict__ cnt_ee, uint32_t* __restrict__ active,
                                               uint32_t E) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  __shared__ uint32_t hits[XRT_HIT_CAP * XRT_BLOCK];
   bool live = false;
-  if (i < E) live = gen_edge_item<true, XRT_BLOCK>(t, pred, rtri, x, edge, ee, cnt_ee, hits + threadIdx.x, i);
+  if (i < E) live = gen_edge_item<true>(t, pred, rtri, x, edge, ee, cnt_ee, i);
   store_active_bits(active, i, E, live);
 }
 __global__ void solve_vertex_contacts_kernel(const float4* __restrict__ pred, float4* __restrict__ x,

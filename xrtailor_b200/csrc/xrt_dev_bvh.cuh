@@ -32,15 +32,17 @@ __device__ __forceinline__ void walk_up(TNode* tn, const BVNode* nodes, int* fla
     const int old = atomicAdd(flags + parent, 1);
     if (PARITY ? ((old & 1) == 0) : (old == 0)) return;
     float la[3], ha[3], lb[3], hb[3];
-    tnode_load_box(tn + nodes[parent].left, la, ha);
-    tnode_load_box(tn + nodes[parent].right, lb, hb);
+    tnode_load_box(tn + tnode_child_slot(parent, false), la, ha);
+    tnode_load_box(tn + tnode_child_slot(parent, true), lb, hb);
 #pragma unroll
     for (int k = 0; k < 3; k++) {
       la[k] = fminf(la[k], lb[k]);
       ha[k] = fmaxf(ha[k], hb[k]);
     }
-    tnode_store_box(tn + parent, la, ha);
-    parent = nodes[parent].parent;
+    const uint32_t gp = nodes[parent].parent;
+    const uint32_t slot = gp == 0xFFFFFFFFu ? 0u : tnode_child_slot(gp, nodes[gp].right == parent);
+    tnode_store_box(tn + slot, la, ha);
+    parent = gp;
   }
 }
 
@@ -53,8 +55,9 @@ __device__ __forceinline__ void refit_item(TNode* tn, const BVNode* nodes, float
                                            uint32_t F, uint32_t i) {
   const uint32_t node = F - 1 + i;
   const uint32_t o = nodes[node].object;
+  TNode* leaf = tn + tnode_slot(nodes, node);
   float lo[3], hi[3];
-  tnode_load_box(tn + node, lo, hi);
+  tnode_load_box(leaf, lo, hi);
 #pragma unroll
   for (int k = 0; k < 3; k++) {
     const uint32_t v = tri[3 * o + k];
@@ -64,7 +67,7 @@ __device__ __forceinline__ void refit_item(TNode* tn, const BVNode* nodes, float
     lo[0] = fminf(lo[0], q.x); lo[1] = fminf(lo[1], q.y); lo[2] = fminf(lo[2], q.z);
     hi[0] = fmaxf(hi[0], q.x); hi[1] = fmaxf(hi[1], q.y); hi[2] = fmaxf(hi[2], q.z);
   }
-  tnode_store_box(tn + node, lo, hi);
+  tnode_store_box(leaf, lo, hi);
   walk_up<PARITY>(tn, nodes, flags, node);
 }
 

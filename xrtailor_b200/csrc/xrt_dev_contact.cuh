@@ -67,6 +67,28 @@ __device__ __forceinline__ bool overlap_segment(const Box& b, f3 p1, f3 p2) {
          (get_isect(p1.z - b.uz, p2.z - b.uz, p1, p2, h) && in_box(h, b, 3));
 }
 
+// The same test with the segment's own min/max corners precomputed once per
+// query: "both endpoints below lo" is "the larger endpoint below lo", so the six
+// slab rejections cost six compares per node instead of twelve.
+struct SegQuery {
+  f3 p1, p2, lo, hi;
+  __device__ __forceinline__ SegQuery(f3 a, f3 b) : p1(a), p2(b) {
+    lo = mk3(fminf(a.x, b.x), fminf(a.y, b.y), fminf(a.z, b.z));
+    hi = mk3(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z));
+  }
+  __device__ __forceinline__ bool overlaps(const Box& b) const {
+    if (hi.x < b.lx || lo.x > b.ux || hi.y < b.ly || lo.y > b.uy || hi.z < b.lz || lo.z > b.uz) return false;
+    if (overlap_point(b, p1)) return true;
+    f3 h;
+    return (get_isect(p1.x - b.lx, p2.x - b.lx, p1, p2, h) && in_box(h, b, 1)) ||
+           (get_isect(p1.y - b.ly, p2.y - b.ly, p1, p2, h) && in_box(h, b, 2)) ||
+           (get_isect(p1.z - b.lz, p2.z - b.lz, p1, p2, h) && in_box(h, b, 3)) ||
+           (get_isect(p1.x - b.ux, p2.x - b.ux, p1, p2, h) && in_box(h, b, 1)) ||
+           (get_isect(p1.y - b.uy, p2.y - b.uy, p1, p2, h) && in_box(h, b, 2)) ||
+           (get_isect(p1.z - b.uz, p2.z - b.uz, p1, p2, h) && in_box(h, b, 3));
+  }
+};
+
 // QueryDeviceStackless (BVH.cu:957-1055) with the leaf visitor inlined.
 // Returns the number of leaf hits (capped at XRT_MAX_HITS like the reference).
 template <bool NC, class Pred, class Visit>
@@ -182,55 +204,34 @@ __device__ __forceinline__ float closest_seg_seg(f3 p1, f3 q1, f3 p2, f3 q2, flo
   return len3(c1 - c2);
 }
 
-// Leaf hits are staged in a small per-thread shared-memory buffer and the
-// narrow phase runs over the buffer after the traversal (or when it fills), so
-// the lanes of a warp execute the expensive primitive tests together instead of
-// one lane at a time as each reaches a leaf.  Hits are consumed in traversal
-// order, so "first minimum wins" is unchanged.  hb = this thread's slot 0;
-// consecutive slots are BS words apart (bank-conflict free).
-#define XRT_HIT_CAP 8
-template <int BS, class Narrow>
-struct HitStage {
-  uint32_t* hb;
-  int n;
-  Narrow& narrow;
-  __device__ __forceinline__ HitStage(uint32_t* b, Narrow& f) : hb(b), n(0), narrow(f) {}
-  __device__ __forceinline__ void flush() {
-    for (int h = 0; h < n; h++) narrow(hb[h * BS]);
-    n = 0;
-  }
-  __device__ __forceinline__ void push(uint32_t o) {
-    hb[n * BS] = o;
-    if (++n == XRT_HIT_CAP) flush();
-  }
-};
-
 // GenerateVF_DCD_Kernel + GenerateVFCCD_Kernel (PBDCollision.cu:17-47,236-268):
-// both per-vertex queries for one vertex (x and x0 are loaded once).
+// both per-vertex queries for one vertex (x and x0 are loaded once).  Each leaf
+// hit goes through its primitive test as the traversal reaches it.  (Measured
+// alternatives that lost on B200, see DESIGN.md section 6: staging hits in shared
+// memory and testing them after the traversal; two traversals per thread in lock
+// step; compacting the items that pass the root box into a dense list.)
 // Returns whether the vertex has any contact (either query).
-template <bool NC, int BS>
+template <bool NC>
 __device__ __forceinline__ bool gen_vertex_item(const TNode* t, const float4* pred, const float4* x0, const float4* x,
                                                 VFContact* vf, VFContact* rt, uint32_t* cnt_vf, uint32_t* cnt_rt,
-                                                uint32_t* hb, uint32_t i) {
+                                                uint32_t i) {
   const f3 p = mk3(x[i]);
   bool live_vf;
   {
     float best = XRT_SCALAR_MAX;
     int best_idx = -1;
     f3 best_q = mk3(0, 0, 0);
-    auto narrow = [&](uint32_t o) {
-      f3 qs;
-      const float d = nearest_point(p, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]), qs);
-      if (d < best) {
-        best = d;
-        best_q = qs;
-        best_idx = (int)o;
-      }
-    };
-    HitStage<BS, decltype(narrow)> st(hb, narrow);
     const uint32_t nf = traverse<NC>(
-        t, [&](const Box& b) { return overlap_point(b, p); }, [&](uint32_t o) { st.push(o); });
-    st.flush();
+        t, [&](const Box& b) { return overlap_point(b, p); },
+        [&](uint32_t o) {
+          f3 qs;
+          const float d = nearest_point(p, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]), qs);
+          if (d < best) {
+            best = d;
+            best_q = qs;
+            best_idx = (int)o;
+          }
+        });
     vf[i] = VFContact{best_idx, {best_q.x, best_q.y, best_q.z}};
     live_vf = best_idx != -1;
     if (cnt_vf) cnt_vf[i] = nf;
@@ -244,18 +245,17 @@ __device__ __forceinline__ bool gen_vertex_item(const TNode* t, const float4* pr
     if (!(length < XRT_EPS)) {
       d = d / length;
       float best = XRT_SCALAR_MAX;
-      auto narrow = [&](uint32_t o) {
-        const float dist = ray_intersect(p1, d, length, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]));
-        if (dist < best) {
-          const f3 qc = p1 + dist * d;
-          out = VFContact{(int)o, {qc.x, qc.y, qc.z}};
-          best = dist;
-        }
-      };
-      HitStage<BS, decltype(narrow)> st(hb, narrow);
+      const SegQuery seg(p1, p);
       nf = traverse<NC>(
-          t, [&](const Box& b) { return overlap_segment(b, p1, p); }, [&](uint32_t o) { st.push(o); });
-      st.flush();
+          t, [&](const Box& b) { return seg.overlaps(b); },
+          [&](uint32_t o) {
+            const float dist = ray_intersect(p1, d, length, mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2]));
+            if (dist < best) {
+              const f3 qc = p1 + dist * d;
+              out = VFContact{(int)o, {qc.x, qc.y, qc.z}};
+              best = dist;
+            }
+          });
     }
     rt[i] = out;
     if (cnt_rt) cnt_rt[i] = nf;
@@ -263,51 +263,49 @@ __device__ __forceinline__ bool gen_vertex_item(const TNode* t, const float4* pr
   }
 }
 
-// GenerateEE_DCD_Kernel, PBDCollision.cu:100-153
-// Returns whether a contact was found; only then is ee[i] written (the active
-// bit, not the record, says "no contact").
-template <bool NC, int BS>
+// GenerateEE_DCD_Kernel, PBDCollision.cu:100-153.  Returns whether a contact was
+// found; only then is ee[i] written (the active bit, not the record, says "none").
+template <bool NC>
 __device__ __forceinline__ bool gen_edge_item(const TNode* t, const float4* pred, const uint32_t* rtri,
                                               const float4* x, const uint2* edge, EEContact* ee, uint32_t* cnt_ee,
-                                              uint32_t* hb, uint32_t i) {
+                                              uint32_t i) {
   const uint2 e = edge[i];
   const f3 pc = mk3(x[e.x]), qc = mk3(x[e.y]);
   float s = 0.f, tt = 0.f, min_dist = XRT_SCALAR_MAX;
-  f3 p2 = mk3(0, 0, 0), q2 = mk3(0, 0, 0);
-  uint32_t best_o = 0xFFFFFFFFu;
-  auto narrow = [&](uint32_t o) {
-    const uint32_t info = rtri[o] >> 3;  // RTriEdge bits
-    if (!info) return;
-    const f3 ov[3] = {mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2])};
+  uint32_t best_ok = 0xFFFFFFFFu;  // (face << 2) | edge k of the current minimum
+  const SegQuery seg(pc, qc);
+  const uint32_t nf = traverse<NC>(
+      t, [&](const Box& b) { return seg.overlaps(b); },
+      [&](uint32_t o) {
+        const uint32_t info = rtri[o] >> 3;  // RTriEdge bits
+        if (!info) return;
+        const f3 ov[3] = {mk3(pred[3 * o]), mk3(pred[3 * o + 1]), mk3(pred[3 * o + 2])};
 #pragma unroll
-    for (uint32_t k = 0; k < 3; k++) {
-      if ((info >> k) & 1u) {
-        float _s, _t;
-        f3 c1, c2;
-        const uint32_t j = (k + 1u) % 3u;
-        // the reference tests the returned distance as a bool: non-zero distance only
-        if (closest_seg_seg(pc, qc, ov[k], ov[j], _s, _t, c1, c2) != 0.f) {
-          const float dist = len3(c1 - c2);
-          if (dist < min_dist) {
-            min_dist = dist;
-            p2 = ov[k];
-            q2 = ov[j];
-            s = _s;
-            tt = _t;
-            best_o = o;
+        for (uint32_t k = 0; k < 3; k++) {
+          if ((info >> k) & 1u) {
+            float _s, _t;
+            f3 c1, c2;
+            const uint32_t j = (k + 1u) % 3u;
+            // the reference tests the returned distance as a bool: non-zero distance only
+            if (closest_seg_seg(pc, qc, ov[k], ov[j], _s, _t, c1, c2) != 0.f) {
+              const float dist = len3(c1 - c2);
+              if (dist < min_dist) {
+                min_dist = dist;
+                s = _s;
+                tt = _t;
+                best_ok = (o << 2) | k;
+              }
+            }
           }
         }
-      }
-    }
-  };
-  HitStage<BS, decltype(narrow)> st(hb, narrow);
-  const uint32_t nf = traverse<NC>(
-      t, [&](const Box& b) { return overlap_segment(b, pc, qc); }, [&](uint32_t o) { st.push(o); });
-  st.flush();
+      });
   if (cnt_ee) cnt_ee[i] = nf;
   if (!(min_dist < 1e6f)) return false;
+  const uint32_t o = best_ok >> 2, k = best_ok & 3u, j = (k + 1u) % 3u;
+  const float4 a0 = pred[3 * o], a1 = pred[3 * o + 1], a2 = pred[3 * o + 2];
   // the winning face's normal, once (the reference recomputes it on every improvement)
-  const f3 fn = face_normal(mk3(pred[3 * best_o]), mk3(pred[3 * best_o + 1]), mk3(pred[3 * best_o + 2]));
+  const f3 fn = face_normal(mk3(a0), mk3(a1), mk3(a2));
+  const float4 p2 = k == 0 ? a0 : (k == 1 ? a1 : a2), q2 = j == 0 ? a0 : (j == 1 ? a1 : a2);
   EEContact c;
   c.dist = min_dist;
   c.p2[0] = p2.x; c.p2[1] = p2.y; c.p2[2] = p2.z;

@@ -111,7 +111,6 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
   const uint32_t V = c.V, E = c.E;
   const float alpha_s = k.stretch_compliance / (k.dt * k.dt);
   const float xpbd_b = k.bend_compliance / k.dt / k.dt;
-  __shared__ uint32_t hits[XRT_HIT_CAP * PT];  // staged leaf hits of the contact queries
   PhaseClock pc;
   pc.start(a.prof, tid);
 
@@ -144,73 +143,18 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
         phase_sync<MULTI>();
     pc.lap(4);
       }
-      // Compacted generation (the reference traverses from every vertex and edge).
-      // Stage 1: test every item against the root box only; items that miss get
-      // their "no contact" result at once, the others are appended to a compact
-      // list (one atomic per warp).  Stage 2: full traversal + narrow phase over the
-      // list, so warps are dense and the load is even whatever the mesh order.
-      {
-        const NodeView root = load_node<false>(a.bvh.tnodes, 0);
-        const uint32_t lane = threadIdx.x & 31u;
-        uint32_t* list_v = a.gen_list;
-        uint32_t* list_e = a.gen_list + V;
-        for (uint32_t i = tid; (i & ~31u) < V; i += nth) {
-          bool act = false;
-          if (i < V) {
-            const f3 p = mk3(c.x[i]), p1 = mk3(c.x0[i]);
-            act = overlap_point(root.b, p) || (!(len3(p - p1) < XRT_EPS) && overlap_segment(root.b, p1, p));
-            if (!act) {
-              c.vf[i] = VFContact{-1, {0.f, 0.f, 0.f}};
-              c.rt[i] = VFContact{-1, {0.f, 0.f, 0.f}};
-            }
-          }
-          const uint32_t m = __ballot_sync(0xFFFFFFFFu, act);
-          uint32_t base = 0;
-          if (lane == 0) {
-            if (i < V) c.v_active[i >> 5] = 0u;
-            if (m) base = atomicAdd(a.gen_count, (uint32_t)__popc(m));
-          }
-          base = __shfl_sync(0xFFFFFFFFu, base, 0);
-          if (act) list_v[base + __popc(m & ((1u << lane) - 1u))] = i;
-        }
-        for (uint32_t i = tid; (i & ~31u) < E; i += nth) {
-          bool act = false;
-          if (i < E) {
-            const uint2 e = c.edge[i];
-            act = overlap_segment(root.b, mk3(c.x[e.x]), mk3(c.x[e.y]));
-          }
-          const uint32_t m = __ballot_sync(0xFFFFFFFFu, act);
-          uint32_t base = 0;
-          if (lane == 0) {
-            if (i < E) c.e_active[i >> 5] = 0u;
-            if (m) base = atomicAdd(a.gen_count + 1, (uint32_t)__popc(m));
-          }
-          base = __shfl_sync(0xFFFFFFFFu, base, 0);
-          if (act) list_e[base + __popc(m & ((1u << lane) - 1u))] = i;
-        }
-        phase_sync<MULTI>();
-        pc.lap(13);
-        const uint32_t nv = a.gen_count[0], ne = a.gen_count[1];
-        if (pc.acc) { pc.acc[16] += nv; pc.acc[17] += ne; pc.acc[18] += 1; }
-        for (uint32_t k2 = tid; k2 < nv; k2 += nth) {
-          const uint32_t i = list_v[k2];
-          if (gen_vertex_item<false, PT>(a.bvh.tnodes, a.bvh.pred, c.x0, c.x, c.vf, c.rt, nullptr, nullptr,
-                                         hits + threadIdx.x, i))
-            atomicOr(c.v_active + (i >> 5), 1u << (i & 31u));
-        }
-        pc.lap(14);
-        for (uint32_t k2 = tid; k2 < ne; k2 += nth) {
-          const uint32_t i = list_e[k2];
-          if (gen_edge_item<false, PT>(a.bvh.tnodes, a.bvh.pred, o.rtri, c.x, c.edge, c.ee, nullptr, hits + threadIdx.x, i))
-            atomicOr(c.e_active + (i >> 5), 1u << (i & 31u));
-        }
-        phase_sync<MULTI>();
-        // every thread has read the counts; clear them for the next pass (next use is barriers away)
-        if (tid == 0) {
-          a.gen_count[0] = 0u;
-          a.gen_count[1] = 0u;
-        }
+      // 32-item groups stay warp-aligned so each warp ballots its own word of the active masks
+      for (uint32_t i = tid; (i & ~31u) < V; i += nth) {
+        const bool live =
+            i < V && gen_vertex_item<false>(a.bvh.tnodes, a.bvh.pred, c.x0, c.x, c.vf, c.rt, nullptr, nullptr, i);
+        store_active_bits(c.v_active, i, V, live);
       }
+      for (uint32_t i = tid; (i & ~31u) < E; i += nth) {
+        const bool live =
+            i < E && gen_edge_item<false>(a.bvh.tnodes, a.bvh.pred, o.rtri, c.x, c.edge, c.ee, nullptr, i);
+        store_active_bits(c.e_active, i, E, live);
+      }
+      phase_sync<MULTI>();
       pc.lap(5);
     }
     // Colour phases of stretch then bend.  The record of this thread's first

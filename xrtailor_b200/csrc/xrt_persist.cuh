@@ -18,8 +18,6 @@ struct PersistArgs {
   uint32_t frequency;     // collision pass every `frequency` (substep, iteration) steps
   int do_predict, do_finalize;
   int self_collision, solve_bending, lra, moved;
-  uint32_t* gen_list;   // [V + E] compacted ids of the items that pass the root box
-  uint32_t* gen_count;  // [2] list lengths (vertices, edges); zero between passes
   unsigned long long* prof;  // optional [16] per-phase-kind ns accumulators (XRT_PERSIST_PROF=1)
   int atomic_s, atomic_b;  // colouring not proper -> float atomics in the projection
 };
