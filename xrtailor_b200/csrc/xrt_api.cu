@@ -42,6 +42,10 @@ struct xrt_solver {
   float4* stage = nullptr;  // pinned host staging for obstacle targets / readback
   size_t stage_elems = 0;
   float4* d_stage = nullptr;
+  // per-frame transfers: raw float3 arrays through pinned memory, converted on the device
+  float *h_up = nullptr, *d_up = nullptr;  // [3 Vo] obstacle target upload
+  float *h_dn = nullptr, *d_dn = nullptr;  // [6 max(V, Vo)] positions + normals download
+  cudaEvent_t ev_up = nullptr;             // upload buffer free again
   float4* d_seq = nullptr;  // pre-staged obstacle animation [seq_frames][Vo]
   size_t seq_frames = 0, seq_cursor = 0;
   cudaEvent_t ev_join = nullptr;
@@ -486,6 +490,11 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
   XRT_CUDA_OK(cudaMallocHost((void**)&s->stage, stage * sizeof(float4)));
   XRT_CUDA_OK(dev_alloc(&s->d_stage, stage));
   s->stage_elems = stage;
+  XRT_CUDA_OK(cudaMallocHost((void**)&s->h_up, std::max<size_t>(o.V, 1) * 3 * sizeof(float)));
+  XRT_CUDA_OK(dev_alloc(&s->d_up, std::max<size_t>(o.V, 1) * 3));
+  XRT_CUDA_OK(cudaMallocHost((void**)&s->h_dn, stage * 6 * sizeof(float)));
+  XRT_CUDA_OK(dev_alloc(&s->d_dn, stage * 6));
+  XRT_CUDA_OK(cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming));
   // ClothSolverUniversal::Start: obstacle normals, BVH UpdateData(0, false) + Construct
   if (o.F) {
     launch_normals(o.x0, o.n, o.tri, o.vf_off, o.vf_idx, o.V, s->st);
@@ -642,10 +651,12 @@ static int ensure_graph(xrt_solver* s, int moved) {
 extern "C" int xrt_set_obstacle_target(xrt_solver* s, const float* xyz, size_t n_verts) {
   XRT_READY();
   XRT_REQUIRE(xyz && n_verts == s->o.V, "set_obstacle_target: vertex count differs from the obstacle");
-  XRT_CUDA_OK(cudaStreamSynchronize(s->st));  // staging buffer reuse
-  for (size_t i = 0; i < n_verts; i++)
-    s->stage[i] = make_float4(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2], s->o_invm[i]);
-  XRT_CUDA_OK(cudaMemcpyAsync(s->o.x, s->stage, n_verts * sizeof(float4), cudaMemcpyHostToDevice, s->st));
+  // no stream sync: only the previous upload must have left the pinned buffer
+  XRT_CUDA_OK(cudaEventSynchronize(s->ev_up));
+  memcpy(s->h_up, xyz, n_verts * 3 * sizeof(float));
+  XRT_CUDA_OK(cudaMemcpyAsync(s->d_up, s->h_up, n_verts * 3 * sizeof(float), cudaMemcpyHostToDevice, s->st));
+  XRT_CUDA_OK(cudaEventRecord(s->ev_up, s->st));
+  launch_unpack_xyz(s->d_up, s->o.x, (uint32_t)n_verts, s->st);  // keeps o.x.w = inverse mass
   s->target_pending = true;
   return XRT_OK;
 }
@@ -943,13 +954,17 @@ static int download_xyz(xrt_solver* s, const float4* d, size_t n, float* out) {
 extern "C" int xrt_get_positions(xrt_solver* s, int which, float* xyz, float* nrm) {
   XRT_READY();
   XRT_REQUIRE(which == 0 || which == 1, "get_positions: which must be 0 (cloth) or 1 (obstacle)");
-  int rc;
-  if (which == 0) {
-    if ((rc = download_xyz(s, s->c.x0, s->c.V, xyz))) return rc;
-    return download_xyz(s, s->c.n, s->c.V, nrm);
-  }
-  if ((rc = download_xyz(s, s->o.x0, s->o.V, xyz))) return rc;
-  return download_xyz(s, s->o.n, s->o.V, nrm);
+  const size_t n = which == 0 ? s->c.V : s->o.V;
+  if (!n || (!xyz && !nrm)) return XRT_OK;
+  const float4* a = which == 0 ? s->c.x0 : s->o.x0;
+  const float4* b = which == 0 ? s->c.n : s->o.n;
+  // pack to float3 on the device, one D2H into pinned memory, memcpy out
+  launch_pack_xyz(xyz ? a : nullptr, nrm ? b : nullptr, s->d_dn, (uint32_t)n, s->st);
+  XRT_CUDA_OK(cudaMemcpyAsync(s->h_dn, s->d_dn, n * 6 * sizeof(float), cudaMemcpyDeviceToHost, s->st));
+  XRT_CUDA_OK(cudaStreamSynchronize(s->st));
+  if (xyz) memcpy(xyz, s->h_dn, n * 3 * sizeof(float));
+  if (nrm) memcpy(nrm, s->h_dn + 3 * n, n * 3 * sizeof(float));
+  return XRT_OK;
 }
 
 extern "C" int xrt_set_cloth_state(xrt_solver* s, const float* xyz, const float* vel) {
@@ -1168,10 +1183,13 @@ extern "C" void xrt_destroy(xrt_solver* s) {
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
                   c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof,
                   c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
-                  s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq};
+                  s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq, s->d_up, s->d_dn};
   for (void* p : ptrs) cudaFree(p);
   if (s->bvh.n_obj) bvh_free(&s->bvh, &s->bw);
   if (s->stage) cudaFreeHost(s->stage);
+  if (s->h_up) cudaFreeHost(s->h_up);
+  if (s->h_dn) cudaFreeHost(s->h_dn);
+  if (s->ev_up) cudaEventDestroy(s->ev_up);
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
   if (s->ev_join) cudaEventDestroy(s->ev_join);

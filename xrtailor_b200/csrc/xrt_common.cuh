@@ -99,11 +99,11 @@ __host__ __device__ __forceinline__ uint32_t tnode_slot(const BVNode* nodes, uin
   return p == 0xFFFFFFFFu ? 0u : tnode_child_slot(p, nodes[p].right == c);
 }
 
-struct VFContact {  // pbd_collision/Contact.cuh VFContact / RTContact
+struct __align__(16) VFContact {  // pbd_collision/Contact.cuh VFContact / RTContact (one 16-byte access)
   int32_t index;
   float q[3];
 };
-struct EEContact {  // pbd_collision/Contact.cuh EEContact (48 bytes)
+struct __align__(16) EEContact {  // pbd_collision/Contact.cuh EEContact (48 bytes = three 16-byte accesses)
   float dist;
   float p2[3], q2[3];
   float s, t;

@@ -55,6 +55,26 @@ __global__ void interpolate_kernel(const float4* __restrict__ x0, const float4* 
   if (i < V) interpolate_item(x0, x, x1, alpha, i);
 }
 
+// host float[3n] <-> device float4[n] at the ABI boundary (dst.w = inverse mass is kept)
+__global__ void unpack_xyz_kernel(const float* __restrict__ src, float4* __restrict__ dst, uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = make_float4(src[3 * i], src[3 * i + 1], src[3 * i + 2], dst[i].w);
+}
+__global__ void pack_xyz_kernel(const float4* __restrict__ a, const float4* __restrict__ b, float* __restrict__ out,
+                                uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (a) {
+    const float4 p = a[i];
+    out[3 * i] = p.x; out[3 * i + 1] = p.y; out[3 * i + 2] = p.z;
+  }
+  if (b) {
+    const float4 q = b[i];
+    float* o2 = out + 3 * (size_t)n;
+    o2[3 * i] = q.x; o2[3 * i + 1] = q.y; o2[3 * i + 2] = q.z;
+  }
+}
+
 }  // namespace
 
 void launch_predict(const ClothDev& c, const StepConst& k, cudaStream_t st) {
@@ -99,4 +119,10 @@ void launch_interpolate(const ObstacleDev& o, int step, int num_steps, cudaStrea
   if (!o.V) return;
   const float alpha = ((float)step + 1.0f) / (float)num_steps;
   interpolate_kernel<<<xrt_grid(o.V), XRT_BLOCK, 0, st>>>(o.x0, o.x, o.x1, alpha, o.V);
+}
+void launch_unpack_xyz(const float* src, float4* dst, uint32_t n, cudaStream_t st) {
+  if (n) unpack_xyz_kernel<<<xrt_grid(n), XRT_BLOCK, 0, st>>>(src, dst, n);
+}
+void launch_pack_xyz(const float4* a, const float4* b, float* out, uint32_t n, cudaStream_t st) {
+  if (n) pack_xyz_kernel<<<xrt_grid(n), XRT_BLOCK, 0, st>>>(a, b, out, n);
 }

@@ -78,6 +78,9 @@ void launch_lra(const ClothDev& c, const StepConst& k, cudaStream_t st);
 void launch_apply_deltas(const ClothDev& c, const StepConst& k, cudaStream_t st);
 void launch_normals(const float4* x, float4* n, const uint32_t* tri, const uint32_t* vf_off,
                     const uint32_t* vf_idx, uint32_t V, cudaStream_t st);
+// ABI boundary conversions: float[3n] -> float4[n] (w kept) and two float4[n] -> float[3n] | float[3n]
+void launch_unpack_xyz(const float* src, float4* dst, uint32_t n, cudaStream_t st);
+void launch_pack_xyz(const float4* a, const float4* b, float* out, uint32_t n, cudaStream_t st);
 void launch_interpolate(const ObstacleDev& o, int step, int num_steps, cudaStream_t st);
 // ---- contacts (xrt_contact.cu) ----
 // counts: also record the per-query leaf-hit counts (debug getters); the frame path passes false
