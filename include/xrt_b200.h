@@ -107,6 +107,15 @@ int xrt_set_bend(xrt_solver* s, const uint32_t* idx0123, const float* theta, siz
 int xrt_add_geodesic(xrt_solver* s, const uint32_t* src, const uint32_t* tgt,
                      const float* rest, size_t n);
 
+/* BindingConstraint::Add + Generate (physics/dynamics/BindingConstraint.cu:11-55,
+ * called from ClothSolverSMPL::Start, pipeline/impl/smpl/ClothSolver.cpp): tether
+ * cloth vertex cloth_idx[i] to the point bary[3i..] of the obstacle triangle with
+ * vertex ids tri[3i..] (the reference's SkinParam).  distance[i] < 1e-6 means
+ * "the distance at setup".  Solved one-sided after the contact solves of every
+ * iteration (SolveBinding_Kernel, BindingConstraint.cu:56-92).  Before finalize. */
+int xrt_add_binding(xrt_solver* s, const uint32_t* cloth_idx, const uint32_t* tri, const float* bary,
+                    const float* stiffness, const float* distance, size_t n);
+
 /* Parity injection of the reference's GraphColoring::colors
  * (physics/graph_coloring/Base.cuh:36).  kind 0 = stretch, 1 = bend.
  * Without it xrt_finalize_setup colours deterministically (greedy). */

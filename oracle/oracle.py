@@ -46,6 +46,8 @@ def _load():
     L.oracle_scene_set_stretch.argtypes = [vp, u32p, f32p, u32p, C.c_uint32]
     L.oracle_scene_set_bend.argtypes = [vp, u32p, f32p, u32p, C.c_uint32]
     L.oracle_scene_set_lra.argtypes = [vp, u32p, u32p, f32p, C.c_uint32]
+    L.oracle_scene_set_binding.argtypes = [vp, u32p, u32p, f32p, f32p, f32p, C.c_uint32]
+    L.oracle_scene_set_binding.restype = None
     L.oracle_scene_set_obstacle.argtypes = [vp, f32p, C.c_uint32, u32p, C.c_uint32]
     L.oracle_scene_set_obstacle_target.argtypes = [vp, f32p]
     L.oracle_scene_set_state.argtypes = [vp, f32p, f32p]
@@ -55,7 +57,7 @@ def _load():
     L.oracle_scene_free.argtypes = [vp]
     for n in ["oracle_step_frame", "oracle_generate_contacts", "oracle_hash", "oracle_collide_particles",
               "oracle_solve_lra", "oracle_apply_deltas", "oracle_solve_vf_ccd", "oracle_solve_vf_dcd",
-              "oracle_solve_ee_dcd"]:
+              "oracle_solve_ee_dcd", "oracle_solve_binding"]:
         f = getattr(L, n); f.argtypes = [vp]; f.restype = None
     L.oracle_predict.argtypes = [vp, C.c_float]; L.oracle_predict.restype = None
     L.oracle_finalize.argtypes = [vp, C.c_float]; L.oracle_finalize.restype = None
@@ -165,6 +167,14 @@ class Scene:
     def set_lra(self, src, tgt, rest):
         L.oracle_scene_set_lra(self.h, _pu(_u(src)), _pu(_u(tgt)), _pf(_f(rest)), len(rest))
 
+    def set_binding(self, vert, tri3, bary3, stiffness, distance):
+        """BindingConstraint::Add + Generate (BindingConstraint.cu:11-55)."""
+        L.oracle_scene_set_binding(self.h, _pu(_u(vert)), _pu(_u(tri3)), _pf(_f(bary3)), _pf(_f(stiffness)),
+                                   _pf(_f(distance)), len(vert))
+
+    def solve_binding(self):
+        L.oracle_solve_binding(self.h)
+
     def set_obstacle_target(self, xyz):
         L.oracle_scene_set_obstacle_target(self.h, _pf(_f(xyz)))
 
@@ -199,6 +209,10 @@ class Scene:
 
     def predicted(self):
         return _arr(L.oracle_scene_x(self.h), 3 * self.V, np.float32).reshape(-1, 3)
+
+    def set_predicted(self, x):
+        """Overwrite Node::x (test helper)."""
+        np.ctypeslib.as_array(L.oracle_scene_x(self.h), shape=(3 * self.V,))[:] = _f(x).ravel()
 
     def velocity(self):
         return _arr(L.oracle_scene_v(self.h), 3 * self.V, np.float32).reshape(-1, 3)

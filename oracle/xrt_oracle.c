@@ -533,6 +533,10 @@ typedef struct {
   uint32_t ns, nb, nl, n_sc, n_bc;
   uint32_t *s_idx, *s_color, *b_idx, *b_color, *l_src, *l_tgt;
   float *s_rest, *s_lambda, *b_theta, *l_rest;
+  /* bindings (BindingItem, dynamics/BindingConstraint.cuh:11-21) */
+  uint32_t nbind;
+  uint32_t *bd_vert, *bd_tri;
+  float *bd_bary, *bd_L, *bd_k;
   /* obstacle */
   uint32_t Vo, Fo;
   float *ox0, *ox, *ox1, *on, *on1;
@@ -739,6 +743,44 @@ void oracle_solve_lra(OScene* s) {
     const v3 diff = sub(ld3(s->x, tgt), ld3(s->x, src));
     const float dist = len(diff);
     if (dist > target) st3(s->x, tgt, add(ld3(s->x, tgt), add(neg(diff), mul(divs(diff, dist), target))));
+  }
+}
+/* BindingConstraint::Add + GenerateBinding_Kernel (BindingConstraint.cu:11-48): the
+ * barycentric anchor (skin_params) is passed in; rest length = given distance, or the
+ * setup-time distance to the anchor when that is < EPSILON.  Call after set_cloth and
+ * set_obstacle. */
+void oracle_scene_set_binding(OScene* s, const uint32_t* vert, const uint32_t* tri3, const float* bary3,
+                              const float* stiffness, const float* distance, uint32_t n) {
+  s->nbind = n;
+  s->bd_vert = (uint32_t*)dup_mem(vert, 4 * (size_t)n);
+  s->bd_tri = (uint32_t*)dup_mem(tri3, 12 * (size_t)n);
+  s->bd_bary = (float*)dup_mem(bary3, 12 * (size_t)n);
+  s->bd_k = (float*)dup_mem(stiffness, 4 * (size_t)n);
+  s->bd_L = (float*)dup_mem(distance, 4 * (size_t)n);
+  for (uint32_t i = 0; i < n; i++) {
+    const v3 pc = ld3(s->x0, vert[i]);
+    const v3 pb = add(add(mul(ld3(s->ox0, tri3[3 * i]), bary3[3 * i]), mul(ld3(s->ox0, tri3[3 * i + 1]), bary3[3 * i + 1])),
+                      mul(ld3(s->ox0, tri3[3 * i + 2]), bary3[3 * i + 2]));
+    if (s->bd_L[i] < EPS) s->bd_L[i] = len(sub(pc, pb));
+  }
+}
+/* SolveBinding_Kernel, BindingConstraint.cu:56-92: one-sided tether of a cloth vertex to
+ * a point of an obstacle triangle at its frame-end position (Node::x) */
+void oracle_solve_binding(OScene* s) {
+  for (uint32_t i = 0; i < s->nbind; i++) {
+    const uint32_t cv = s->bd_vert[i];
+    const float inv_mass = s->invm[cv];
+    if (inv_mass < EPS) continue;
+    const float* b = s->bd_bary + 3 * i;
+    const uint32_t* t = s->bd_tri + 3 * i;
+    const v3 po = add(add(mul(ld3(s->ox, t[0]), b[0]), mul(ld3(s->ox, t[1]), b[1])), mul(ld3(s->ox, t[2]), b[2]));
+    const v3 d = sub(ld3(s->x, cv), po);
+    const float C = len(d) - s->bd_L[i];
+    const v3 n = normalize(d);
+    float sc = C / inv_mass;
+    if (C < 0.0f) continue;
+    sc *= s->bd_k[i];
+    st3(s->x, cv, add(ld3(s->x, cv), mul(n, -sc * inv_mass)));
   }
 }
 /* ApplyDeltas_Kernel, ClothSolverHelper.cu:139-148 */
@@ -1005,6 +1047,7 @@ void oracle_iteration(OScene* s, float dt, int iteration) {
   oracle_solve_vf_dcd(s);
   oracle_solve_ee_dcd(s);
   if (s->bvh) oracle_apply_deltas(s);
+  if (s->bvh) oracle_solve_binding(s); /* binding_->Solve, ClothSolverBase.cpp:236 (no-op without an obstacle) */
 }
 
 void oracle_step_frame(OScene* s) {
@@ -1063,6 +1106,7 @@ void oracle_scene_free(OScene* s) {
   free(s->x0); free(s->x); free(s->v); free(s->invm); free(s->n); free(s->rest); free(s->tri); free(s->edge);
   free(s->s_idx); free(s->s_color); free(s->b_idx); free(s->b_color); free(s->l_src); free(s->l_tgt);
   free(s->s_rest); free(s->s_lambda); free(s->b_theta); free(s->l_rest);
+  free(s->bd_vert); free(s->bd_tri); free(s->bd_bary); free(s->bd_L); free(s->bd_k);
   free(s->ox0); free(s->ox); free(s->ox1); free(s->on); free(s->on1); free(s->otri); free(s->rtri);
   oracle_bvh_free(s->bvh);
   free(s->vf_idx); free(s->rt_idx); free(s->vf_q); free(s->rt_q); free(s->ee);

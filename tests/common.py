@@ -14,14 +14,16 @@ def params(**kw):
     return p
 
 
-def pair(sc, **kw):
+def pair(sc, bindings=None, **kw):
     """(cuda solver, oracle scene) on identical inputs and colours."""
     kw.setdefault("particle_diameter", sc.particle_diameter())
     kw.setdefault("morton_fast_div", 0)  # IEEE division: bit parity with the CPU oracle
     cs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
     cb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
-    s = scene.make_solver(sc, colors=(cs, cb), **kw)
+    s = scene.make_solver(sc, colors=(cs, cb), bindings=bindings, **kw)
     o = O.Scene(sc, s.params, (cs, cb))
+    if bindings is not None:
+        o.set_binding(*bindings)
     return s, o
 
 

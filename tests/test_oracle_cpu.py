@@ -218,3 +218,28 @@ def test_contact_keeps_cloth_outside_sphere():
     assert r.min() > 0.295          # nothing tunnels into the r = 0.3 sphere (faceted: ~0.297 at face centres)
     c = o.contacts()
     assert (c["vf_idx"] >= 0).sum() > 10 and (c["ee"][:, 0] < 1e6).sum() > 10
+
+
+def test_binding_known_answer():
+    """SolveBinding_Kernel by hand: vertex 1 m above its anchor, rest length 0.25, stiffness 0.5
+    -> C = 0.75, moved down by 0.5 * 0.75; slack tethers and pinned vertices do not move."""
+    from xrtailor_b200 import scene
+    sc = scene.drop_scene(4, sphere=(4, 6))
+    p = X.default_params()
+    p.particle_diameter = sc.particle_diameter()
+    cs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
+    cb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+    o = O.Scene(sc, p, (cs, cb))
+    tri = sc.obs_tri[:2].astype(np.uint32)
+    bary = np.array([[1, 0, 0], [0.25, 0.25, 0.5]], np.float32)
+    anchor = np.einsum("nk,nkd->nd", bary, sc.obs_pos[tri])
+    o.set_binding(np.array([0, 1], np.uint32), tri, bary, np.array([0.5, 1.0], np.float32),
+                  np.array([0.25, 100.0], np.float32))
+    x = o.predicted().copy()
+    x[0] = anchor[0] + [0, 1.0, 0]
+    x[1] = anchor[1] + [0, 1.0, 0]          # slack: rest length 100
+    o.set_predicted(x)
+    o.solve_binding()
+    y = o.predicted()
+    np.testing.assert_allclose(y[0], anchor[0] + [0, 1.0 - 0.5 * 0.75, 0], atol=1e-6)
+    np.testing.assert_array_equal(y[1], x[1])

@@ -279,3 +279,40 @@ def test_per_stage_shape_still_matches_oracle(small):
     o.step_frame()
     assert rel_rms(s.GetPositions(0), o.positions()) <= 1e-5
     s.close()
+
+
+def _waist_bindings(sc, n=64, seed=3):
+    """Tether n cloth vertices to the obstacle triangle under them (a belt)."""
+    rng = np.random.default_rng(seed)
+    verts = rng.choice(len(sc.cloth_pos), n, replace=False).astype(np.uint32)
+    tris = sc.obs_tri[rng.integers(0, len(sc.obs_tri), n)].astype(np.uint32)
+    bary = rng.dirichlet(np.ones(3), n).astype(np.float32)
+    stiff = rng.uniform(0.2, 1.0, n).astype(np.float32)
+    dist = np.where(rng.random(n) < 0.7, 0.0, rng.uniform(0.05, 0.5, n)).astype(np.float32)  # 0: length at setup
+    return verts, tris, bary, stiff, dist
+
+
+@pytest.mark.parametrize("cluster", [0, 8])
+def test_binding_constraints_vs_oracle(small, cluster):
+    """SolveBinding_Kernel (row a8): tethers pull while the obstacle moves away."""
+    b = _waist_bindings(small)
+    s, o = pair(small, bindings=b, num_substeps=1, persist_cluster=cluster)
+    s0, o0 = pair(small, num_substeps=1, persist_cluster=cluster)
+    tgt = scene.sphere_motion(small.obs_pos, 45, amp=0.05)  # sphere 5 cm down: the tethers above it go taut
+    for obj in (s, s0):
+        obj.UpdateObstacleAnimationFrame(tgt)
+    for obj in (o, o0):
+        obj.set_obstacle_target(tgt)
+    for obj in (s, s0):
+        obj.SimulateSwift()
+    for obj in (o, o0):
+        obj.step_frame()
+    g, c = s.GetPositions(0), o.positions()
+    assert rel_rms(g, c) <= 1e-5, rel_rms(g, c)
+    # the tethers did something, and the same thing on both sides
+    moved_g = np.linalg.norm(g - s0.GetPositions(0), axis=1)[b[0]]
+    moved_o = np.linalg.norm(c - o0.positions(), axis=1)[b[0]]
+    assert (moved_o > 1e-4).sum() >= 8
+    np.testing.assert_allclose(moved_g, moved_o, atol=2e-5)
+    for obj in (s, s0):
+        obj.close()

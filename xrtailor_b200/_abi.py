@@ -51,7 +51,7 @@ SYMBOLS = [
     "xrt_set_obstacle_target", "xrt_set_obstacle_sequence", "xrt_batch_run", "xrt_profile_kernel", "xrt_step_frame", "xrt_step_frame_async", "xrt_sync", "xrt_get_positions",
     "xrt_set_cloth_state", "xrt_set_cloth_predicted", "xrt_bvh_build_obstacle", "xrt_bvh_refit_obstacle", "xrt_generate_contacts",
     "xrt_hash_particles", "xrt_predict", "xrt_solve_iteration", "xrt_finalize", "xrt_debug_get",
-    "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone", "xrt_persist_info", "xrt_batch_profile_substep",
+    "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone", "xrt_persist_info", "xrt_batch_profile_substep", "xrt_add_binding",
 ]
 
 
@@ -93,6 +93,7 @@ def _load():
         "xrt_debug_candidates": [vp, C.c_int, u32p, u32p, C.POINTER(C.c_size_t)],
         "xrt_greedy_color": [u32p, C.c_size_t, C.c_int, C.c_uint32, u32p, u32p],
         "xrt_batch_profile_substep": [C.POINTER(vp), C.c_int, C.c_int, f32p, C.POINTER(C.c_double)],
+        "xrt_add_binding": [vp, u32p, u32p, f32p, f32p, f32p, C.c_size_t],
         "xrt_persist_info": [C.c_int, i32p, i32p],
         "xrt_bvh_build_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, C.c_int, C.c_int, u32p, u32p, u32p, f32p,
                                      i32p, i32p, f32p],

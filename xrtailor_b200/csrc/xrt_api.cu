@@ -24,6 +24,8 @@ struct xrt_solver {
   std::vector<uint32_t> c_tri, c_edge, o_tri, o_edge;
   std::vector<uint32_t> s_idx, b_idx, s_color, b_color, l_src, l_tgt;
   std::vector<float> s_rest, b_theta, l_rest;
+  std::vector<uint32_t> bd_vert, bd_tri;
+  std::vector<float> bd_bary, bd_k, bd_dist;
   bool s_color_set = false, b_color_set = false;
   // colour ranges over the permuted constraint arrays
   std::vector<uint32_t> s_off, b_off;
@@ -196,6 +198,19 @@ extern "C" int xrt_add_geodesic(xrt_solver* s, const uint32_t* src, const uint32
   s->l_src.insert(s->l_src.end(), src, src + n);
   s->l_tgt.insert(s->l_tgt.end(), tgt, tgt + n);
   s->l_rest.insert(s->l_rest.end(), rest, rest + n);
+  return XRT_OK;
+}
+
+extern "C" int xrt_add_binding(xrt_solver* s, const uint32_t* cloth_idx, const uint32_t* tri, const float* bary,
+                               const float* stiffness, const float* distance, size_t n) {
+  if (!s) return XRT_ERR_INVALID;
+  XRT_REQUIRE(!s->finalized, "add_binding after finalize_setup");
+  XRT_REQUIRE(n == 0 || (cloth_idx && tri && bary && stiffness && distance), "add_binding: null array");
+  s->bd_vert.insert(s->bd_vert.end(), cloth_idx, cloth_idx + n);
+  s->bd_tri.insert(s->bd_tri.end(), tri, tri + 3 * n);
+  s->bd_bary.insert(s->bd_bary.end(), bary, bary + 3 * n);
+  s->bd_k.insert(s->bd_k.end(), stiffness, stiffness + n);
+  s->bd_dist.insert(s->bd_dist.end(), distance, distance + n);
   return XRT_OK;
 }
 
@@ -473,6 +488,34 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
       return XRT_ERR_CUDA;
     }
   }
+  // --- bindings: GenerateBinding_Kernel (BindingConstraint.cu:22-46) on the host ---
+  c.n_bind = (uint32_t)s->bd_vert.size();
+  if (c.n_bind) {
+    XRT_REQUIRE(o.V, "bindings need an obstacle");
+    std::vector<uint4> bi(c.n_bind);
+    std::vector<float4> bp(c.n_bind);
+    for (uint32_t i = 0; i < c.n_bind; i++) {
+      const uint32_t cv = s->bd_vert[i];
+      const uint32_t* t = &s->bd_tri[3 * (size_t)i];
+      const float* w = &s->bd_bary[3 * (size_t)i];
+      XRT_REQUIRE(cv < c.V && t[0] < o.V && t[1] < o.V && t[2] < o.V, "binding index out of range");
+      float L = s->bd_dist[i];
+      if (L < XRT_EPS) {
+        float d2 = 0.f;
+        for (int k = 0; k < 3; k++) {
+          const float pb = w[0] * s->o_pos[3 * t[0] + k] + w[1] * s->o_pos[3 * t[1] + k] + w[2] * s->o_pos[3 * t[2] + k];
+          const float d = s->c_pos[3 * cv + k] - pb;
+          d2 += d * d;
+        }
+        L = sqrtf(d2);
+      }
+      bi[i] = make_uint4(cv, t[0], t[1], t[2]);
+      bp[i] = make_float4(w[0], w[1], w[2], L);
+    }
+    XRT_CUDA_OK(dev_upload(&c.bd_idx, bi));
+    XRT_CUDA_OK(dev_upload(&c.bd_par, bp));
+    XRT_CUDA_OK(dev_upload(&c.bd_k, s->bd_k));
+  }
   // launch shape (xrt_params.persist_cluster)
   {
     int cl = s->p.persist_cluster;
@@ -534,6 +577,10 @@ static void enqueue_iteration(xrt_solver* s, int iteration, uint32_t* launches) 
     (*launches) += c.E ? 2 : 1;
     launch_apply_deltas(c, s->k, st);
     (*launches)++;
+    if (c.n_bind) {
+      launch_binding(c, s->o, st);  // binding_->Solve, ClothSolverBase.cpp:236
+      (*launches)++;
+    }
   }
 }
 
@@ -1181,7 +1228,7 @@ extern "C" void xrt_destroy(xrt_solver* s) {
   ClothDev& c = s->c;
   void* ptrs[] = {c.x0, c.x, c.v, c.n, c.rest, c.tri, c.edge, c.vf_off, c.vf_idx, c.s_idx, c.s_rest, c.s_lambda,
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
-                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof,
+                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof, c.bd_idx, c.bd_par, c.bd_k,
                   c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
                   s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq, s->d_up, s->d_dn};
   for (void* p : ptrs) cudaFree(p);

@@ -131,6 +131,29 @@ __device__ __forceinline__ void lra_item(float4* x, const uint32_t* src, const u
   }
 }
 
+// SolveBinding_Kernel, BindingConstraint.cu:56-92: one-sided tether of a cloth
+// vertex to a barycentric point of an obstacle triangle at its frame-end
+// position (Node::x); the kernel's `s = C / inv_mass ... * inv_mass` is kept as written.
+__device__ __forceinline__ void binding_item(float4* x, const float4* ox, const uint4* bd_idx, const float4* bd_par,
+                                             const float* bd_k, uint32_t i) {
+  const uint4 id = bd_idx[i];
+  const float4 par = bd_par[i];
+  float4 pc = x[id.x];
+  const float inv_mass = pc.w;
+  if (inv_mass < XRT_EPS) return;
+  const f3 po = par.x * mk3(ox[id.y]) + par.y * mk3(ox[id.z]) + par.z * mk3(ox[id.w]);
+  const f3 d = mk3(pc) - po;
+  const float dl = xf_len(d);
+  const float C = dl - par.w;
+  if (C < 0.f) return;
+  const f3 n = d * xf_rcp(dl);
+  const float s = xf_div(C, inv_mass) * bd_k[i];
+  pc.x = fmaf(-s * inv_mass, n.x, pc.x);
+  pc.y = fmaf(-s * inv_mass, n.y, pc.y);
+  pc.z = fmaf(-s * inv_mass, n.z, pc.z);
+  x[id.x] = pc;
+}
+
 // ApplyDeltas_Kernel, ClothSolverHelper.cu:139-148
 __device__ __forceinline__ void apply_delta_item(float4* x, float4* delta, float relaxation, uint32_t i) {
   const float4 d = delta[i];

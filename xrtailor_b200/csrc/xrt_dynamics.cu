@@ -39,6 +39,11 @@ __global__ void lra_kernel(float4* x, const uint32_t* __restrict__ src, const ui
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) lra_item(x, src, tgt, rest, stretchiness, i);
 }
+__global__ void binding_kernel(float4* x, const float4* __restrict__ ox, const uint4* __restrict__ bd_idx,
+                               const float4* __restrict__ bd_par, const float* __restrict__ bd_k, uint32_t n) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) binding_item(x, ox, bd_idx, bd_par, bd_k, i);
+}
 __global__ void apply_deltas_kernel(float4* x, float4* delta, float relaxation, uint32_t V) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < V) apply_delta_item(x, delta, relaxation, i);
@@ -106,6 +111,10 @@ void launch_bend_color(const ClothDev& c, const StepConst& k, uint32_t begin, ui
 void launch_lra(const ClothDev& c, const StepConst& k, cudaStream_t st) {
   if (!c.n_lra) return;
   lra_kernel<<<xrt_grid(c.n_lra), XRT_BLOCK, 0, st>>>(c.x, c.l_src, c.l_tgt, c.l_rest, c.n_lra, k.lra_stretchiness);
+}
+void launch_binding(const ClothDev& c, const ObstacleDev& o, cudaStream_t st) {
+  if (c.n_bind && o.V)
+    binding_kernel<<<xrt_grid(c.n_bind), XRT_BLOCK, 0, st>>>(c.x, o.x, c.bd_idx, c.bd_par, c.bd_k, c.n_bind);
 }
 void launch_apply_deltas(const ClothDev& c, const StepConst& k, cudaStream_t st) {
   apply_deltas_kernel<<<xrt_grid(c.V), XRT_BLOCK, 0, st>>>(c.x, c.delta, k.relaxation, c.V);

@@ -204,6 +204,10 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
       for (uint32_t i = tid; i < V; i += nth) apply_delta_item(c.x, c.delta, k.relaxation, i);
       phase_sync<MULTI>();
     pc.lap(11);
+      if (c.n_bind) {  // binding_->Solve, ClothSolverBase.cpp:236
+        for (uint32_t i = tid; i < c.n_bind; i += nth) binding_item(c.x, o.x, c.bd_idx, c.bd_par, c.bd_k, i);
+        phase_sync<MULTI>();
+      }
     }
   }
   if (a.do_finalize)

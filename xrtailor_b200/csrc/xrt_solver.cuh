@@ -28,6 +28,11 @@ struct ClothDev {
   uint32_t n_lra = 0;
   uint32_t *l_src = nullptr, *l_tgt = nullptr;
   float* l_rest = nullptr;
+  // bindings (BindingItem): idx = cloth vertex + 3 obstacle vertices, par = barycentric u,v,w + rest length
+  uint32_t n_bind = 0;
+  uint4* bd_idx = nullptr;
+  float4* bd_par = nullptr;
+  float* bd_k = nullptr;
   // Jacobi accumulators (MemoryPool::deltas / delta_counts)
   float4* delta = nullptr;  // xyz = sum, w = count
   // contacts
@@ -75,6 +80,7 @@ void launch_stretch_color(const ClothDev& c, const StepConst& k, uint32_t begin,
 void launch_bend_color(const ClothDev& c, const StepConst& k, uint32_t begin, uint32_t end, bool atomic,
                        cudaStream_t st);
 void launch_lra(const ClothDev& c, const StepConst& k, cudaStream_t st);
+void launch_binding(const ClothDev& c, const ObstacleDev& o, cudaStream_t st);
 void launch_apply_deltas(const ClothDev& c, const StepConst& k, cudaStream_t st);
 void launch_normals(const float4* x, float4* n, const uint32_t* tri, const uint32_t* vf_off,
                     const uint32_t* vf_idx, uint32_t V, cudaStream_t st);

@@ -142,7 +142,7 @@ def sphere_motion(obs_pos, frame, amp=0.05, hz=1.0, fps=60.0):
     return out.astype(np.float32)
 
 
-def make_solver(scene, colors=None, **params):
+def make_solver(scene, colors=None, bindings=None, **params):
     """Reference call order: AddCloth, AddObstacle, constraints, (colours), Start."""
     from .solver import ClothSolver
     if "particle_diameter" not in params:
@@ -153,6 +153,8 @@ def make_solver(scene, colors=None, **params):
         s.AddObstacle(scene.obs_pos, scene.obs_tri, scene.obs_edges)
     s.SetStretch(scene.stretch_idx, scene.stretch_rest)
     s.SetBend(scene.bend_idx, scene.bend_theta)
+    if bindings is not None:
+        s.AddBinding(*bindings)
     if colors is not None:
         s.SetColors(0, colors[0])
         s.SetColors(1, colors[1])

@@ -117,6 +117,12 @@ class ClothSolver:
         s, t, r = _u32(src), _u32(tgt), _f32(rest)
         self._ck(lib.xrt_add_geodesic(self._h, _pu(s), _pu(t), _pf(r), len(r)))
 
+    def AddBinding(self, cloth_idx, tri, bary, stiffness, distance):
+        """BindingConstraint::Add (BindingConstraint.cu:11-20) with the SkinParam anchor passed in."""
+        v, t, b = _u32(cloth_idx), _u32(tri).reshape(-1, 3), _f32(bary).reshape(-1, 3)
+        k, d = _f32(stiffness), _f32(distance)
+        self._ck(lib.xrt_add_binding(self._h, _pu(v), _pu(t), _pf(b), _pf(k), _pf(d), len(v)))
+
     def SetColors(self, kind, colors):
         c = _u32(colors)
         self._ck(lib.xrt_set_colors(self._h, int(kind), _pu(c), len(c)))
