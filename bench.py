@@ -111,7 +111,9 @@ def run_ours(args):
     sc = build_scene(args.n)
     V, E, Vo = len(sc.cloth_pos), len(sc.cloth_edges), len(sc.obs_pos)
     cluster = args.cluster
-    if cluster != 0:
+    if cluster == -2:
+        resident = 1  # every SM on one garment: instances run back to back
+    elif cluster != 0:
         mx, resident = X.persist_info(cluster)
         if cluster < 0 or cluster > mx:
             cluster = mx
@@ -303,7 +305,8 @@ def main():
     ap.add_argument("--instances", type=int, default=0,
                     help="independent simulations per GPU (0: one per resident cluster)")
     ap.add_argument("--cluster", type=int, default=8,
-                    help="CTAs per garment of the persistent substep kernel (0: per-stage launches, -1: largest)")
+                    help="CTAs per garment of the persistent substep kernel (0: per-stage launches, -1: largest cluster, "
+                         "-2: every SM on one garment)")
     ap.add_argument("--cpu-frames", type=int, default=8)
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

@@ -62,6 +62,8 @@ typedef struct xrt_params {
    * thread-block cluster of C CTAs (1, 2, 4, 8 or 16; one CTA per SM) with
    * hardware cluster barriers between the phases; 148 / C garments run
    * concurrently on a B200.  -1: the largest cluster the device schedules.
+   * -2: every SM of the device on ONE garment (cooperative launch, grid-wide
+   * software barrier): lowest latency for a single garment, no concurrency.
    * Both shapes call the same device bodies and give identical results. */
   int32_t persist_cluster;
   int32_t device;                /* CUDA device ordinal                */

@@ -236,7 +236,7 @@ def _run_frames(sc, frames, **kw):
     return x, st, vf
 
 
-@pytest.mark.parametrize("cluster", [1, 2, 8, 16])
+@pytest.mark.parametrize("cluster", [1, 2, 8, 16, -2])
 def test_persistent_bit_equal_before_contact(cluster):
     """Same device bodies, same phase order: with a proper colouring and no EE
     contact (whose Jacobi sum uses float atomics) the two launch shapes agree
@@ -249,7 +249,7 @@ def test_persistent_bit_equal_before_contact(cluster):
     assert st1["launches_per_frame"] < st0["launches_per_frame"] / 10
 
 
-@pytest.mark.parametrize("cluster", [1, 8, -1])
+@pytest.mark.parametrize("cluster", [1, 8, -1, -2])
 def test_persistent_in_contact_vs_oracle(small, cluster):
     s, o = pair(small, persist_cluster=cluster)
     for f in range(6):

@@ -52,6 +52,7 @@ struct xrt_solver {
   size_t seq_frames = 0, seq_cursor = 0;
   cudaEvent_t ev_join = nullptr;
   int cluster = 0;  // resolved persist_cluster (0: per-stage launches)
+  unsigned long long* d_grid_bar = nullptr;  // grid-wide barrier counter (persist_cluster -2)
   unsigned long long* d_prof = nullptr;  // [16] per-phase-kind ns of the persistent kernel (XRT_PERSIST_PROF=1)
 };
 
@@ -520,8 +521,16 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
   {
     int cl = s->p.persist_cluster;
     const int mx = persist_max_cluster();
-    if (cl < 0 || cl > mx) cl = mx;
-    XRT_REQUIRE(cl == 0 || (cl & (cl - 1)) == 0, "persist_cluster must be 0, -1 or a power of two up to 16");
+    if (cl == -2) {
+      XRT_REQUIRE(persist_grid_ctas() > 0, "persist_cluster -2: the substep kernel cannot be co-resident on this device");
+      cl = XRT_PERSIST_GRID;
+      XRT_CUDA_OK(dev_alloc(&s->d_grid_bar, 1));
+      XRT_CUDA_OK(cudaMemset(s->d_grid_bar, 0, sizeof(unsigned long long)));
+    } else if (cl < 0 || cl > mx) {
+      cl = mx;
+    }
+    XRT_REQUIRE(cl == 0 || cl == XRT_PERSIST_GRID || (cl & (cl - 1)) == 0,
+                "persist_cluster must be 0, -1, -2 or a power of two up to 16");
     s->cluster = cl;
     const char* pe = getenv("XRT_PERSIST_PROF");
     if (cl > 0 && pe && pe[0] == '1') {
@@ -615,6 +624,7 @@ static PersistArgs make_persist_args(const xrt_solver* s, int substep, bool move
   a.lra = p.geodesic_lra; a.moved = moved ? 1 : 0;
   a.atomic_s = s->atomic_s ? 1 : 0; a.atomic_b = s->atomic_b ? 1 : 0;
   a.prof = s->d_prof;
+  a.grid_bar = s->d_grid_bar;
   return a;
 }
 
@@ -1228,7 +1238,7 @@ extern "C" void xrt_destroy(xrt_solver* s) {
   ClothDev& c = s->c;
   void* ptrs[] = {c.x0, c.x, c.v, c.n, c.rest, c.tri, c.edge, c.vf_off, c.vf_idx, c.s_idx, c.s_rest, c.s_lambda,
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
-                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof, c.bd_idx, c.bd_par, c.bd_k,
+                  c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof, s->d_grid_bar, c.bd_idx, c.bd_par, c.bd_k,
                   c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
                   s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq, s->d_up, s->d_dn};
   for (void* p : ptrs) cudaFree(p);

@@ -36,14 +36,34 @@ __device__ __forceinline__ uint32_t cluster_nctarank() {
   return r;
 }
 
-// Barrier between two phases.  Release/acquire at cluster scope orders the
-// global-memory writes of every CTA of the cluster before the reads that
-// follow (ptxas emits the L1 invalidate with the acquire).  A one-CTA cluster
-// shares one L1, so bar.sync is enough.
-template <bool MULTI>
-__device__ __forceinline__ void phase_sync() {
-  if (MULTI) {
+// Barrier between two phases, by launch shape:
+//  SYNC_BLOCK    one CTA: bar.sync (one L1, nothing to invalidate);
+//  SYNC_CLUSTER  hardware cluster barrier; release/acquire at cluster scope orders
+//                the global-memory writes of every CTA before the reads that follow
+//                (ptxas emits MEMBAR.GPU before the arrive and CCTL.IVALL after the wait);
+//  SYNC_GRID     every SM of the device on ONE garment (cooperative launch): bar.sync,
+//                then thread 0 publishes with a gpu-scope fence, takes a ticket on a
+//                monotonically increasing counter and spins until all CTAs of this
+//                round have arrived; its acquiring fence invalidates the SM's L1.
+enum { SYNC_BLOCK = 0, SYNC_CLUSTER = 1, SYNC_GRID = 2 };
+template <int MODE>
+__device__ __forceinline__ void phase_sync(unsigned long long* grid_bar = nullptr) {
+  if (MODE == SYNC_CLUSTER) {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+  } else if (MODE == SYNC_GRID) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      const unsigned long long n = gridDim.x;
+      const unsigned long long ticket = atomicAdd(grid_bar, 1ull);
+      const unsigned long long target = (ticket / n + 1ull) * n;
+      unsigned long long seen;
+      do {
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(seen) : "l"(grid_bar) : "memory");
+      } while (seen < target);
+      __threadfence();
+    }
+    __syncthreads();
   } else {
     __syncthreads();
   }
@@ -101,10 +121,11 @@ __device__ __forceinline__ ColorRec fetch_color_rec(const PersistArgs& a, uint32
   return r;
 }
 
-template <bool MULTI>
+template <int MODE>
 __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_constant__ PersistArgs a) {
-  const uint32_t nth = (MULTI ? cluster_nctarank() : 1u) * PT;
-  const uint32_t tid = (MULTI ? cluster_ctarank() : 0u) * PT + threadIdx.x;
+  const uint32_t nth = (MODE == SYNC_CLUSTER ? cluster_nctarank() : (MODE == SYNC_GRID ? gridDim.x : 1u)) * PT;
+  const uint32_t tid =
+      (MODE == SYNC_CLUSTER ? cluster_ctarank() : (MODE == SYNC_GRID ? blockIdx.x : 0u)) * PT + threadIdx.x;
   const ClothDev& c = a.c;
   const ObstacleDev& o = a.o;
   const StepConst& k = a.k;
@@ -116,16 +137,16 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
 
   if (a.do_predict) {
     for (uint32_t i = tid; i < V; i += nth) predict_item(c.x0, c.x, c.v, k, i);
-    phase_sync<MULTI>();
+    phase_sync<MODE>(a.grid_bar);
     pc.lap(0);
   }
   for (int it = 0; it < a.n_iter; it++) {
     if (a.self_collision) {
       for (uint32_t i = tid; i < V; i += nth) collide_item(c.delta, c.x, c.x0, c.neighbors, k, V, i);
-      phase_sync<MULTI>();
+      phase_sync<MODE>(a.grid_bar);
     pc.lap(1);
       for (uint32_t i = tid; i < V; i += nth) apply_delta_item(c.x, c.delta, k.relaxation, i);
-      phase_sync<MULTI>();
+      phase_sync<MODE>(a.grid_bar);
     pc.lap(2);
     }
     const uint32_t step = (uint32_t)(a.substep * a.n_iter + it);
@@ -134,13 +155,13 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
         const int cnt = (int)(step / a.frequency);
         const float alpha = ((float)cnt + 1.0f) / (float)a.n_passes;
         for (uint32_t i = tid; i < o.V; i += nth) interpolate_item(o.x0, o.x, o.x1, alpha, i);
-        phase_sync<MULTI>();
+        phase_sync<MODE>(a.grid_bar);
         for (uint32_t i = tid; i < o.V; i += nth) normals_item(o.x1, o.n1, o.tri, o.vf_off, o.vf_idx, i);
-        phase_sync<MULTI>();
+        phase_sync<MODE>(a.grid_bar);
     pc.lap(3);
         for (uint32_t i = tid; i < o.F; i += nth)
           refit_item<true>(a.bvh.tnodes, a.bvh.nodes, a.bvh.pred, o.x1, o.n1, o.tri, a.tol, a.refit_flags, o.F, i);
-        phase_sync<MULTI>();
+        phase_sync<MODE>(a.grid_bar);
     pc.lap(4);
       }
       // 32-item groups stay warp-aligned so each warp ballots its own word of the active masks
@@ -154,7 +175,7 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
             i < E && gen_edge_item<false>(a.bvh.tnodes, a.bvh.pred, o.rtri, c.x, c.edge, c.ee, nullptr, i);
         store_active_bits(c.e_active, i, E, live);
       }
-      phase_sync<MULTI>();
+      phase_sync<MODE>(a.grid_bar);
       pc.lap(5);
     }
     // Colour phases of stretch then bend.  The record of this thread's first
@@ -181,32 +202,32 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
           }
         }
         cur = fetch_color_rec(a, ph + 1, n_sc, n_ph, tid, it);
-        phase_sync<MULTI>();
+        phase_sync<MODE>(a.grid_bar);
         pc.lap(ph < n_sc ? 6 : 7);
       }
     }
     if (a.lra && c.n_lra) {
       for (uint32_t i = tid; i < c.n_lra; i += nth) lra_item(c.x, c.l_src, c.l_tgt, c.l_rest, k.lra_stretchiness, i);
-      phase_sync<MULTI>();
+      phase_sync<MODE>(a.grid_bar);
     pc.lap(8);
     }
     if (o.F) {
       for (uint32_t i = tid; i < V; i += nth)
         if (load_active_bit(c.v_active, i)) solve_vertex_item(a.bvh.pred, c.x, c.vf, c.rt, i);
-      phase_sync<MULTI>();
+      phase_sync<MODE>(a.grid_bar);
     pc.lap(9);
       if (E) {
         for (uint32_t i = tid; i < E; i += nth)
           if (load_active_bit(c.e_active, i)) solve_edge_item(c.x, c.edge, c.ee, c.delta, i);
-        phase_sync<MULTI>();
+        phase_sync<MODE>(a.grid_bar);
     pc.lap(10);
       }
       for (uint32_t i = tid; i < V; i += nth) apply_delta_item(c.x, c.delta, k.relaxation, i);
-      phase_sync<MULTI>();
+      phase_sync<MODE>(a.grid_bar);
     pc.lap(11);
       if (c.n_bind) {  // binding_->Solve, ClothSolverBase.cpp:236
         for (uint32_t i = tid; i < c.n_bind; i += nth) binding_item(c.x, o.x, c.bd_idx, c.bd_par, c.bd_k, i);
-        phase_sync<MULTI>();
+        phase_sync<MODE>(a.grid_bar);
       }
     }
   }
@@ -221,7 +242,7 @@ int persist_max_cluster() {
   static int cached = -1;
   if (cached >= 0) return cached;
   // clusters above 8 CTAs need the non-portable opt-in
-  cudaFuncSetAttribute(swift_substep_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  cudaFuncSetAttribute(swift_substep_kernel<SYNC_CLUSTER>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   int best = 1;
   for (int cs = 2; cs <= 16; cs *= 2) {
     cudaLaunchConfig_t cfg = {};
@@ -235,7 +256,7 @@ int persist_max_cluster() {
     cfg.attrs = at;
     cfg.numAttrs = 1;
     int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, swift_substep_kernel<true>, &cfg) == cudaSuccess && n > 0) best = cs;
+    if (cudaOccupancyMaxActiveClusters(&n, swift_substep_kernel<SYNC_CLUSTER>, &cfg) == cudaSuccess && n > 0) best = cs;
   }
   (void)cudaGetLastError();
   cached = best;
@@ -261,16 +282,40 @@ int persist_active_clusters(int cluster) {
   cfg.attrs = at;
   cfg.numAttrs = 1;
   int n = 0;
-  if (cudaOccupancyMaxActiveClusters(&n, swift_substep_kernel<true>, &cfg) != cudaSuccess) {
+  if (cudaOccupancyMaxActiveClusters(&n, swift_substep_kernel<SYNC_CLUSTER>, &cfg) != cudaSuccess) {
     (void)cudaGetLastError();
     return 0;
   }
   return n;
 }
 
+int persist_grid_ctas() {
+  static int cached = -1;
+  if (cached >= 0) return cached;
+  int dev = 0, sms = 0, per_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, swift_substep_kernel<SYNC_GRID>, PT, 0);
+  cached = per_sm > 0 ? sms : 0;  // one CTA per SM, all co-resident
+  return cached;
+}
+
 cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t st) {
+  if (cluster == XRT_PERSIST_GRID) {
+    // whole device on one garment; the cooperative attribute guarantees co-residency
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(persist_grid_ctas());
+    cfg.blockDim = dim3(PT);
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, swift_substep_kernel<SYNC_GRID>, a);
+  }
   if (cluster <= 1) {
-    swift_substep_kernel<false><<<1, PT, 0, st>>>(a);
+    swift_substep_kernel<SYNC_BLOCK><<<1, PT, 0, st>>>(a);
     return cudaGetLastError();
   }
   persist_max_cluster();  // sets the non-portable attribute once
@@ -285,5 +330,5 @@ cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, swift_substep_kernel<true>, a);
+  return cudaLaunchKernelEx(&cfg, swift_substep_kernel<SYNC_CLUSTER>, a);
 }

@@ -3,6 +3,7 @@
 #include "xrt_solver.cuh"
 
 #define XRT_PERSIST_THREADS 1024
+#define XRT_PERSIST_GRID 1000  // resolved launch shape "every SM of the device on one garment"
 
 struct PersistArgs {
   ClothDev c;
@@ -18,6 +19,7 @@ struct PersistArgs {
   uint32_t frequency;     // collision pass every `frequency` (substep, iteration) steps
   int do_predict, do_finalize;
   int self_collision, solve_bending, lra, moved;
+  unsigned long long* grid_bar;  // ticket counter of the grid-wide barrier (XRT_PERSIST_GRID shape)
   unsigned long long* prof;  // optional [16] per-phase-kind ns accumulators (XRT_PERSIST_PROF=1)
   int atomic_s, atomic_b;  // colouring not proper -> float atomics in the projection
 };
@@ -26,4 +28,6 @@ struct PersistArgs {
 int persist_max_cluster();
 // how many clusters of that size can be resident at once
 int persist_active_clusters(int cluster);
+// CTAs of the grid-wide shape (= SMs), 0 if the kernel cannot be co-resident
+int persist_grid_ctas();
 cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t st);
