@@ -154,9 +154,23 @@ def run_ours(args):
     value = frames_total / (ms_max * 1e-3)
     st = solvers[0].stats()
 
-    # ---- single instance latency (ms / frame, ms / substep) --------------
+    # ---- single garment latency (ms / frame) in each launch shape ---------
     lat = [solvers[0].SimulateSwift() for _ in range(max(5, args.steps))]
     ms_frame_single = float(np.median(lat))
+    single = {f"cluster{cluster}" if cluster > 0 else ("grid" if cluster == -2 else "per_stage_graph"):
+              round(ms_frame_single, 4)}
+    if rank == 0 and not args.no_single:
+        for name, shape in (("grid", -2), ("per_stage_graph", 0), ("cluster16", 16)):
+            if name in single:
+                continue
+            try:
+                s1 = scene.make_solver(sc, device=local_rank, persist_cluster=shape)
+                s1.SetObstacleSequence(seqs[0])
+                t1 = [s1.SimulateSwift() for _ in range(25)]
+                single[name] = round(float(np.median(t1[5:])), 4)
+                s1.close()
+            except Exception as e:  # a shape the device cannot schedule
+                single[name] = f"unavailable: {e}"
 
     # ---- end to end through host buffers ---------------------------------
     xyz = [np.empty((V, 3), np.float32) for _ in range(M)]
@@ -217,8 +231,9 @@ def run_ours(args):
             "config": {"workload": f"C1m: {args.n}x{args.n} grid cloth ({V} verts, {E} edges) on moving UV sphere "
                                    f"({Vo} verts), Swift S=4 N=10 C=10, bending+self-collision on",
                        "instances_per_gpu": M, "parallelism": f"replicas x{world}",
-                       "l2_policy": "instances' working sets are cycled (M instances x ~25 MB each); inputs are "
-                                    "larger than one kernel's reuse window but a single instance fits L2",
+                       "l2_policy": f"inputs larger than L2: {M} garments x ~25 MB of state are cycled every step "
+                                    "(126 MB L2); one garment alone is L2 resident",
+                       "single_garment_ms_per_frame": single,
                        "single_instance_ms_per_frame": round(ms_frame_single, 4),
                        "single_instance_ms_per_substep": round(ms_frame_single / 4, 4),
                        "persist_cluster": cluster, "colors": [st["n_stretch_colors"], st["n_bend_colors"]]},
@@ -309,6 +324,7 @@ def main():
                          "-2: every SM on one garment)")
     ap.add_argument("--cpu-frames", type=int, default=8)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-single", action="store_true", help="skip the single-garment latency of the other shapes")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl == "reference":
