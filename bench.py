@@ -5,9 +5,11 @@
   python bench.py --impl reference --gpus N --steps K ...   (reference arm, see below)
 
 One "step" = one simulated frame (1/60 s = S substeps) of every instance on
-this GPU.  Workload C1m: 224x224 grid cloth (50,176 verts) draped
-on a moving UV sphere (8,066 verts, synthetic body motion), Swift S=4 N=10
-C=10, bending and self-collision on.  `value` = frames/s over all GPUs with the
+this GPU.  Default workload C2 (BASELINE.json configs[1]): capsule body of SMPL's
+size with a procedural pose sequence, shirt + trousers (30,050 verts) tethered
+to it, Swift S=4 N=10 C=10, bending and self-collision on.  `--workload c1` is the
+grid cloth dropped on a moving UV sphere (configs[0]; `--n 317` = 100k verts).
+`value` = frames/s over all GPUs with the
 obstacle animation resident in HBM; `e2e` = the same through host buffers
 (H2D of each frame's obstacle target, D2H of positions + normals).  Multi-GPU is
 replica sharding (independent instances, no collective on the timed path).
@@ -88,14 +90,44 @@ def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
-def build_scene(n):
-    from xrtailor_b200 import scene
-    return scene.drop_scene(n)
+class Workload:
+    """Scene + motion + optional bindings + a one-line description, for both arms.
+    c2 (default; BASELINE.json configs[1]): capsule body (8 052 verts) with a sinusoidal
+    shoulder / hip swing, shirt + trousers (30 050 verts) tethered at their top rings.
+    c1: n x n grid cloth on a moving UV sphere (configs[0]; --n 317 is the 100k-vertex case)."""
 
+    def __init__(self, args):
+        from xrtailor_b200 import scene
+        self.kind = args.workload
+        if self.kind == "c2":
+            self.sc, self.body, self.bindings = scene.body_scene()
+            self.name = (f"C2: capsule body ({len(self.sc.obs_pos)} verts), shoulder/hip swing +-30 deg at 1 Hz, shirt + "
+                         f"trousers ({len(self.sc.cloth_pos)} verts, {len(self.sc.cloth_edges)} edges, "
+                         f"{len(self.bindings[0])} tethers)")
+        else:
+            self.sc, self.body, self.bindings = scene.drop_scene(args.n), None, None
+            self.name = (f"C1m: {args.n}x{args.n} grid cloth ({len(self.sc.cloth_pos)} verts, "
+                         f"{len(self.sc.cloth_edges)} edges) on moving UV sphere ({len(self.sc.obs_pos)} verts)")
+        self.name += ", Swift S=4 N=10 C=10, bending+self-collision on"
 
-def motion_sequence(sc, frames, phase=0.0, amp=0.05):
-    from xrtailor_b200 import scene
-    return np.stack([scene.sphere_motion(sc.obs_pos, f + 1 + phase, amp=amp) for f in range(frames)])
+    def motion(self, f, phase=0.0, amp=None):
+        """Obstacle target of frame f (0-based); phase / amp vary it per instance."""
+        from xrtailor_b200 import scene
+        if self.kind == "c2":
+            return self.body.pose(f + 1, amp_deg=30.0 if amp is None else amp, phase=phase)
+        return scene.sphere_motion(self.sc.obs_pos, f + 1 + phase, amp=0.05 if amp is None else amp)
+
+    def instance(self, rng):
+        """(scene, 60-frame motion sequence) of one seed-varied instance."""
+        from xrtailor_b200 import scene
+        sc = self.sc
+        sci = scene.Scene(sc.cloth_pos + rng.uniform(-1e-4, 1e-4, sc.cloth_pos.shape).astype(np.float32),
+                          sc.cloth_tri, sc.obs_pos, sc.obs_tri)
+        if self.kind == "c2":
+            ph, amp = float(rng.uniform(0, 2 * np.pi)), float(rng.uniform(20.0, 30.0))
+        else:
+            ph, amp = float(rng.uniform(0, 30)), float(rng.uniform(0.03, 0.06))
+        return sci, np.stack([self.motion(f, ph, amp) for f in range(60)])
 
 
 def run_ours(args):
@@ -108,7 +140,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    sc = build_scene(args.n)
+    wl = Workload(args)
+    sc = wl.sc
     V, E, Vo = len(sc.cloth_pos), len(sc.cloth_edges), len(sc.obs_pos)
     cluster = args.cluster
     if cluster == -2:
@@ -126,10 +159,8 @@ def run_ours(args):
     solvers, seqs = [], []
     for i in range(M):
         # seed-varied instances: jittered cloth, phase / amplitude of the body motion
-        sci = scene.Scene(sc.cloth_pos + rng.uniform(-1e-4, 1e-4, sc.cloth_pos.shape).astype(np.float32),
-                          sc.cloth_tri, sc.obs_pos, sc.obs_tri)
-        s = scene.make_solver(sci, device=local_rank, persist_cluster=cluster)
-        seq = motion_sequence(sc, seq_len, phase=float(rng.uniform(0, 30)), amp=float(rng.uniform(0.03, 0.06)))
+        sci, seq = wl.instance(rng)
+        s = scene.make_solver(sci, device=local_rank, persist_cluster=cluster, bindings=wl.bindings)
         s.SetObstacleSequence(seq)
         solvers.append(s)
         seqs.append(seq)
@@ -164,7 +195,7 @@ def run_ours(args):
             if name in single:
                 continue
             try:
-                s1 = scene.make_solver(sc, device=local_rank, persist_cluster=shape)
+                s1 = scene.make_solver(sc, device=local_rank, persist_cluster=shape, bindings=wl.bindings)
                 s1.SetObstacleSequence(seqs[0])
                 t1 = [s1.SimulateSwift() for _ in range(25)]
                 single[name] = round(float(np.median(t1[5:])), 4)
@@ -223,16 +254,16 @@ def run_ours(args):
 
     out = None
     if rank == 0:
-        cpu = cpu_baseline(args, sc) if (world == 1 and not args.no_cpu) else None
+        cpu = cpu_baseline(args, wl) if (world == 1 and not args.no_cpu) else None
         out = {
             "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms_max / args.steps, 4), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"C1m: {args.n}x{args.n} grid cloth ({V} verts, {E} edges) on moving UV sphere "
-                                   f"({Vo} verts), Swift S=4 N=10 C=10, bending+self-collision on",
+            "config": {"workload": wl.name,
                        "instances_per_gpu": M, "parallelism": f"replicas x{world}",
-                       "l2_policy": f"inputs larger than L2: {M} garments x ~25 MB of state are cycled every step "
-                                    "(126 MB L2); one garment alone is L2 resident",
+                       "l2_policy": f"inputs larger than L2: the state of {M} garments "
+                                    f"(~{M * 0.5e-3 * V:.0f} MB) is cycled every step through the 126 MB L2; one "
+                                    "garment alone is L2 resident",
                        "single_garment_ms_per_frame": single,
                        "single_instance_ms_per_frame": round(ms_frame_single, 4),
                        "single_instance_ms_per_substep": round(ms_frame_single / 4, 4),
@@ -252,26 +283,28 @@ def run_ours(args):
     return out
 
 
-def oracle_frames(sc, frames, n_threads=1):
+def oracle_frames(wl, frames):
     """Time the CPU oracle (kind 'port') on `frames` frames of the workload."""
     import xrtailor_b200 as X
     from oracle import oracle as O
-    from xrtailor_b200 import scene
+    sc = wl.sc
     p = X.default_params()
     p.particle_diameter = sc.particle_diameter()
     cs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
     cb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
     o = O.Scene(sc, p, (cs, cb))
+    if wl.bindings is not None:
+        o.set_binding(*wl.bindings)
     t0 = time.perf_counter()
     for f in range(frames):
-        o.set_obstacle_target(scene.sphere_motion(sc.obs_pos, f + 1))
+        o.set_obstacle_target(wl.motion(f))
         o.step_frame()
     return time.perf_counter() - t0
 
 
-def cpu_baseline(args, sc):
+def cpu_baseline(args, wl):
     frames = args.cpu_frames
-    dt = oracle_frames(sc, frames)
+    dt = oracle_frames(wl, frames)
     return {"value": round(frames / dt, 4), "unit": UNIT, "cores": 1, "kind": "port",
             "sample": f"{frames} frames of the same workload on the CPU oracle (oracle/xrt_oracle.c, scalar C, 1 thread)"}
 
@@ -283,7 +316,8 @@ def run_reference(args):
     rank, local_rank, world = dist_env()
     if rank != 0:
         return
-    sc = build_scene(args.n)
+    wl = Workload(args)
+    sc = wl.sc
     ref = None
     try:
         from oracle.ref_harness import ref as ref_mod
@@ -291,20 +325,21 @@ def run_reference(args):
     except Exception:
         ref = None
     if ref is not None:
-        res = ref.time_frames(sc, steps=args.steps, warmup=args.warmup, device=local_rank)
+        res = ref.time_frames(sc, steps=args.steps, warmup=args.warmup, device=local_rank, motion=wl.motion,
+                              bindings=wl.bindings)
         value, kind, cores = res["frames_per_s"], "reference", res.get("cores", 1)
         sample = res["sample"]
         ms_step = res["ms_per_frame"]
     else:
         frames = max(1, min(args.steps, args.cpu_frames))
-        dt = oracle_frames(sc, frames)
+        dt = oracle_frames(wl, frames)
         value, kind, cores = frames / dt, "port", 1
         sample = f"{frames} frames on the CPU oracle port (the reference's CUDA harness is not built on this box)"
         ms_step = dt / frames * 1e3
     out = {"impl": "reference", "metric": METRIC, "value": round(value, 4), "unit": UNIT, "n_gpus": world,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4), "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": f"C1m: {args.n}x{args.n} grid cloth on moving UV sphere, Swift S=4 N=10 C=10"},
+           "config": {"workload": wl.name, "instances_per_gpu": 1},
            "cpu_baseline": {"value": round(value, 4), "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
            "e2e": {"value": round(value, 4), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out), flush=True)
@@ -316,6 +351,8 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c1"],
+                    help="c2: capsule body + shirt + trousers, 30k verts (BASELINE configs[1]); c1: grid cloth on a sphere")
     ap.add_argument("--n", type=int, default=224, help="cloth grid size (224 -> 50,176 verts; 317 -> 100,489)")
     ap.add_argument("--instances", type=int, default=0,
                     help="independent simulations per GPU (0: one per resident cluster)")

@@ -199,6 +199,28 @@ void* ref_create(const int* ip, const float* fp, const float* cpos, const float*
   return s;
 }
 
+// BindingConstraint::Add + Generate with the SkinParam table filled from the caller's
+// anchors (what ClothSolverSMPL::Start does with the garment's skin weights and bind_* lists)
+void ref_set_bindings(void* h, const uint* idx, const uint* tri3, const float* bary3, const float* stiff,
+                      const float* dist, int n) {
+  auto* s = (RefSolver*)h;
+  const int V = s->cloth->NumNodes();
+  thrust::host_vector<SkinParam> sk(V);
+  for (int i = 0; i < V; i++) sk[i] = SkinParam{0, 0, 0, 0.f, 0.f, 0.f};
+  std::vector<uint> bi(n);
+  std::vector<Scalar> bs(n), bd(n);
+  for (int i = 0; i < n; i++) {
+    sk[idx[i]] = SkinParam{(int)tri3[3 * i], (int)tri3[3 * i + 1], (int)tri3[3 * i + 2], bary3[3 * i],
+                           bary3[3 * i + 1], bary3[3 * i + 2]};
+    bi[i] = idx[i]; bs[i] = stiff[i]; bd[i] = dist[i];
+  }
+  s->pool->skin_params = sk;
+  s->binding = std::make_shared<BindingConstraint>();
+  s->binding->Add(bi, bs, bd, 0);
+  s->binding->Generate(pointer(s->cloth->nodes), pointer(s->obstacle->nodes), pointer(s->pool->skin_params));
+  cudaDeviceSynchronize();
+}
+
 void ref_set_obstacle_target(void* h, const float* xyz) {
   auto* s = (RefSolver*)h;
   int n = s->obstacle->NumNodes();

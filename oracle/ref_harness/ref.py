@@ -33,6 +33,7 @@ def lib():
                                  u32p, f32p, C.c_int, f32p, C.c_int, u32p, C.c_int, u32p, C.c_int]
         L.ref_create.restype = vp
         L.ref_set_obstacle_target.argtypes = [vp, f32p]; L.ref_set_obstacle_target.restype = None
+        L.ref_set_bindings.argtypes = [vp, u32p, u32p, f32p, f32p, f32p, C.c_int]; L.ref_set_bindings.restype = None
         L.ref_step_frame.argtypes = [vp]; L.ref_step_frame.restype = C.c_float
         L.ref_get_state.argtypes = [vp, C.c_int, f32p, f32p, f32p, f32p]; L.ref_get_state.restype = None
         L.ref_set_cloth_state.argtypes = [vp, f32p, f32p, f32p]; L.ref_set_cloth_state.restype = None
@@ -101,6 +102,10 @@ class RefSolver:
         lib().ref_set_colors(self.h, 0, _pu(cs), len(cs), int(cs.max()) + 1)
         lib().ref_set_colors(self.h, 1, _pu(cb), len(cb), int(cb.max()) + 1)
 
+    def set_bindings(self, idx, tri, bary, stiffness, distance):
+        k = [_u(idx), _u(tri), _f(bary), _f(stiffness), _f(distance)]
+        lib().ref_set_bindings(self.h, _pu(k[0]), _pu(k[1]), _pf(k[2]), _pf(k[3]), _pf(k[4]), len(k[0]))
+
     def set_obstacle_target(self, xyz):
         lib().ref_set_obstacle_target(self.h, _pf(_f(xyz)))
 
@@ -145,7 +150,7 @@ class RefSolver:
             self.h = None
 
 
-def time_frames(sc, steps, warmup, device=0, params=None):
+def time_frames(sc, steps, warmup, device=0, params=None, motion=None, bindings=None):
     """Reference arm of bench.py: the reference's own Solver_Total (CUDA events
     around SimulateSwift) over `steps` frames after `warmup`, same workload."""
     import xrtailor_b200 as X
@@ -154,12 +159,16 @@ def time_frames(sc, steps, warmup, device=0, params=None):
     if p.particle_diameter <= 0:
         p.particle_diameter = sc.particle_diameter()
     r = RefSolver(sc, p, device=device)
+    if bindings is not None:
+        r.set_bindings(*bindings)
+    if motion is None:
+        motion = lambda f: scene.sphere_motion(sc.obs_pos, f + 1)  # noqa: E731
     ms = []
     wall0 = None
     for f in range(warmup + steps):
         if f == warmup:
             wall0 = time.perf_counter()
-        r.set_obstacle_target(scene.sphere_motion(sc.obs_pos, f + 1))
+        r.set_obstacle_target(motion(f))
         ms.append(r.step_frame())
     wall = time.perf_counter() - wall0
     ms = np.array(ms[warmup:])

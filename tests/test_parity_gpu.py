@@ -316,3 +316,38 @@ def test_binding_constraints_vs_oracle(small, cluster):
     np.testing.assert_allclose(moved_g, moved_o, atol=2e-5)
     for obj in (s, s0):
         obj.close()
+
+
+@pytest.mark.parametrize("cluster", [0, 8])
+def test_c2_body_scene_vs_oracle(cluster):
+    """BASELINE configs[1] at oracle size: capsule body with a pose sequence, shirt + trousers
+    tethered by binding constraints; moving-obstacle contact on every limb."""
+    sc, body, bind = scene.body_scene(0.05)
+    # one substep from rest (gravity against the tethers, body still): the strict gate
+    s, o = pair(sc, bindings=bind, persist_cluster=cluster, num_substeps=1)
+    s.SimulateSwift()
+    o.step_frame()
+    assert rel_rms(s.GetPositions(0), o.positions()) <= 1e-5
+    s.close()
+    # ten frames of the pose sequence: every limb pushes cloth from the first frame on
+    s, o = pair(sc, bindings=bind, persist_cluster=cluster)
+    for f in range(10):
+        tgt = body.pose(f + 1)
+        s.UpdateObstacleAnimationFrame(tgt)
+        o.set_obstacle_target(tgt)
+        s.SimulateSwift()
+        o.step_frame()
+    g = s.GetPositions(0)
+    assert np.isfinite(g).all()
+    assert rms(g, o.positions()) <= 1e-3, rms(g, o.positions())
+    assert_bvh_equal(s.bvh(), o.bvh())
+    # nothing inside a limb: distance to each capsule's axis segment >= its radius
+    pose = body.pose(10)
+    for (name, r, *_), (_, lo, hi, _) in zip(scene._BODY_PARTS, body.parts):
+        top, bot = pose[lo].astype(np.float64), pose[hi - 1].astype(np.float64)
+        ax = (top - bot) / np.linalg.norm(top - bot)
+        a, b = top - ax * r, bot + ax * r
+        t = np.clip(((g - a) @ (b - a)) / ((b - a) @ (b - a)), 0, 1)
+        d = np.linalg.norm(g - (a + t[:, None] * (b - a)), axis=1)
+        assert d.min() >= r - 1e-3, (name, d.min(), r)
+    s.close()

@@ -159,3 +159,46 @@ def test_in_contact_within_the_references_own_spread(trio):
           "colour conflicts %d/%d" % (ours, spread, *conflicts))
     assert ours <= 3 * spread + 5e-5
     assert rms(a, b) <= 1e-3
+
+
+def test_c2_bindings_against_the_reference():
+    """Row a8 against the reference's own SolveBinding_Kernel: C2 scene at small size, ten
+    frames of the pose sequence, same colours injected on both sides."""
+    sc, body, bind = scene.body_scene(0.05)
+    p = X.default_params()
+    p.particle_diameter = sc.particle_diameter()
+    gs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
+    gb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+    # one substep from rest, body still: gravity against the tethers (the strict gate)
+    p.num_substeps = 1
+    r = R.RefSolver(sc, p)
+    r.set_colors(gs, gb)
+    r.set_bindings(*bind)
+    s = scene.make_solver(sc, colors=(gs, gb), bindings=bind, morton_fast_div=1, num_substeps=1)
+    s.SimulateSwift()
+    r.step_frame()
+    one = rel_rms(s.GetPositions(0), r.state(0)["x0"])
+    print("C2 one substep from rest, rel rms vs reference: %.2e" % one)
+    assert one <= 1e-5
+    s.close(); r.close()
+    # ten frames of the pose sequence (in contact from the first frame on)
+    p.num_substeps = 4
+    r = R.RefSolver(sc, p)
+    r.set_colors(gs, gb)
+    r.set_bindings(*bind)
+    s = scene.make_solver(sc, colors=(gs, gb), bindings=bind, morton_fast_div=1)
+    errs = []
+    for f in range(10):
+        tgt = body.pose(f + 1)
+        s.UpdateObstacleAnimationFrame(tgt)
+        r.set_obstacle_target(tgt)
+        s.SimulateSwift()
+        r.step_frame()
+        errs.append(rms(s.GetPositions(0), r.state(0)["x0"]))
+    print("C2 rms vs reference per frame:", ["%.2e" % e for e in errs])
+    # the tethers hold both garments up on both sides: the top rings stay at their anchors
+    ring = bind[0]
+    assert np.abs(s.GetPositions(0)[ring, 1] - sc.cloth_pos[ring, 1]).max() < 0.08
+    assert np.abs(r.state(0)["x0"][ring, 1] - sc.cloth_pos[ring, 1]).max() < 0.08
+    assert max(errs) <= 1e-3   # 1e-3 m RMS over 10 frames
+    s.close(); r.close()

@@ -102,6 +102,58 @@ def uv_sphere(r=0.3, stacks=64, slices=128, center=(0.0, 0.0, 0.0)):
     return pos, tri
 
 
+def lathe(rows, slices, center=(0.0, 0.0, 0.0)):
+    """Closed surface of revolution about y: rows = [(y, radius), ...] from top to bottom
+    (poles added above / below at the first / last row's y + / - its radius... see capsule)."""
+    rows = np.asarray(rows, np.float64)
+    ph = 2 * np.pi * np.arange(slices, dtype=np.float64) / slices
+    ring = np.stack([np.outer(rows[:, 1], np.cos(ph)), np.repeat(rows[:, :1], slices, 1),
+                     np.outer(rows[:, 1], np.sin(ph))], -1).reshape(-1, 3)
+    return ring, len(rows)
+
+
+def capsule(r, h, slices=32, hemi=8, cyl=20, center=(0.0, 0.0, 0.0)):
+    """Capsule with its axis on y: cylinder of height h (cyl rows) capped by two hemispheres
+    (hemi rows each), outward normals.  (2*hemi + cyl - 1) * slices + 2 vertices."""
+    th = 0.5 * np.pi * np.arange(1, hemi + 1, dtype=np.float64) / hemi           # (0, pi/2]
+    top = [(h / 2 + r * np.cos(t), r * np.sin(t)) for t in th]
+    mid = [(h / 2 - h * k / cyl, r) for k in range(1, cyl)]
+    bot = [(-h / 2 - r * np.cos(t), r * np.sin(t)) for t in th[::-1]]
+    ring, nrows = lathe(top + mid + bot, slices)
+    pos = np.concatenate([[[0, h / 2 + r, 0]], ring, [[0, -h / 2 - r, 0]]])
+    s = np.arange(slices)
+    s1 = (s + 1) % slices
+    tris = [np.stack([np.zeros(slices, np.int64), 1 + s1, 1 + s], 1)]
+    for k in range(nrows - 1):
+        a, b = 1 + k * slices, 1 + (k + 1) * slices
+        tris.append(np.stack([a + s, a + s1, b + s1], 1))
+        tris.append(np.stack([a + s, b + s1, b + s], 1))
+    a = 1 + (nrows - 1) * slices
+    tris.append(np.stack([np.full(slices, a + slices), a + s, a + s1], 1))
+    tri = np.concatenate(tris).astype(np.uint32)
+    pos = pos.astype(np.float32)
+    fn = np.cross(pos[tri[:, 1]] - pos[tri[:, 0]], pos[tri[:, 2]] - pos[tri[:, 0]])
+    flip = (pos[tri].mean(1) * fn).sum(1) < 0
+    tri[flip] = tri[flip][:, [0, 2, 1]]
+    return pos + np.asarray(center, np.float32), tri
+
+
+def tube_cloth(r, y_top, y_bot, n_around, n_high, center_xz=(0.0, 0.0), jitter=1e-4, rng=None):
+    """Open cylinder of cloth about a vertical axis (C2 garments); row 0 is the top ring."""
+    ph = 2 * np.pi * np.arange(n_around, dtype=np.float64) / n_around
+    ys = np.linspace(y_top, y_bot, n_high)
+    pos = np.stack([np.tile(center_xz[0] + r * np.cos(ph), n_high), np.repeat(ys, n_around),
+                    np.tile(center_xz[1] + r * np.sin(ph), n_high)], 1).astype(np.float32)
+    if rng is not None and jitter > 0:
+        pos += rng.uniform(-jitter, jitter, pos.shape).astype(np.float32)
+    i, j = np.meshgrid(np.arange(n_high - 1), np.arange(n_around), indexing="ij")
+    v00 = (i * n_around + j).ravel()
+    v01 = (i * n_around + (j + 1) % n_around).ravel()
+    v10, v11 = v00 + n_around, v01 + n_around
+    tri = np.concatenate([np.stack([v00, v01, v11], 1), np.stack([v00, v11, v10], 1)]).astype(np.uint32)
+    return pos, tri
+
+
 class Scene:
     """Everything AddCloth/AddObstacle + the constraint generators hand to the solver."""
 
@@ -160,3 +212,83 @@ def make_solver(scene, colors=None, bindings=None, **params):
         s.SetColors(1, colors[1])
     s.Start()
     return s
+
+
+# ---- C2: capsule body with a procedural pose sequence, shirt + trousers ----------
+# (SMPL's own topology is a licensed download and not in the archive, so
+# the body is a union of six capsules of SMPL's size: ~7k vertices / ~14k faces.)
+_BODY_PARTS = (
+    # name, radius, cylinder height, centre at rest, joint the part swings about, slices, hemi, cyl rows
+    ("torso", 0.150, 0.43, (0.00, 1.235, 0.0), None, 48, 12, 20),
+    ("head", 0.095, 0.05, (0.00, 1.72, 0.0), None, 32, 10, 2),
+    ("arm_l", 0.045, 0.52, (0.235, 1.15, 0.0), (0.235, 1.41, 0.0), 20, 5, 30),
+    ("arm_r", 0.045, 0.52, (-0.235, 1.15, 0.0), (-0.235, 1.41, 0.0), 20, 5, 30),
+    ("leg_l", 0.070, 0.74, (0.085, 0.49, 0.0), (0.085, 0.90, 0.0), 32, 8, 42),
+    ("leg_r", 0.070, 0.74, (-0.085, 0.49, 0.0), (-0.085, 0.90, 0.0), 32, 8, 42),
+)
+
+
+class Body:
+    """Obstacle mesh of the C2 scene and its pose function."""
+
+    def __init__(self):
+        pos, tri, self.parts = [], [], []
+        base = 0
+        for name, r, h, c, joint, sl, hemi, cyl in _BODY_PARTS:
+            p, t = capsule(r, h, sl, hemi, cyl, center=c)
+            pos.append(p)
+            tri.append(t + base)
+            self.parts.append((name, base, base + len(p), joint))
+            base += len(p)
+        self.rest = np.concatenate(pos).astype(np.float32)
+        self.tri = np.concatenate(tri).astype(np.uint32)
+
+    def pose(self, frame, amp_deg=30.0, hz=1.0, fps=60.0, phase=0.0):
+        """Sinusoidal shoulder / hip swing about the x axis: arms and legs in opposite phase."""
+        t = frame / fps
+        a = np.deg2rad(amp_deg) * np.sin(2 * np.pi * hz * t + phase)
+        out = self.rest.copy()
+        for name, lo, hi, joint in self.parts:
+            if joint is None:
+                continue
+            ang = a if name in ("arm_l", "leg_r") else -a
+            c, s = np.float32(np.cos(ang)), np.float32(np.sin(ang))
+            j = np.asarray(joint, np.float32)
+            d = self.rest[lo:hi] - j
+            out[lo:hi, 1] = j[1] + c * d[:, 1] - s * d[:, 2]
+            out[lo:hi, 2] = j[2] + s * d[:, 1] + c * d[:, 2]
+        return out
+
+
+def body_scene(scale=1.0, seed=SEED, gap=0.012):
+    """C2: shirt (~18k verts) around the torso and two trouser legs (~6k verts each) around the
+    legs, `gap` metres off the body.  The top ring of each garment is tethered to the body with
+    binding constraints (what the reference's SMPL pipeline does with its bind_* lists,
+    BindingConstraint.cu:11-55): anchor = nearest body vertex, rest length = distance at setup.
+    scale < 1 coarsens the garments for the oracle-sized tests.
+    Returns (Scene, Body, bindings) with bindings = (cloth_idx, tri, bary, stiffness, distance)."""
+    rng = np.random.default_rng(seed)
+    body = Body()
+    k = float(np.sqrt(scale))
+    na_s, nh_s = max(24, int(190 * k)), max(12, int(95 * k))
+    na_p, nh_p = max(16, int(80 * k)), max(12, int(75 * k))
+    sp, st = tube_cloth(0.150 + gap, 1.44, 1.04, na_s, nh_s, rng=rng)
+    lp, lt = tube_cloth(0.070 + gap, 0.84, 0.22, na_p, nh_p, center_xz=(0.085, 0.0), rng=rng)
+    rp, rt = tube_cloth(0.070 + gap, 0.84, 0.22, na_p, nh_p, center_xz=(-0.085, 0.0), rng=rng)
+    pos = np.concatenate([sp, lp, rp])
+    tri = np.concatenate([st, lt + len(sp), rt + len(sp) + len(lp)])
+    o1, o2 = len(sp), len(sp) + len(lp)
+    ring = np.array(list(range(na_s)) + list(range(o1, o1 + na_p)) + list(range(o2, o2 + na_p)), np.uint32)
+    sc = Scene(pos, tri, body.rest, body.tri)
+    # anchor of a ring vertex: the nearest body vertex, as corner 0 of one of its triangles
+    d = ((pos[ring][:, None, :] - body.rest[None, :, :]) ** 2).sum(-1)
+    near = d.argmin(1)
+    first_tri = np.full(len(body.rest), -1, np.int64)
+    for c in range(3):
+        first_tri[body.tri[::-1, c]] = np.arange(len(body.tri))[::-1]
+    t = body.tri[first_tri[near]]
+    corner = (t == near[:, None]).argmax(1)
+    bary = np.zeros((len(ring), 3), np.float32)
+    bary[np.arange(len(ring)), corner] = 1.0
+    bindings = (ring, t.astype(np.uint32), bary, np.ones(len(ring), np.float32), np.zeros(len(ring), np.float32))
+    return sc, body, bindings
