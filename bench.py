@@ -270,7 +270,7 @@ def run_ours(args):
                        "persist_cluster": cluster, "colors": [st["n_stretch_colors"], st["n_bend_colors"]]},
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(M * Vo * 12),
                     "d2h_bytes_per_step": int(M * V * 12 * 2)},
-            "gpu_launches": int(st["launches_per_frame"] * M * args.steps),
+            "gpu_launches": int(st["launches_per_frame"] * M * args.steps * world),
             "clocks": clk.summary(), "roofline": roofline,
         }
         if cpu:
