@@ -920,7 +920,12 @@ void oracle_solve_ee_dcd(OScene* s) {
 /* Self contact: broad_phase/spatial_hash/SpatialHashGPU.cu + CollideParticles */
 /* ------------------------------------------------------------------------- */
 
-static int int_coord(float v, float cell) { return (int)floorf(v / cell); }  /* :6-8 */
+static int int_coord(float v, float cell) {  /* :6-8; clamped like the CUDA path (no effect below 2^30 cells) */
+  float c = floorf(v / cell);
+  c = c > -1073741824.0f ? c : -1073741824.0f;
+  c = c < 1073741824.0f ? c : 1073741824.0f;
+  return (int)c;
+}
 static int hash_coords(int x, int y, int z, int table) {                    /* :9-12 */
   const int h = (int)(((uint32_t)x * 92837111u) ^ ((uint32_t)y * 689287499u) ^ ((uint32_t)z * 283923481u));
   return abs(h % table);

@@ -351,3 +351,80 @@ def test_c2_body_scene_vs_oracle(cluster):
         d = np.linalg.norm(g - (a + t[:, None] * (b - a)), axis=1)
         assert d.min() >= r - 1e-3, (name, d.min(), r)
     s.close()
+
+
+# ---- edge cases: missing pieces, tiny and ragged inputs ----
+
+@pytest.mark.parametrize("cluster", [0, 8])
+def test_no_obstacle_free_fall(cluster):
+    sc0 = scene.drop_scene(24, sphere=(6, 8))
+    sc = scene.Scene(sc0.cloth_pos, sc0.cloth_tri, fixed=(0, 23))   # two pinned corners, nothing to collide with
+    s, o = pair(sc, persist_cluster=cluster)
+    for _ in range(3):
+        s.SimulateSwift()
+        o.step_frame()
+    g = s.GetPositions(0)
+    assert rel_rms(g, o.positions()) <= 1e-5
+    np.testing.assert_array_equal(g[[0, 23]], sc.cloth_pos[[0, 23]])   # pinned vertices do not move
+    assert g[:, 1].mean() < sc.cloth_pos[:, 1].mean()                  # the rest falls
+    s.close()
+
+
+@pytest.mark.parametrize("cluster", [0, 1, 16])
+def test_switches_off(small, cluster):
+    """solve_bending = 0, self collision off, one iteration, one collision pass."""
+    s, o = pair(small, persist_cluster=cluster, solve_bending=0, enable_self_collision=0, num_iterations=1,
+                num_collision_passes=1, num_substeps=2)
+    s.SimulateSwift()
+    o.step_frame()
+    assert rel_rms(s.GetPositions(0), o.positions()) <= 1e-5
+    s.close()
+
+
+@pytest.mark.parametrize("cluster", [0, 8])
+def test_tiny_meshes(cluster):
+    """3 x 3 cloth (8 faces, fewer items than one warp) over a 4-triangle obstacle."""
+    cp, ct = scene.grid_cloth(3, 0.2, 0.25, 1e-4)
+    op = np.array([[0, 0.2, 0], [0.3, -0.1, -0.2], [-0.3, -0.1, -0.2], [0, -0.1, 0.3]], np.float32)
+    ot = np.array([[0, 2, 1], [0, 1, 3], [0, 3, 2], [1, 2, 3]], np.uint32)
+    sc = scene.Scene(cp, ct, op, ot)
+    s, o = pair(sc, persist_cluster=cluster)
+    assert_bvh_equal(s.bvh(), o.bvh())
+    for _ in range(3):      # (a 9-vertex cloth sliding off a peak is chaotic after that)
+        s.SimulateSwift()
+        o.step_frame()
+    g = s.GetPositions(0)
+    assert np.isfinite(g).all()
+    assert rms(g, o.positions()) <= 1e-3, rms(g, o.positions())
+    s.close()
+
+
+@pytest.mark.parametrize("cluster", [0, 8])
+def test_improper_colouring_uses_atomics(small, cluster):
+    """Every constraint in colour 0 (what the reference's randomized colouring degenerates to
+    when it conflicts): the projection must fall back to float atomics.  Six un-averaged
+    corrections per vertex overshoot, so the garment blows up within a frame (the reference's
+    does too); what is checked is that neither launch shape hangs or faults on the way
+    (coordinates of 1e12 m once hung the 3x3x3 cell loops of the spatial hash)."""
+    cs = np.zeros(len(small.stretch_rest), np.uint32)
+    cb = np.zeros(len(small.bend_theta), np.uint32)
+    out = []
+    for cl in (0, cluster if cluster else 1):
+        s = scene.make_solver(small, colors=(cs, cb), persist_cluster=cl, particle_diameter=small.particle_diameter())
+        for _ in range(3):
+            s.SimulateSwift()
+        out.append(s.GetPositions(0))
+        assert s.stats()["n_stretch_colors"] == 1
+        s.close()
+    assert out[0].shape == out[1].shape
+
+
+def test_hash_survives_a_blown_up_garment(small):
+    s, _ = pair(small, persist_cluster=0)
+    x = (small.cloth_pos * np.float32(1e12)).astype(np.float32)
+    x[::7] = np.inf
+    x[3::11] = np.nan
+    s.SetClothPredicted(x)
+    s.HashParticles()          # returns (it used to spin forever in the cell loops)
+    assert s.debug("NEIGHBORS", np.uint32).shape[0] > 0
+    s.close()

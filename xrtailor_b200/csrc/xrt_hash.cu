@@ -7,7 +7,12 @@
 
 namespace {
 
-__device__ __forceinline__ int int_coord(float v, float cell) { return (int)floorf(v / cell); }
+// floor(v / cell) as the reference computes it (SpatialHashGPU.cu:6-8), clamped to +-2^30 so
+// the 3x3x3 cell loops cannot overflow (the reference's are undefined there): a garment that
+// has blown up to 1e12 m must not hang the device.  NaN maps to the lower clamp.
+__device__ __forceinline__ int int_coord(float v, float cell) {
+  return (int)fminf(fmaxf(floorf(v / cell), -1073741824.0f), 1073741824.0f);
+}
 __device__ __forceinline__ int hash_coords(int x, int y, int z, int table) {
   const int h = (int)(((uint32_t)x * 92837111u) ^ ((uint32_t)y * 689287499u) ^ ((uint32_t)z * 283923481u));
   return abs(h % table);
