@@ -255,6 +255,24 @@ int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts,
                              uint32_t* nodes, float* aabbs,
                              int32_t* esc_int, int32_t* esc_ext, float* build_ms);
 
+/* Face-face broad phase between two triangle meshes (F_r == 0: the left mesh
+ * against itself).  Replaces BVH::Traverse / TraverseSelf with
+ * CountPairs_Kernel + thrust::inclusive_scan + FindPairs_Kernel
+ * (xrtailor/src/physics/broad_phase/lbvh/BVH.cu:1149-1340, callers
+ * :1342-1400): both trees are built here (UpdateData(ccd=false)+Construct),
+ * each left leaf box is dilated by `thickness` (Bounds.cu:95-128) and walked
+ * through the right tree.  pairs: uint32[2*capacity] rows (left face, right
+ * face) in the reference's order.  *n_pairs is always the full count; call
+ * with pairs == NULL to size the buffer (XRT_ERR_INVALID if capacity is too
+ * small).  traverse_ms times count + scan + fill on the device. */
+int xrt_traverse_pairs_standalone(const float* pos_l, uint32_t nv_l,
+                                  const uint32_t* tri_l, uint32_t F_l,
+                                  const float* pos_r, uint32_t nv_r,
+                                  const uint32_t* tri_r, uint32_t F_r,
+                                  float thickness, int morton_fast_div,
+                                  int device, uint32_t* pairs, size_t capacity,
+                                  size_t* n_pairs, float* traverse_ms);
+
 #ifdef __cplusplus
 }
 #endif

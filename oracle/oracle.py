@@ -34,6 +34,7 @@ def _load():
                  ("esc_ext", i32p), ("pred", f32p)]:
         f = getattr(L, "oracle_bvh_" + n); f.argtypes = [vp]; f.restype = t
     L.oracle_bvh_used64.argtypes = [vp]; L.oracle_bvh_used64.restype = C.c_int
+    L.oracle_traverse_pairs.argtypes = [vp, vp, C.c_float, u32p, C.c_size_t]; L.oracle_traverse_pairs.restype = C.c_size_t
     L.oracle_nearest_point_f.argtypes = [f32p, f32p, f32p]; L.oracle_nearest_point_f.restype = C.c_float
     L.oracle_ray_intersect_f.argtypes = [f32p, f32p, C.c_float, f32p]; L.oracle_ray_intersect_f.restype = C.c_float
     L.oracle_closest_seg_seg_f.argtypes = [f32p, f32p, f32p]; L.oracle_closest_seg_seg_f.restype = C.c_float
@@ -132,6 +133,16 @@ class Bvh:
         p2 = _f(p2) if p2 is not None else None
         n = L.oracle_query_f(self.h, kind, _pf(p1), _pf(p2), _pu(out))
         return out[:n].copy()
+
+    def pairs(self, other=None, thickness=0.0):
+        """CountPairs + scan + FindPairs (BVH.cu:1149-1340): (lhs face, rhs face) rows in the reference's order;
+        other=None is the self traversal."""
+        o = other if other is not None else self
+        n = L.oracle_traverse_pairs(self.h, o.h, thickness, None, 0)
+        out = np.zeros((n, 2), np.uint32)
+        if n:
+            L.oracle_traverse_pairs(self.h, o.h, thickness, _pu(out), n)
+        return out
 
     def __del__(self):
         if getattr(self, "h", None):

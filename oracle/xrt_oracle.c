@@ -290,6 +290,46 @@ void oracle_bvh_refit_midstep(OBvh* b, const float* x1, const float* n1, const u
   if (b->F > 1) refit_internal(b, 0);
 }
 
+/* CountPairs_Kernel + thrust::inclusive_scan + FindPairs_Kernel, BVH.cu:1149-1238 (self variants :1240-1340
+ * are the same walk with lhs == rhs).  Overlap test: Bounds::Overlap(b, thickness) = Overlap(b.Dilate(thickness)),
+ * Bounds.cu:95-128.  Pairs are (object of the lhs leaf, object of the rhs leaf); leaf `id` owns
+ * pairs[scan[id-1] .. scan[id]-1] and fills it from the top down.  Returns the total; writes at most cap pairs. */
+static size_t pairs_walk(const OBvh* l, const OBvh* r, float th, uint32_t id, uint32_t* out /* NULL: count */, long index) {
+  const uint32_t nl = l->F - 1 + id, ni = r->F - 1;
+  const float* a = l->aabb + 6 * (size_t)nl;
+  const float q[6] = {a[0] - th, a[1] - th, a[2] - th, a[3] + th, a[4] + th, a[5] + th};
+  const uint32_t obj_l = l->nodes[4 * (size_t)nl + 3];
+  size_t n = 0;
+  int node = 0;
+  while (node != -1) {
+    const float* b = r->aabb + 6 * (size_t)node;
+    const uint32_t obj = r->nodes[4 * (size_t)node + 3];
+    const int leaf = obj != 0xFFFFFFFFu;
+    int hit = 1;
+    for (int k = 0; k < 3; k++)
+      if (b[k] > q[3 + k] || b[3 + k] < q[k]) hit = 0;
+    if (hit && leaf) {
+      if (out) { out[2 * index] = obj_l; out[2 * index + 1] = obj; index--; }
+      n++;
+    }
+    if (hit && !leaf) node = (int)r->nodes[4 * (size_t)node + 1];
+    else node = leaf ? r->esc_ext[(uint32_t)node - ni] : r->esc_int[node];
+  }
+  return n;
+}
+size_t oracle_traverse_pairs(const OBvh* l, const OBvh* r, float thickness, uint32_t* pairs, size_t cap) {
+  size_t* scan = (size_t*)malloc(sizeof(size_t) * l->F);
+  size_t total = 0;
+  for (uint32_t id = 0; id < l->F; id++) {
+    total += pairs_walk(l, r, thickness, id, NULL, 0);
+    scan[id] = total;
+  }
+  if (pairs && cap >= total)
+    for (uint32_t id = 0; id < l->F; id++) pairs_walk(l, r, thickness, id, pairs, (long)scan[id] - 1);
+  free(scan);
+  return total;
+}
+
 /* accessors for ctypes */
 uint32_t* oracle_bvh_morton(OBvh* b) { return b->morton; }
 uint32_t* oracle_bvh_object(OBvh* b) { return b->object; }

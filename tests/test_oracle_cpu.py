@@ -243,3 +243,55 @@ def test_binding_known_answer():
     y = o.predicted()
     np.testing.assert_allclose(y[0], anchor[0] + [0, 1.0 - 0.5 * 0.75, 0], atol=1e-6)
     np.testing.assert_array_equal(y[1], x[1])
+
+
+def _leaf_boxes(pos, tri):
+    p = pos[tri]
+    return p.min(1), p.max(1)
+
+
+def _brute_pairs(pl, tl, pr, tr, th):
+    lo_l, hi_l = _leaf_boxes(pl, tl)
+    lo_r, hi_r = _leaf_boxes(pr, tr)
+    lo_q, hi_q = lo_l - np.float32(th), hi_l + np.float32(th)
+    hit = np.all((lo_r[None] <= hi_q[:, None]) & (hi_r[None] >= lo_q[:, None]), axis=2)
+    return {(int(a), int(b)) for a, b in zip(*np.nonzero(hit))}
+
+
+@pytest.mark.parametrize("th", [0.0, 2e-3])
+def test_pair_traversal_equals_brute_force_and_keeps_the_reference_order(th):
+    # BVH.cu:1149-1238: every overlapping leaf pair exactly once, grouped by lhs leaf in sorted order
+    pl, tl = scene.grid_cloth(21, 0.5, 0.29, 1e-4)
+    pr, tr = scene.uv_sphere(0.3, 12, 20)
+    bl, br = O.Bvh(pl, tl), O.Bvh(pr, tr)
+    got = bl.pairs(br, th)
+    want = _brute_pairs(pl, tl, pr, tr, th)
+    assert len(got) == len(want) > 0
+    assert {(int(a), int(b)) for a, b in got} == want
+    order = {int(o): i for i, o in enumerate(bl.arrays()["object"])}
+    rank = np.array([order[int(a)] for a in got[:, 0]])
+    assert np.all(np.diff(rank) >= 0)
+    # within one lhs leaf the rhs leaves come out in reverse traversal (= descending sorted-leaf) order
+    r_order = {int(o): i for i, o in enumerate(br.arrays()["object"])}
+    for leaf in np.unique(rank)[:50]:
+        rr = [r_order[int(b)] for b in got[rank == leaf, 1]]
+        assert rr == sorted(rr, reverse=True)
+
+
+def test_pair_traversal_self_has_the_diagonal_and_is_symmetric():
+    # CountPairsSelf/FindPairsSelf, BVH.cu:1240-1340: lhs == rhs, nothing filtered at this stage
+    pl, tl = scene.grid_cloth(17, 0.5, 0.0, 1e-4)
+    b = O.Bvh(pl, tl)
+    got = {(int(a), int(c)) for a, c in b.pairs(None, 1e-3)}
+    assert got == _brute_pairs(pl, tl, pl, tl, 1e-3)
+    assert all((a, a) in got for a in range(len(tl)))
+    assert all((c, a) in got for a, c in got)
+
+
+def test_pair_traversal_disjoint_and_single_face():
+    pl, tl = scene.grid_cloth(5, 0.5, 5.0, 0.0)
+    pr, tr = scene.uv_sphere(0.3, 6, 8)
+    assert len(O.Bvh(pl, tl).pairs(O.Bvh(pr, tr), 1e-3)) == 0
+    one = np.array([[0, 1, 2]], np.uint32)
+    p3 = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    np.testing.assert_array_equal(O.Bvh(p3, one).pairs(None, 0.0), [[0, 0]])

@@ -50,6 +50,39 @@ def test_bvh_tiny():
                          O.Bvh(pos, np.array(tri, np.uint32)).arrays())
 
 
+@pytest.mark.parametrize("n,sph,th", [(8, (4, 6), 1e-3), (65, (16, 32), 0.0), (224, (64, 128), 2e-3)])
+def test_pair_traversal_bit_exact_and_ordered(n, sph, th):
+    # BVH::Traverse = CountPairs + inclusive_scan + FindPairs (BVH.cu:1149-1238): same rows in the same order
+    pl, tl = scene.grid_cloth(n, 1.0, 0.3, 1e-4)
+    pr, tr = scene.uv_sphere(0.3, *sph)
+    want = O.Bvh(pl, tl).pairs(O.Bvh(pr, tr), th)
+    got = X.traverse_pairs(pl, tl, pr, tr, thickness=th, fast_div=0)
+    assert len(want) > 0
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("n", [3, 40, 150])
+def test_pair_traversal_self_bit_exact(n):
+    # TraverseSelf (BVH.cu:1240-1340)
+    pl, tl = scene.grid_cloth(n, 1.0, 0.0, 1e-4)
+    np.testing.assert_array_equal(X.traverse_pairs(pl, tl, thickness=1e-3, fast_div=0), O.Bvh(pl, tl).pairs(None, 1e-3))
+
+
+def test_pair_traversal_edge_cases():
+    pl, tl = scene.grid_cloth(5, 0.5, 5.0, 0.0)
+    pr, tr = scene.uv_sphere(0.3, 6, 8)
+    assert X.traverse_pairs(pl, tl, pr, tr, thickness=1e-3, fast_div=0).shape == (0, 2)  # disjoint
+    one = np.array([[0, 1, 2]], np.uint32)
+    p3 = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    np.testing.assert_array_equal(X.traverse_pairs(p3, one, fast_div=0), [[0, 0]])  # one-leaf tree against itself
+    np.testing.assert_array_equal(X.traverse_pairs(p3, one, pr, tr, thickness=2.0, fast_div=0),
+                                  O.Bvh(p3, one).pairs(O.Bvh(pr, tr), 2.0))  # everything overlaps
+    # duplicate Morton codes (64-bit key path) on both sides
+    pd, td = scene.grid_cloth(20, jitter=0.0)
+    td = np.concatenate([td, td])
+    np.testing.assert_array_equal(X.traverse_pairs(pd, td, thickness=1e-3, fast_div=0), O.Bvh(pd, td).pairs(None, 1e-3))
+
+
 def test_refit_midstep_bit_exact_boxes(small):
     s, o = pair(small)
     tgt = scene.sphere_motion(small.obs_pos, 7)

@@ -52,6 +52,7 @@ SYMBOLS = [
     "xrt_set_cloth_state", "xrt_set_cloth_predicted", "xrt_bvh_build_obstacle", "xrt_bvh_refit_obstacle", "xrt_generate_contacts",
     "xrt_hash_particles", "xrt_predict", "xrt_solve_iteration", "xrt_finalize", "xrt_debug_get",
     "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone", "xrt_persist_info", "xrt_batch_profile_substep", "xrt_add_binding",
+    "xrt_traverse_pairs_standalone",
 ]
 
 
@@ -97,6 +98,8 @@ def _load():
         "xrt_persist_info": [C.c_int, i32p, i32p],
         "xrt_bvh_build_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, C.c_int, C.c_int, u32p, u32p, u32p, f32p,
                                      i32p, i32p, f32p],
+        "xrt_traverse_pairs_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, f32p, C.c_uint32, u32p, C.c_uint32,
+                                          C.c_float, C.c_int, C.c_int, u32p, C.c_size_t, C.POINTER(C.c_size_t), f32p],
     }
     for name, args in sig.items():
         fn = getattr(L, name)

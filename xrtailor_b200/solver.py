@@ -293,3 +293,24 @@ def bvh_build_standalone(positions, indices, fast_div=1, device=0):
     out["esc_int"] = out["esc_int"][:F - 1]
     out["build_ms"] = ms.value
     return out
+
+
+def traverse_pairs(positions, indices, other_positions=None, other_indices=None, thickness=0.0, fast_div=1, device=0,
+                   timing=False):
+    """BVH::Traverse (two meshes) / TraverseSelf (other_* = None), BVH.cu:1342-1400: face-face candidate rows
+    (left face, right face) in the reference's order, on the GPU."""
+    pl, tl = _f32(positions).reshape(-1, 3), _u32(indices).reshape(-1, 3)
+    self_mode = other_indices is None
+    pr = None if self_mode else _f32(other_positions).reshape(-1, 3)
+    tr = None if self_mode else _u32(other_indices).reshape(-1, 3)
+    n, ms = C.c_size_t(0), C.c_float()
+    args = (_pf(pl), len(pl), _pu(tl), len(tl), _pf(pr), 0 if self_mode else len(pr), _pu(tr),
+            0 if self_mode else len(tr), thickness, fast_div, device)
+    rc = lib.xrt_traverse_pairs_standalone(*args, None, 0, C.byref(n), None)
+    if rc:
+        raise XrtError(rc, "pair traversal failed (no CUDA device? there is no CPU fallback)")
+    out = np.zeros((n.value, 2), np.uint32)
+    rc = lib.xrt_traverse_pairs_standalone(*args, _pu(out), n.value, C.byref(n), C.byref(ms))
+    if rc:
+        raise XrtError(rc, "pair traversal failed")
+    return (out, ms.value) if timing else out
