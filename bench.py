@@ -243,7 +243,8 @@ def run_ours(args):
     achieved = k_bytes / (k_ms * 1e-3) / 1e9
     if os.path.exists(tf):
         try:
-            traffic = json.load(open(tf)).get(kname)
+            tj = json.load(open(tf))
+            traffic = tj.get(f"{kname}:{wl.kind}", tj.get(kname))
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "kernel": kname, "achieved": round(achieved, 2), "peak": peak,
