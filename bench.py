@@ -154,10 +154,17 @@ def run_ours(args):
         resident = 8
     # one garment per resident cluster: every instance steps concurrently on its own SMs
     M = args.instances if args.instances > 0 else max(1, resident)
+    shared = bool(args.shared) and cluster >= 1
+    # end to end, shared launches: the garments step as several small batches that take turns on the host,
+    # so only one batch at a time has its SMs idle while its frames cross PCIe (no oversubscription: a
+    # queued substep kernel would starve the small per-garment kernels of SMs)
+    n_e2e_batches = max(1, min(args.e2e_batches, M)) if shared else 1
+    M_e2e = (M // n_e2e_batches) * n_e2e_batches if shared else M
+    M_all = max(M, M_e2e)
     rng = np.random.default_rng(SEED + rank)
     seq_len = 60
     solvers, seqs = [], []
-    for i in range(M):
+    for i in range(M_all):
         # seed-varied instances: jittered cloth, phase / amplitude of the body motion
         sci, seq = wl.instance(rng)
         s = scene.make_solver(sci, device=local_rank, persist_cluster=cluster, bindings=wl.bindings)
@@ -172,10 +179,13 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---- device-resident throughput -------------------------------------
-    X.batch_run(solvers, args.warmup)
+    batch = X.Batch(solvers[:M], groups=args.groups, workers=args.workers) if shared else None
+    launches_shared = batch.launches_per_frame(True) if shared else 0
+    run = batch.run if shared else (lambda frames: X.batch_run(solvers[:M], frames))
+    run(args.warmup)
     barrier()
     with ClockSampler(local_rank) as clk:
-        ms = X.batch_run(solvers, args.steps)
+        ms = run(args.steps)
     barrier()
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -191,7 +201,7 @@ def run_ours(args):
     single = {f"cluster{cluster}" if cluster > 0 else ("grid" if cluster == -2 else "per_stage_graph"):
               round(ms_frame_single, 4)}
     if rank == 0 and not args.no_single:
-        for name, shape in (("grid", -2), ("per_stage_graph", 0), ("cluster16", 16)):
+        for name, shape in (("grid", -2), ("per_stage_graph", 0), ("cluster16", 16), ("cluster8", 8)):
             if name in single:
                 continue
             try:
@@ -204,24 +214,50 @@ def run_ours(args):
                 single[name] = f"unavailable: {e}"
 
     # ---- end to end through host buffers ---------------------------------
-    xyz = [np.empty((V, 3), np.float32) for _ in range(M)]
+    xyz = [np.empty((V, 3), np.float32) for _ in range(M_e2e)]
+    if shared:
+        batch.close()
+        per = M_e2e // n_e2e_batches
+        e2e_batches = [X.Batch(solvers[k * per:(k + 1) * per], groups=1, workers=max(0, 32 // n_e2e_batches - 1))
+                       for k in range(n_e2e_batches)]
+        for b in e2e_batches:
+            b.run(1)
     barrier()
     t0 = time.perf_counter()
-    # per instance: read back frame f-1 (D2H positions + normals, SaveCache), upload frame f's
-    # obstacle target (H2D), enqueue frame f; the other instances keep the GPU busy meanwhile
-    for f in range(args.steps + 1):
-        for i, s in enumerate(solvers):
-            if f > 0:
-                xyz[i], _nrm = s.GetPositions(0, normals=True)
-            if f < args.steps:
-                s.UpdateObstacleAnimationFrame(seqs[i][f % seq_len])
-                s.SimulateSwiftAsync()
+    if shared:
+        # per batch: read back frame f-1 of its garments (D2H positions + normals into host arrays, SaveCache),
+        # upload their frame-f obstacle targets from host arrays (H2D), enqueue frame f as shared launches;
+        # the other batches compute meanwhile
+        out_xyz = [np.empty((per * V, 3), np.float32) for _ in e2e_batches]
+        out_nrm = [np.empty((per * V, 3), np.float32) for _ in e2e_batches]
+        tgt = [np.stack([np.concatenate([seqs[k * per + j][f] for j in range(per)]) for f in range(seq_len)])
+               for k in range(n_e2e_batches)]  # host-side animation source, [seq_len][per * Vo][3]
+        for f in range(args.steps + 1):
+            for k, b in enumerate(e2e_batches):
+                if f > 0:
+                    b.GetPositions(0, out_xyz[k], out_nrm[k])
+                if f < args.steps:
+                    b.UpdateObstacleAnimationFrames(tgt[k][f % seq_len])
+                    b.SimulateSwiftAsync()
+        for b in e2e_batches:
+            b.Sync()
+        xyz = out_xyz
+    else:
+        # per instance: read back frame f-1 (D2H positions + normals, SaveCache), upload frame f's
+        # obstacle target (H2D), enqueue frame f; the other instances keep the GPU busy meanwhile
+        for f in range(args.steps + 1):
+            for i, s in enumerate(solvers):
+                if f > 0:
+                    xyz[i], _nrm = s.GetPositions(0, normals=True)
+                if f < args.steps:
+                    s.UpdateObstacleAnimationFrame(seqs[i][f % seq_len])
+                    s.SimulateSwiftAsync()
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = frames_total / float(t.item())
+    e2e_value = world * M_e2e * args.steps / float(t.item())
     assert all(np.isfinite(a).all() for a in xyz)
 
     # ---- roofline of the dominant kernel ----------------------------------
@@ -231,10 +267,17 @@ def run_ours(args):
     if cluster != 0:
         # the persistent substep kernel, timed as it runs in the batch: one round = M launches
         # side by side on disjoint clusters; bytes = algorithmic bytes of those M launches
-        kname = "swift_substep_kernel"
-        k_ms, k_bytes = X.batch_profile_substep(solvers, reps=8)
+        kname = "swift_substep_batch_kernel" if shared else "swift_substep_kernel"
+        if shared:
+            for b in e2e_batches:
+                b.close()
+            batch = X.Batch(solvers[:M], groups=1, workers=0)  # one launch carries all M garments
+            k_ms, k_bytes = batch.profile(reps=4)
+            batch.close()
+        else:
+            k_ms, k_bytes = X.batch_profile_substep(solvers[:M], reps=8)
         solo_ms, solo_bytes = solvers[0].ProfileKernel(5, reps=8)
-        extra = {"concurrent_launches": M, "solo_us_per_launch": round(solo_ms * 1e3, 2),
+        extra = {"garments_per_launch" if shared else "concurrent_launches": M, "solo_us_per_launch": round(solo_ms * 1e3, 2),
                  "solo_achieved": round(solo_bytes / (solo_ms * 1e-3) / 1e9, 2)}
     else:
         kname = "bend_color_kernel"
@@ -268,10 +311,11 @@ def run_ours(args):
                        "single_garment_ms_per_frame": single,
                        "single_instance_ms_per_frame": round(ms_frame_single, 4),
                        "single_instance_ms_per_substep": round(ms_frame_single / 4, 4),
-                       "persist_cluster": cluster, "colors": [st["n_stretch_colors"], st["n_bend_colors"]]},
-            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(M * Vo * 12),
-                    "d2h_bytes_per_step": int(M * V * 12 * 2)},
-            "gpu_launches": int(st["launches_per_frame"] * M * args.steps * world),
+                       "persist_cluster": cluster, "shared_launch": shared, "groups": args.groups if shared else None,
+                       "e2e_instances_per_gpu": M_e2e, "colors": [st["n_stretch_colors"], st["n_bend_colors"]]},
+            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(M_e2e * Vo * 12),
+                    "d2h_bytes_per_step": int(M_e2e * V * 12 * 2)},
+            "gpu_launches": int((launches_shared if shared else st["launches_per_frame"] * M) * args.steps * world),
             "clocks": clk.summary(), "roofline": roofline,
         }
         if cpu:
@@ -357,9 +401,17 @@ def main():
     ap.add_argument("--n", type=int, default=224, help="cloth grid size (224 -> 50,176 verts; 317 -> 100,489)")
     ap.add_argument("--instances", type=int, default=0,
                     help="independent simulations per GPU (0: one per resident cluster)")
-    ap.add_argument("--cluster", type=int, default=8,
+    ap.add_argument("--cluster", type=int, default=1,
                     help="CTAs per garment of the persistent substep kernel (0: per-stage launches, -1: largest cluster, "
                          "-2: every SM on one garment)")
+    ap.add_argument("--shared", type=int, default=1,
+                    help="1: shared launches (one kernel per substep over all garments, xrt_batch_*); "
+                         "0: one stream and one launch per garment")
+    ap.add_argument("--e2e-batches", type=int, default=8,
+                    help="shared-launch batches the garments are split into for the end-to-end loop")
+    ap.add_argument("--groups", type=int, default=4, help="independently stepping sets of a shared-launch batch")
+    ap.add_argument("--workers", type=int, default=7,
+                    help="extra streams per set for the per-garment builds / hashes (groups * (1 + workers) <= 32)")
     ap.add_argument("--cpu-frames", type=int, default=8)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-single", action="store_true", help="skip the single-garment latency of the other shapes")

@@ -171,6 +171,42 @@ int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg_ms, double
  * disjoint clusters), *bytes = algorithmic bytes of those n launches. */
 int xrt_batch_profile_substep(xrt_solver** handles, int n, int reps, float* avg_ms, double* bytes);
 
+/* Shared-launch batch ("instances batched into shared launches").
+ * n finalized handles on one device, all with the same persist_cluster >= 1
+ * and substep count, step in lockstep: each substep of the whole batch is ONE
+ * launch with one CTA (persist_cluster 1) or one cluster per garment, so the
+ * batch is as wide as the device (148 garments at one SM each) instead of as
+ * wide as the hardware queue count.  The handles stay usable on their own
+ * (targets, sequences, getters); the batch keeps no state besides launch
+ * tables.  Destroy the batch before its handles.  `groups` >= 1 splits the
+ * garments into that many independently stepping sets (own stream and shared
+ * launches each), so one set's per-garment work between substeps (obstacle
+ * BVH build, predict + spatial hash) overlaps the other sets' substep kernels;
+ * that per-garment work is spread over `workers` extra streams per set (0: the
+ * set's own stream).  Keep groups * (1 + workers) <= 32, the hardware queues of
+ * a device.  Everything a batch enqueues runs on the batch's streams; a
+ * handle's own stream joins it on the next per-handle call.
+ *   xrt_batch_step_frame_async  enqueue one SimulateSwift frame of every handle
+ *   xrt_batch_sync              wait for all of it
+ *   xrt_batch_step_frames       `frames` frames back to back; *ms = device time
+ *   xrt_batch_profile           `reps` shared launches of one substep between two
+ *                               events: *avg_ms per launch, *bytes algorithmic */
+typedef struct xrt_batch xrt_batch;
+int xrt_batch_create(xrt_solver** handles, int n, int groups, int workers, xrt_batch** out);
+int xrt_batch_step_frame_async(xrt_batch* b);
+int xrt_batch_sync(xrt_batch* b);
+int xrt_batch_step_frames(xrt_batch* b, int frames, float* ms);
+int xrt_batch_profile(xrt_batch* b, int reps, float* avg_ms, double* bytes);
+/* xrt_get_positions / xrt_set_obstacle_target for every handle of the batch in
+ * one call: rows of the handles back to back in batch order (xyz / nrm:
+ * 3 * sum(n_verts) floats; n_verts_total is checked).  One garment's copy
+ * overlaps the previous garment's memcpy into the caller's buffer. */
+int xrt_batch_get_positions(xrt_batch* b, int which, float* xyz, float* nrm);
+int xrt_batch_set_obstacle_targets(xrt_batch* b, const float* xyz, size_t n_verts_total);
+/* Kernels one frame of the batch launches (moved: with a new obstacle target). */
+int xrt_batch_launches_per_frame(xrt_batch* b, int moved, uint32_t* out);
+void xrt_batch_destroy(xrt_batch* b);
+
 /* SaveCache (impl/universal/ClothSolver.cpp:107-144): which 0 = cloth,
  * 1 = obstacle.  xyz / nrm: 3*n_verts floats each, either may be NULL. */
 int xrt_get_positions(xrt_solver* s, int which, float* xyz, float* nrm);

@@ -298,6 +298,71 @@ def test_persistent_in_contact_vs_oracle(small, cluster):
     s.close()
 
 
+@pytest.mark.parametrize("cluster,groups", [(1, 1), (2, 2), (8, 3), (1, 2)])
+def test_shared_launch_batch_bit_equal_to_single_handles(cluster, groups):
+    """xrt_batch_*: one launch per substep over all garments (one CTA / cluster each) gives every garment
+    exactly what it gets stepped on its own stream: different garments, different obstacle motion, a handle
+    whose obstacle does not move, hash + BVH build per garment between the shared launches."""
+    scs = [scene.drop_scene(40, sphere=(12, 24), y=0.6), scene.drop_scene(33, sphere=(16, 32), y=0.55),
+           scene.drop_scene(48, sphere=(8, 16), y=0.6)]
+    amps = [0.05, 0.0, 0.03]
+
+    def run(batched):
+        ss = [scene.make_solver(sc, persist_cluster=cluster) for sc in scs]
+        b = X.Batch(ss, groups=groups) if batched else None
+        for f in range(3):
+            for s, sc, a in zip(ss, scs, amps):
+                if a:
+                    s.UpdateObstacleAnimationFrame(scene.sphere_motion(sc.obs_pos, f + 1, amp=a))
+            if batched:
+                b.SimulateSwiftAsync()
+                b.Sync()
+            else:
+                for s in ss:
+                    s.SimulateSwift()
+        out = [(s.GetPositions(0), s.debug("VF_CONTACTS", np.uint32)) for s in ss]
+        if b:
+            b.close()
+        for s in ss:
+            s.close()
+        return out
+
+    for (xa, ca), (xb, cb) in zip(run(False), run(True)):
+        np.testing.assert_array_equal(xa, xb)
+        np.testing.assert_array_equal(ca, cb)
+
+
+def test_shared_launch_batch_in_contact_vs_oracle(small):
+    ss, oo = zip(*[pair(small, persist_cluster=1) for _ in range(3)])
+    b = X.Batch(ss)
+    for f in range(6):
+        for i, (s, o) in enumerate(zip(ss, oo)):
+            tgt = scene.sphere_motion(small.obs_pos, f + 1 + 7 * i)
+            s.UpdateObstacleAnimationFrame(tgt)
+            o.set_obstacle_target(tgt)
+        b.run(1)
+        for o in oo:
+            o.step_frame()
+    for s, o in zip(ss, oo):
+        g = s.GetPositions(0)
+        assert np.isfinite(g).all()
+        assert rms(g, o.positions()) <= 1e-3, rms(g, o.positions())
+    b.close()
+    for s in ss:
+        s.close()
+
+
+def test_shared_launch_batch_rejects_mixed_shapes(small):
+    a = scene.make_solver(small, persist_cluster=8)
+    c = scene.make_solver(small, persist_cluster=4)
+    d = scene.make_solver(small, persist_cluster=0)
+    for hs in ([a, c], [d, d]):
+        with pytest.raises(X.XrtError):
+            X.Batch(hs)
+    for s in (a, c, d):
+        s.close()
+
+
 def test_persistent_one_substep_positions(small):
     s, o = pair(small, num_substeps=1, persist_cluster=8)
     s.SimulateSwift()

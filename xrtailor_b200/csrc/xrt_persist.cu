@@ -122,7 +122,7 @@ __device__ __forceinline__ ColorRec fetch_color_rec(const PersistArgs& a, uint32
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_constant__ PersistArgs a) {
+__device__ __forceinline__ void swift_substep_body(const PersistArgs& a) {
   const uint32_t nth = (MODE == SYNC_CLUSTER ? cluster_nctarank() : (MODE == SYNC_GRID ? gridDim.x : 1u)) * PT;
   const uint32_t tid =
       (MODE == SYNC_CLUSTER ? cluster_ctarank() : (MODE == SYNC_GRID ? blockIdx.x : 0u)) * PT + threadIdx.x;
@@ -236,6 +236,28 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
   pc.lap(12);
 }
 
+template <int MODE>
+__global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_constant__ PersistArgs a) {
+  swift_substep_body<MODE>(a);
+}
+
+// Shared launch: ONE kernel steps a whole batch of garments, one CTA (SYNC_BLOCK) or one
+// cluster (SYNC_CLUSTER) per garment.  The garment's argument block is copied from the batch's
+// device table into shared memory; `moved` selects the variant with / without a new obstacle
+// target.  No stream (and no hardware queue) per garment: the batch is as wide as the device.
+template <int MODE>
+__global__ void __launch_bounds__(PT, 1) swift_substep_batch_kernel(const PersistArgs* __restrict__ table,
+                                                                    const int* __restrict__ moved, uint32_t n) {
+  __shared__ PersistArgs sa;
+  const uint32_t g = MODE == SYNC_CLUSTER ? blockIdx.x / cluster_nctarank() : blockIdx.x;
+  static_assert(sizeof(PersistArgs) % 4 == 0, "argument block is copied word by word");
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(table + (size_t)(moved[g] ? n : 0) + g);
+  uint32_t* dst = reinterpret_cast<uint32_t*>(&sa);
+  for (uint32_t w = threadIdx.x; w < sizeof(PersistArgs) / 4; w += PT) dst[w] = src[w];
+  __syncthreads();
+  swift_substep_body<MODE>(sa);
+}
+
 }  // namespace
 
 int persist_max_cluster() {
@@ -243,6 +265,7 @@ int persist_max_cluster() {
   if (cached >= 0) return cached;
   // clusters above 8 CTAs need the non-portable opt-in
   cudaFuncSetAttribute(swift_substep_kernel<SYNC_CLUSTER>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+  cudaFuncSetAttribute(swift_substep_batch_kernel<SYNC_CLUSTER>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   int best = 1;
   for (int cs = 2; cs <= 16; cs *= 2) {
     cudaLaunchConfig_t cfg = {};
@@ -331,4 +354,25 @@ cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t
   cfg.attrs = at;
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, swift_substep_kernel<SYNC_CLUSTER>, a);
+}
+
+cudaError_t launch_swift_substep_batch(const PersistArgs* table, const int* moved, uint32_t n, int cluster,
+                                       cudaStream_t st) {
+  if (cluster <= 1) {
+    swift_substep_batch_kernel<SYNC_BLOCK><<<n, PT, 0, st>>>(table, moved, n);
+    return cudaGetLastError();
+  }
+  persist_max_cluster();
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(n * (uint32_t)cluster);
+  cfg.blockDim = dim3(PT);
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cluster;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, swift_substep_batch_kernel<SYNC_CLUSTER>, table, moved, n);
 }

@@ -247,6 +247,70 @@ def batch_run(solvers, frames):
     return ms.value
 
 
+class Batch:
+    """Shared-launch batch over solvers with the same persist_cluster >= 1: every substep of all of them is one
+    kernel launch (xrt_batch_*).  The solvers stay usable on their own between frames.  groups > 1: that many
+    independently stepping sets, so one set's BVH builds / hashes overlap the other sets' substep kernels."""
+
+    def __init__(self, solvers, groups=1, workers=3):
+        self.solvers = list(solvers)
+        arr = (C.c_void_p * len(self.solvers))(*[s._h for s in self.solvers])
+        h = C.c_void_p()
+        rc = lib.xrt_batch_create(arr, len(self.solvers), int(groups), int(workers), C.byref(h))
+        if rc:
+            raise XrtError(rc, lib.xrt_last_error(self.solvers[0]._h).decode(errors="replace"))
+        self._h = h
+
+    def _ck(self, rc):
+        if rc:
+            raise XrtError(rc, lib.xrt_last_error(self.solvers[0]._h).decode(errors="replace"))
+
+    def SimulateSwiftAsync(self):
+        self._ck(lib.xrt_batch_step_frame_async(self._h))
+
+    def Sync(self):
+        self._ck(lib.xrt_batch_sync(self._h))
+
+    def run(self, frames):
+        """`frames` frames of every garment back to back; returns device ms."""
+        ms = C.c_float()
+        self._ck(lib.xrt_batch_step_frames(self._h, int(frames), C.byref(ms)))
+        return ms.value
+
+    def profile(self, reps=8):
+        ms, b = C.c_float(), C.c_double()
+        self._ck(lib.xrt_batch_profile(self._h, int(reps), C.byref(ms), C.byref(b)))
+        return ms.value, b.value
+
+    def GetPositions(self, which=0, xyz=None, nrm=None, normals=False):
+        """Positions (and normals) of every garment back to back, into caller arrays when given."""
+        n = sum((s.n_cloth_verts if which == 0 else s.n_obstacle_verts) for s in self.solvers)
+        if xyz is None:
+            xyz = np.empty((n, 3), np.float32)
+        if nrm is None and normals:
+            nrm = np.empty((n, 3), np.float32)
+        assert xyz.shape == (n, 3) and xyz.dtype == np.float32 and xyz.flags.c_contiguous
+        self._ck(lib.xrt_batch_get_positions(self._h, int(which), _pf(xyz), _pf(nrm)))
+        return (xyz, nrm) if nrm is not None else xyz
+
+    def UpdateObstacleAnimationFrames(self, xyz):
+        t = _f32(xyz).reshape(-1, 3)
+        self._ck(lib.xrt_batch_set_obstacle_targets(self._h, _pf(t), len(t)))
+
+    def launches_per_frame(self, moved=True):
+        n = C.c_uint32()
+        self._ck(lib.xrt_batch_launches_per_frame(self._h, int(bool(moved)), C.byref(n)))
+        return n.value
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib.xrt_batch_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.close()
+
+
 def batch_profile_substep(solvers, reps=20):
     """(ms of one round of the persistent substep kernel on every solver side by side, bytes of that round)."""
     arr = (C.c_void_p * len(solvers))(*[s._h for s in solvers])
