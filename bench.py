@@ -218,20 +218,22 @@ def run_ours(args):
     if shared:
         batch.close()
         per = M_e2e // n_e2e_batches
-        e2e_batches = [X.Batch(solvers[k * per:(k + 1) * per], groups=1, workers=max(0, 32 // n_e2e_batches - 1))
+        e2e_batches = [X.Batch(solvers[k * per:(k + 1) * per], groups=1,
+                               workers=args.e2e_workers if args.e2e_workers >= 0 else max(0, 32 // n_e2e_batches - 1))
                        for k in range(n_e2e_batches)]
         for b in e2e_batches:
             b.run(1)
+        # host buffers of the caller: results, and the animation source [seq_len][per * Vo][3] per batch
+        out_xyz = [np.zeros((per * V, 3), np.float32) for _ in e2e_batches]
+        out_nrm = [np.zeros((per * V, 3), np.float32) for _ in e2e_batches]
+        tgt = [np.stack([np.concatenate([seqs[k * per + j][f] for j in range(per)]) for f in range(seq_len)])
+               for k in range(n_e2e_batches)]
     barrier()
     t0 = time.perf_counter()
     if shared:
         # per batch: read back frame f-1 of its garments (D2H positions + normals into host arrays, SaveCache),
         # upload their frame-f obstacle targets from host arrays (H2D), enqueue frame f as shared launches;
         # the other batches compute meanwhile
-        out_xyz = [np.empty((per * V, 3), np.float32) for _ in e2e_batches]
-        out_nrm = [np.empty((per * V, 3), np.float32) for _ in e2e_batches]
-        tgt = [np.stack([np.concatenate([seqs[k * per + j][f] for j in range(per)]) for f in range(seq_len)])
-               for k in range(n_e2e_batches)]  # host-side animation source, [seq_len][per * Vo][3]
         for f in range(args.steps + 1):
             for k, b in enumerate(e2e_batches):
                 if f > 0:
@@ -409,6 +411,7 @@ def main():
                          "0: one stream and one launch per garment")
     ap.add_argument("--e2e-batches", type=int, default=8,
                     help="shared-launch batches the garments are split into for the end-to-end loop")
+    ap.add_argument("--e2e-workers", type=int, default=-1, help="worker streams per end-to-end batch (-1: fill 32 queues)")
     ap.add_argument("--groups", type=int, default=4, help="independently stepping sets of a shared-launch batch")
     ap.add_argument("--workers", type=int, default=7,
                     help="extra streams per set for the per-garment builds / hashes (groups * (1 + workers) <= 32)")
