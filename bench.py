@@ -315,8 +315,8 @@ def run_ours(args):
                        "single_instance_ms_per_substep": round(ms_frame_single / 4, 4),
                        "persist_cluster": cluster, "shared_launch": shared, "groups": args.groups if shared else None,
                        "e2e_instances_per_gpu": M_e2e, "colors": [st["n_stretch_colors"], st["n_bend_colors"]]},
-            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(M_e2e * Vo * 12),
-                    "d2h_bytes_per_step": int(M_e2e * V * 12 * 2)},
+            "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(world * M_e2e * Vo * 12),
+                    "d2h_bytes_per_step": int(world * M_e2e * V * 12 * 2)},
             "gpu_launches": int((launches_shared if shared else st["launches_per_frame"] * M) * args.steps * world),
             "clocks": clk.summary(), "roofline": roofline,
         }

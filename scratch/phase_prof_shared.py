@@ -1,0 +1,30 @@
+"""C2, shared launch: per-phase-kind time inside garment 0's CTA / cluster while the whole batch runs."""
+import os, sys
+os.environ["XRT_PERSIST_PROF"] = "1"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import xrtailor_b200 as X
+from xrtailor_b200 import scene
+
+NAMES = ["predict", "collide", "apply1", "interp+normals", "refit", "generate", "stretch", "bend", "lra",
+         "solve_vertex", "solve_edge", "apply2", "finalize"]
+cl = int(sys.argv[1]) if len(sys.argv) > 1 else 1
+Ms = [int(a) for a in sys.argv[2:]] or [1, X.persist_info(cl)[1]]
+sc, body, bindings = scene.body_scene()
+seq = np.stack([body.pose(f + 1, amp_deg=30.0) for f in range(60)])
+solvers = []
+for i in range(max(Ms)):
+    s = scene.make_solver(sc, persist_cluster=cl, bindings=bindings)
+    s.SetObstacleSequence(seq)
+    solvers.append(s)
+frames = 10
+for M in Ms:
+    b = X.Batch(solvers[:M], groups=min(4, M), workers=7)
+    b.run(3)
+    p0 = solvers[0].debug("PERSIST_PROF", np.uint64).copy()
+    ms = b.run(frames)
+    p = (solvers[0].debug("PERSIST_PROF", np.uint64) - p0).astype(np.float64) / frames / 1e3
+    print(f"cluster {cl} M={M}: {ms / frames:.3f} ms per round = {M * frames / ms * 1e3:.0f} f/s; "
+          f"garment 0 per-phase-kind us/frame (sum {p[:13].sum():.0f}):")
+    print("   " + "  ".join(f"{nm} {v:.0f}" for nm, v in zip(NAMES, p[:13])))
+    b.close()
