@@ -24,11 +24,16 @@ __device__ __forceinline__ void tnode_load_box(const TNode* t, float lo[3], floa
 // PARITY: the counters are never cleared; a parent is reached exactly twice per
 // pass, so "first arrival" is "old value even" (saves the memset the per-stage
 // path issues before each pass).
-template <bool PARITY>
+// ONE_CTA: every thread of the pass is in one CTA (one SM per garment), so the box store only
+// has to be ordered before the counter at CTA scope -- no MEMBAR.GPU per level.
+template <bool PARITY, bool ONE_CTA = false>
 __device__ __forceinline__ void walk_up(TNode* tn, const BVNode* nodes, int* flags, uint32_t leaf_node) {
   uint32_t parent = nodes[leaf_node].parent;
   while (parent != 0xFFFFFFFFu) {
-    __threadfence();
+    if (ONE_CTA)
+      __threadfence_block();
+    else
+      __threadfence();
     const int old = atomicAdd(flags + parent, 1);
     if (PARITY ? ((old & 1) == 0) : (old == 0)) return;
     float la[3], ha[3], lb[3], hb[3];
@@ -49,7 +54,7 @@ __device__ __forceinline__ void walk_up(TNode* tn, const BVNode* nodes, int* fla
 // Interpolated obstacle -> primitive pred + grow-only leaf boxes + exact
 // internal merge (RefitExternalNodeMidstep_Kernel + AssignAABBCAS_Kernel,
 // BVH.cu:770-793,515-538) for leaf i.
-template <bool PARITY>
+template <bool PARITY, bool ONE_CTA = false>
 __device__ __forceinline__ void refit_item(TNode* tn, const BVNode* nodes, float4* pred, const float4* x1,
                                            const float4* n1, const uint32_t* tri, float tol, int* flags,
                                            uint32_t F, uint32_t i) {
@@ -68,7 +73,7 @@ __device__ __forceinline__ void refit_item(TNode* tn, const BVNode* nodes, float
     hi[0] = fmaxf(hi[0], q.x); hi[1] = fmaxf(hi[1], q.y); hi[2] = fmaxf(hi[2], q.z);
   }
   tnode_store_box(leaf, lo, hi);
-  walk_up<PARITY>(tn, nodes, flags, node);
+  walk_up<PARITY, ONE_CTA>(tn, nodes, flags, node);
 }
 
 }  // namespace xrtdev

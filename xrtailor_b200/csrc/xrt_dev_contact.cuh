@@ -91,23 +91,36 @@ struct SegQuery {
 
 // QueryDeviceStackless (BVH.cu:957-1055) with the leaf visitor inlined.
 // Returns the number of leaf hits (capped at XRT_MAX_HITS like the reference).
+// "while-while" form: every lane first walks to its next leaf hit (or the end), then the
+// warp runs the leaf visitor together -- the heavy primitive tests execute with most lanes
+// active instead of only the lanes that happen to stand on a leaf in this iteration.
+// Same visits in the same order per lane as the reference's single loop.
 template <bool NC, class Pred, class Visit>
 __device__ __forceinline__ uint32_t traverse(const TNode* t, Pred pred, Visit visit) {
   int node = 0;
   uint32_t found = 0;
   while (node != -1) {
-    const NodeView n = load_node<NC>(t, node);
-    if (found >= XRT_MAX_HITS) break;
-    if (pred(n.b)) {
-      if (n.hit < 0) {  // leaf
-        visit((uint32_t)~n.hit);
-        found++;
-        node = n.miss;
-      } else {
-        node = n.hit;
+    int leaf = -1;
+    while (node != -1) {
+      const NodeView n = load_node<NC>(t, node);
+      if (found >= XRT_MAX_HITS) {
+        node = -1;
+        break;
       }
-    } else {
-      node = n.miss;
+      if (pred(n.b)) {
+        if (n.hit < 0) {
+          leaf = ~n.hit;
+          node = n.miss;
+          break;
+        }
+        node = n.hit;
+      } else {
+        node = n.miss;
+      }
+    }
+    if (leaf >= 0) {
+      visit((uint32_t)leaf);
+      found++;
     }
   }
   return found;

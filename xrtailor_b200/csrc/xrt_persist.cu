@@ -160,7 +160,7 @@ __device__ __forceinline__ void swift_substep_body(const PersistArgs& a) {
         phase_sync<MODE>(a.grid_bar);
     pc.lap(3);
         for (uint32_t i = tid; i < o.F; i += nth)
-          refit_item<true>(a.bvh.tnodes, a.bvh.nodes, a.bvh.pred, o.x1, o.n1, o.tri, a.tol, a.refit_flags, o.F, i);
+          refit_item<true, MODE == SYNC_BLOCK>(a.bvh.tnodes, a.bvh.nodes, a.bvh.pred, o.x1, o.n1, o.tri, a.tol, a.refit_flags, o.F, i);
         phase_sync<MODE>(a.grid_bar);
     pc.lap(4);
       }
