@@ -973,7 +973,7 @@ extern "C" int xrt_batch_profile_substep(xrt_solver** handles, int n, int reps, 
 // boundary is a bar.sync) fill the device.  What stays per garment and per stream is the work
 // before a substep: the obstacle BVH build of the frame and predict + spatial hash when due.
 struct BatchGroup {
-  int first = 0, n = 0;
+  int first = 0, n = 0, seg_begin = 0;
   cudaStream_t st = nullptr;
   std::vector<cudaStream_t> wk;   // worker streams for the garments' own graphs between shared launches
   std::vector<cudaEvent_t> ev_wk;
@@ -1178,9 +1178,11 @@ static int batch_enqueue_frame(xrt_batch* b) {
     XRT_CUDA_OK(cudaMemcpyAsync(g.d_moved, g.h_moved, g.n * sizeof(int), cudaMemcpyHostToDevice, g.st));
     XRT_CUDA_OK(cudaEventRecord(g.ev_flags, g.st));
   }
+  for (BatchGroup& g : b->g) g.seg_begin = 0;
   for (int sub = 0; sub <= b->S; sub++)  // sub == S: end of frame
     for (BatchGroup& g : b->g) {
       gr.assign(g.n, nullptr);
+      bool any = sub == 0 || sub == b->S;
       for (int i = 0; i < g.n; i++) {
         xrt_solver* h = b->h[g.first + i];
         const int rc = sub < b->S ? batch_pre_graph(h, sub, g.h_moved[i], &gr[i]) : batch_post_graph(h, g.h_moved[i], &gr[i]);
@@ -1188,11 +1190,15 @@ static int batch_enqueue_frame(xrt_batch* b) {
           if (h != s) xrt_set_error(s, "batch: handle %d: %s", g.first + i, h->err);
           return rc;
         }
+        any = any || gr[i];
       }
+      if (!any) continue;  // this substep joins the running segment
+      // substeps [seg_begin, sub) need nothing from outside: one launch
+      if (sub > g.seg_begin)
+        XRT_CUDA_OK(launch_swift_substep_batch(g.d_table, g.d_moved, (uint32_t)g.n, g.seg_begin, sub, b->cluster, g.st));
+      g.seg_begin = sub;
       if (int rc = batch_fan_out(b, g, gr)) return rc;
-      if (sub < b->S) {
-        XRT_CUDA_OK(launch_swift_substep_batch(g.d_table + (size_t)sub * 2 * g.n, g.d_moved, (uint32_t)g.n, b->cluster, g.st));
-      } else {
+      if (sub == b->S) {
         XRT_CUDA_OK(cudaEventRecord(g.ev_done, g.st));
         for (int i = 0; i < g.n; i++) {
           b->h[g.first + i]->target_pending = false;
@@ -1312,7 +1318,16 @@ extern "C" int xrt_batch_set_obstacle_targets(xrt_batch* b, const float* xyz, si
 // kernels one frame of the batch launches (the count bench.py reports)
 extern "C" int xrt_batch_launches_per_frame(xrt_batch* b, int moved, uint32_t* out) {
   if (!b || b->h.empty() || !out) return XRT_ERR_INVALID;
-  uint32_t n = (uint32_t)(b->S * (int)b->g.size());
+  uint32_t n = 0;
+  for (const BatchGroup& g : b->g)  // shared launches: one per run of substeps without per-garment work in between
+    for (int sub = 0; sub < b->S; sub++) {
+      bool any = sub == 0;
+      for (int i = 0; i < g.n && !any; i++) {
+        const xrt_solver* h = b->h[g.first + i];
+        any = h->p.enable_self_collision && sub % std::max(1, h->p.inter_leaved_hash) == 0;
+      }
+      n += any ? 1u : 0u;
+    }
   for (const xrt_solver* h : b->h) {
     if (moved && h->o.F) n += (uint32_t)bvh_build_launches();
     for (int sub = 0; sub < b->S; sub++)
@@ -1353,7 +1368,7 @@ extern "C" int xrt_batch_profile(xrt_batch* b, int reps, float* avg_ms, double* 
       if (gi) cudaStreamWaitEvent(g.st, b->ev0, 0);
       cudaMemsetAsync(g.d_moved, 0, g.n * sizeof(int), g.st);
       for (int r = 0; r < (pass ? reps : 2); r++)
-        launch_swift_substep_batch(d_tabs[gi], g.d_moved, (uint32_t)g.n, b->cluster, g.st);
+        launch_swift_substep_batch(d_tabs[gi], g.d_moved, (uint32_t)g.n, 0, 1, b->cluster, g.st);
       if (gi) {
         cudaEventRecord(g.ev_fork, g.st);
         cudaStreamWaitEvent(st0, g.ev_fork, 0);

@@ -247,15 +247,22 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_kernel(const __grid_const
 // target.  No stream (and no hardware queue) per garment: the batch is as wide as the device.
 template <int MODE>
 __global__ void __launch_bounds__(PT, 1) swift_substep_batch_kernel(const PersistArgs* __restrict__ table,
-                                                                    const int* __restrict__ moved, uint32_t n) {
+                                                                    const int* __restrict__ moved, uint32_t n,
+                                                                    int sub_begin, int sub_end) {
   __shared__ PersistArgs sa;
   const uint32_t g = MODE == SYNC_CLUSTER ? blockIdx.x / cluster_nctarank() : blockIdx.x;
   static_assert(sizeof(PersistArgs) % 4 == 0, "argument block is copied word by word");
-  const uint32_t* src = reinterpret_cast<const uint32_t*>(table + (size_t)(moved[g] ? n : 0) + g);
-  uint32_t* dst = reinterpret_cast<uint32_t*>(&sa);
-  for (uint32_t w = threadIdx.x; w < sizeof(PersistArgs) / 4; w += PT) dst[w] = src[w];
-  __syncthreads();
-  swift_substep_body<MODE>(sa);
+  const uint32_t mv = moved[g] ? 1u : 0u;
+  // consecutive substeps that need nothing from outside (no hash, no build) run in one launch:
+  // a garment does not wait for the slowest garment of the batch between them
+  for (int sub = sub_begin; sub < sub_end; sub++) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(table + ((size_t)sub * 2u + mv) * n + g);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(&sa);
+    for (uint32_t w = threadIdx.x; w < sizeof(PersistArgs) / 4; w += PT) dst[w] = src[w];
+    __syncthreads();
+    swift_substep_body<MODE>(sa);
+    phase_sync<MODE>();  // the substep's last phase is complete (and sa is free) before the next one starts
+  }
 }
 
 }  // namespace
@@ -356,10 +363,10 @@ cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t
   return cudaLaunchKernelEx(&cfg, swift_substep_kernel<SYNC_CLUSTER>, a);
 }
 
-cudaError_t launch_swift_substep_batch(const PersistArgs* table, const int* moved, uint32_t n, int cluster,
-                                       cudaStream_t st) {
+cudaError_t launch_swift_substep_batch(const PersistArgs* table, const int* moved, uint32_t n, int sub_begin,
+                                       int sub_end, int cluster, cudaStream_t st) {
   if (cluster <= 1) {
-    swift_substep_batch_kernel<SYNC_BLOCK><<<n, PT, 0, st>>>(table, moved, n);
+    swift_substep_batch_kernel<SYNC_BLOCK><<<n, PT, 0, st>>>(table, moved, n, sub_begin, sub_end);
     return cudaGetLastError();
   }
   persist_max_cluster();
@@ -374,5 +381,5 @@ cudaError_t launch_swift_substep_batch(const PersistArgs* table, const int* move
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
-  return cudaLaunchKernelEx(&cfg, swift_substep_batch_kernel<SYNC_CLUSTER>, table, moved, n);
+  return cudaLaunchKernelEx(&cfg, swift_substep_batch_kernel<SYNC_CLUSTER>, table, moved, n, sub_begin, sub_end);
 }

@@ -31,7 +31,7 @@ int persist_active_clusters(int cluster);
 // CTAs of the grid-wide shape (= SMs), 0 if the kernel cannot be co-resident
 int persist_grid_ctas();
 cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t st);
-// shared launch over a batch: table = [2][n] argument blocks (row 1: obstacle target moved), moved = [n] flags;
-// garment g runs on CTA g (cluster <= 1) or on cluster g of `cluster` CTAs
-cudaError_t launch_swift_substep_batch(const PersistArgs* table, const int* moved, uint32_t n, int cluster,
-                                       cudaStream_t st);
+// shared launch over a batch: table = [S][2][n] argument blocks (middle index 1: obstacle target moved),
+// moved = [n] flags; garment g runs substeps [sub_begin, sub_end) on CTA g (cluster <= 1) or on cluster g
+cudaError_t launch_swift_substep_batch(const PersistArgs* table, const int* moved, uint32_t n, int sub_begin,
+                                       int sub_end, int cluster, cudaStream_t st);
