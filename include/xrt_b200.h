@@ -203,6 +203,14 @@ int xrt_batch_profile(xrt_batch* b, int reps, float* avg_ms, double* bytes);
  * overlaps the previous garment's memcpy into the caller's buffer. */
 int xrt_batch_get_positions(xrt_batch* b, int which, float* xyz, float* nrm);
 int xrt_batch_set_obstacle_targets(xrt_batch* b, const float* xyz, size_t n_verts_total);
+/* Read-back mode.  on != 0: every frame ends with a device-side snapshot of each
+ * garment's positions + normals that a copy stream brings to pinned host memory
+ * while the next frame computes.  xrt_batch_get_positions(b, 0, ...) then returns
+ * the OLDEST unread snapshot (frame f may be fetched after frame f+1 has been
+ * enqueued); at most two frames may be outstanding - a third
+ * xrt_batch_step_frame_async fails with XRT_ERR_INVALID until one is read.
+ * xrt_batch_step_frames cannot be used in this mode for more than two frames. */
+int xrt_batch_set_readback(xrt_batch* b, int on);
 /* Kernels one frame of the batch launches (moved: with a new obstacle target). */
 int xrt_batch_launches_per_frame(xrt_batch* b, int moved, uint32_t* out);
 void xrt_batch_destroy(xrt_batch* b);

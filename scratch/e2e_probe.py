@@ -8,16 +8,18 @@ sc, body, bindings = scene.body_scene()
 seq = np.stack([body.pose(f + 1, amp_deg=30.0) for f in range(60)])
 NB, per = int(sys.argv[1]), int(sys.argv[2])
 W = int(sys.argv[3]) if len(sys.argv) > 3 else 3
+G = int(sys.argv[4]) if len(sys.argv) > 4 else 1
 solvers = []
 for i in range(NB * per):
     s = scene.make_solver(sc, persist_cluster=1, bindings=bindings)
     s.SetObstacleSequence(seq)
     solvers.append(s)
-batches = [X.Batch(solvers[k * per:(k + 1) * per], groups=1, workers=W) for k in range(NB)]
+batches = [X.Batch(solvers[k * per:(k + 1) * per], groups=G, workers=W) for k in range(NB)]
 V, Vo = len(sc.cloth_pos), len(sc.obs_pos)
 xyz = [np.empty((per * V, 3), np.float32) for _ in batches]
 nrm = [np.empty((per * V, 3), np.float32) for _ in batches]
 tgt = np.stack([np.concatenate([seq[f]] * per) for f in range(60)])
+print('groups', G)
 steps = 12
 for mode in ["sync", "get", "set", "get+set"]:
     for b in batches:

@@ -352,6 +352,40 @@ def test_shared_launch_batch_in_contact_vs_oracle(small):
         s.close()
 
 
+def test_shared_launch_readback_returns_frames_in_order(small):
+    """Read-back mode: frame f can be fetched after frame f+1 was enqueued, and is exactly what an immediate
+    GetPositions after frame f returns; a third outstanding frame is refused."""
+    def run(readback):
+        ss = [scene.make_solver(small, persist_cluster=1) for _ in range(3)]
+        b = X.Batch(ss, groups=2, workers=1)
+        frames = []
+        tg = lambda f: np.concatenate([scene.sphere_motion(small.obs_pos, f + 1 + 3 * i) for i in range(3)])
+        if readback:
+            b.SetReadback(True)
+            b.UpdateObstacleAnimationFrames(tg(0))
+            b.SimulateSwiftAsync()
+            for f in range(1, 5):
+                b.UpdateObstacleAnimationFrames(tg(f))
+                b.SimulateSwiftAsync()
+                frames.append(tuple(a.copy() for a in b.GetPositions(0, normals=True)))
+            with pytest.raises(X.XrtError):
+                b.SimulateSwiftAsync()
+                b.SimulateSwiftAsync()
+        else:
+            for f in range(4):
+                b.UpdateObstacleAnimationFrames(tg(f))
+                b.SimulateSwiftAsync()
+                frames.append(tuple(a.copy() for a in b.GetPositions(0, normals=True)))
+        b.close()
+        for s in ss:
+            s.close()
+        return frames
+
+    for (xa, na), (xb, nb) in zip(run(False), run(True)):
+        np.testing.assert_array_equal(xa, xb)
+        np.testing.assert_array_equal(na, nb)
+
+
 def test_shared_launch_batch_rejects_mixed_shapes(small):
     a = scene.make_solver(small, persist_cluster=8)
     c = scene.make_solver(small, persist_cluster=4)

@@ -54,7 +54,7 @@ SYMBOLS = [
     "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone", "xrt_persist_info", "xrt_batch_profile_substep", "xrt_add_binding",
     "xrt_traverse_pairs_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
-    "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame",
+    "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
 ]
 
 
@@ -110,6 +110,7 @@ def _load():
         "xrt_batch_get_positions": [vp, C.c_int, f32p, f32p],
         "xrt_batch_set_obstacle_targets": [vp, f32p, C.c_size_t],
         "xrt_batch_launches_per_frame": [vp, C.c_int, u32p],
+        "xrt_batch_set_readback": [vp, C.c_int],
     }
     for name, args in sig.items():
         fn = getattr(L, name)

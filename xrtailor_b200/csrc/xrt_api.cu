@@ -978,6 +978,8 @@ struct BatchGroup {
   std::vector<cudaStream_t> wk;   // worker streams for the garments' own graphs between shared launches
   std::vector<cudaEvent_t> ev_wk;
   cudaEvent_t ev_fork = nullptr, ev_flags = nullptr, ev_done = nullptr;
+  cudaStream_t st_copy = nullptr;  // read-back mode: D2H of the frame snapshots
+  cudaEvent_t ev_snap = nullptr;
   PersistArgs* d_table = nullptr;  // [S][2][n]
   int *d_moved = nullptr, *h_moved = nullptr;
 };
@@ -990,6 +992,13 @@ struct xrt_batch {
   int cluster = 1, S = 1;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   std::vector<cudaEvent_t> ev_pre;  // per garment: handle stream -> batch join, pipelined read-back
+  // read-back mode (xrt_batch_set_readback): every frame ends with a device-side snapshot of the cloth
+  // (positions + normals, packed float3) that a copy stream brings to pinned host memory while the next
+  // frame computes; two frames may be outstanding
+  bool readback = false;
+  std::vector<float*> d_snap, h_snap[2];
+  std::vector<cudaEvent_t> ev_dn[2];
+  unsigned long long snap_written = 0, snap_read = 0;
 };
 
 extern "C" void xrt_batch_destroy(xrt_batch* b) {
@@ -1000,6 +1009,19 @@ extern "C" void xrt_batch_destroy(xrt_batch* b) {
     for (cudaStream_t w : g.wk)
       if (w) cudaStreamDestroy(w);
     for (cudaEvent_t e : g.ev_wk)
+      if (e) cudaEventDestroy(e);
+  }
+  for (BatchGroup& g : b->g) {
+    if (g.st_copy) {
+      cudaStreamSynchronize(g.st_copy);
+      cudaStreamDestroy(g.st_copy);
+    }
+    if (g.ev_snap) cudaEventDestroy(g.ev_snap);
+  }
+  for (float* p : b->d_snap) cudaFree(p);
+  for (int k = 0; k < 2; k++) {
+    for (float* p : b->h_snap[k]) cudaFreeHost(p);
+    for (cudaEvent_t e : b->ev_dn[k])
       if (e) cudaEventDestroy(e);
   }
   for (xrt_solver* h : b->h) h->batch_ev = nullptr;  // everything it pointed at has completed
@@ -1159,9 +1181,63 @@ static int batch_fan_out(xrt_batch* b, BatchGroup& g, const std::vector<cudaGrap
   return XRT_OK;
 }
 
+extern "C" int xrt_batch_set_readback(xrt_batch* b, int on) {
+  if (!b || b->h.empty()) return XRT_ERR_INVALID;
+  xrt_solver* s = b->h[0];
+  XRT_CUDA_OK(cudaSetDevice(s->p.device));
+  XRT_REQUIRE(b->snap_read == b->snap_written, "batch_set_readback: read the outstanding frames back first");
+  if (on && b->d_snap.empty()) {
+    const size_t n = b->h.size();
+    b->d_snap.assign(n, nullptr);
+    for (int k = 0; k < 2; k++) {
+      b->h_snap[k].assign(n, nullptr);
+      b->ev_dn[k].assign(n, nullptr);
+    }
+    for (size_t i = 0; i < n; i++) {
+      const size_t bytes = (size_t)b->h[i]->c.V * 6 * sizeof(float);
+      XRT_CUDA_OK(cudaMalloc((void**)&b->d_snap[i], bytes ? bytes : 16));
+      for (int k = 0; k < 2; k++) {
+        XRT_CUDA_OK(cudaMallocHost((void**)&b->h_snap[k][i], bytes ? bytes : 16));
+        XRT_CUDA_OK(cudaEventCreateWithFlags(&b->ev_dn[k][i], cudaEventDisableTiming));
+      }
+    }
+    for (BatchGroup& g : b->g) {
+      XRT_CUDA_OK(cudaStreamCreateWithFlags(&g.st_copy, cudaStreamNonBlocking));
+      XRT_CUDA_OK(cudaEventCreateWithFlags(&g.ev_snap, cudaEventDisableTiming));
+    }
+  }
+  b->readback = on != 0;
+  return XRT_OK;
+}
+
+// end of frame in read-back mode: snapshot on the group's stream, D2H on its copy stream
+static int batch_snapshot(xrt_batch* b, BatchGroup& g) {
+  xrt_solver* s = b->h[0];
+  const int par = (int)(b->snap_written & 1ull);
+  for (int i = 0; i < g.n; i++) {
+    xrt_solver* h = b->h[g.first + i];
+    if (!h->c.V) continue;
+    // the copy of the previous frame has left the device staging buffer
+    XRT_CUDA_OK(cudaStreamWaitEvent(g.st, b->ev_dn[par ^ 1][g.first + i], 0));
+    launch_pack_xyz(h->c.x0, h->c.n, b->d_snap[g.first + i], (uint32_t)h->c.V, g.st);
+  }
+  XRT_CUDA_OK(cudaEventRecord(g.ev_snap, g.st));
+  XRT_CUDA_OK(cudaStreamWaitEvent(g.st_copy, g.ev_snap, 0));
+  for (int i = 0; i < g.n; i++) {
+    xrt_solver* h = b->h[g.first + i];
+    if (!h->c.V) continue;
+    XRT_CUDA_OK(cudaMemcpyAsync(b->h_snap[par][g.first + i], b->d_snap[g.first + i], (size_t)h->c.V * 6 * sizeof(float),
+                                cudaMemcpyDeviceToHost, g.st_copy));
+    XRT_CUDA_OK(cudaEventRecord(b->ev_dn[par][g.first + i], g.st_copy));
+  }
+  return XRT_OK;
+}
+
 // one frame of every garment (SimulateSwift, ClothSolverBase.cpp:171-247), each group in lockstep
 static int batch_enqueue_frame(xrt_batch* b) {
   xrt_solver* s = b->h[0];
+  XRT_REQUIRE(!b->readback || b->snap_written - b->snap_read < 2,
+              "batch: two frames are waiting to be read back (xrt_batch_get_positions)");
   std::vector<cudaGraphExec_t> gr;
   for (BatchGroup& g : b->g) {
     XRT_CUDA_OK(cudaEventSynchronize(g.ev_flags));  // previous frame's flags have left the pinned buffer
@@ -1199,6 +1275,8 @@ static int batch_enqueue_frame(xrt_batch* b) {
       g.seg_begin = sub;
       if (int rc = batch_fan_out(b, g, gr)) return rc;
       if (sub == b->S) {
+        if (b->readback)
+          if (int rc = batch_snapshot(b, g)) return rc;
         XRT_CUDA_OK(cudaEventRecord(g.ev_done, g.st));
         for (int i = 0; i < g.n; i++) {
           b->h[g.first + i]->target_pending = false;
@@ -1206,6 +1284,7 @@ static int batch_enqueue_frame(xrt_batch* b) {
         }
       }
     }
+  if (b->readback) b->snap_written++;
   return XRT_OK;
 }
 
@@ -1221,7 +1300,10 @@ extern "C" int xrt_batch_sync(xrt_batch* b) {
   if (!b || b->h.empty()) return XRT_ERR_INVALID;
   xrt_solver* s = b->h[0];
   XRT_CUDA_OK(cudaSetDevice(s->p.device));
-  for (BatchGroup& g : b->g) XRT_CUDA_OK(cudaStreamSynchronize(g.st));
+  for (BatchGroup& g : b->g) {
+    XRT_CUDA_OK(cudaStreamSynchronize(g.st));
+    if (g.st_copy) XRT_CUDA_OK(cudaStreamSynchronize(g.st_copy));
+  }
   return XRT_OK;
 }
 
@@ -1254,6 +1336,21 @@ extern "C" int xrt_batch_get_positions(xrt_batch* b, int which, float* xyz, floa
   xrt_solver* s = b->h[0];
   XRT_CUDA_OK(cudaSetDevice(s->p.device));
   if (!xyz && !nrm) return XRT_OK;
+  if (which == 0 && b->readback && b->snap_read < b->snap_written) {
+    // oldest unread snapshot: wait for its copy garment by garment, memcpy out
+    const int par = (int)(b->snap_read & 1ull);
+    size_t row = 0;
+    for (size_t i = 0; i < b->h.size(); i++) {
+      const size_t n = b->h[i]->c.V;
+      if (!n) continue;
+      XRT_CUDA_OK(cudaEventSynchronize(b->ev_dn[par][i]));
+      if (xyz) memcpy(xyz + 3 * row, b->h_snap[par][i], n * 3 * sizeof(float));
+      if (nrm) memcpy(nrm + 3 * row, b->h_snap[par][i] + 3 * n, n * 3 * sizeof(float));
+      row += n;
+    }
+    b->snap_read++;
+    return XRT_OK;
+  }
   for (BatchGroup& g : b->g)
     for (int i = 0; i < g.n; i++) {
       xrt_solver* h = b->h[g.first + i];

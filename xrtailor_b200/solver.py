@@ -297,6 +297,11 @@ class Batch:
         t = _f32(xyz).reshape(-1, 3)
         self._ck(lib.xrt_batch_set_obstacle_targets(self._h, _pf(t), len(t)))
 
+    def SetReadback(self, on=True):
+        """Frames end with a snapshot that is copied to the host while the next frame computes; GetPositions(0)
+        then returns the oldest unread frame (at most two outstanding)."""
+        self._ck(lib.xrt_batch_set_readback(self._h, int(bool(on))))
+
     def launches_per_frame(self, moved=True):
         n = C.c_uint32()
         self._ck(lib.xrt_batch_launches_per_frame(self._h, int(bool(moved)), C.byref(n)))
