@@ -381,8 +381,22 @@ def run_reference(args):
     except Exception:
         ref = None
     if ref is not None:
-        res = ref.time_frames(sc, steps=args.steps, warmup=args.warmup, device=local_rank, motion=wl.motion,
-                              bindings=wl.bindings)
+        # the reference's own setup chatter goes to stderr: stdout carries the one JSON line
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            res = ref.time_frames(sc, steps=args.steps, warmup=args.warmup, device=local_rank, motion=wl.motion,
+                                  bindings=wl.bindings)
+        finally:
+            sys.stdout.flush()
+            try:
+                import ctypes
+                ctypes.CDLL(None).fflush(None)  # the harness prints through C stdio
+            except Exception:
+                pass
+            os.dup2(saved, 1)
+            os.close(saved)
         value, kind, cores = res["frames_per_s"], "reference", res.get("cores", 1)
         sample = res["sample"]
         ms_step = res["ms_per_frame"]
