@@ -57,25 +57,34 @@ __global__ void cache_neighbors_kernel(uint32_t* __restrict__ neighbors, const u
             iz = int_coord(p.z, k.cell_spacing);
   const long long limit = (long long)V * k.max_neighbors;
   long long ni = id;
-  for (int cx = ix - 1; cx <= ix + 1; cx++)
-    for (int cy = iy - 1; cy <= iy + 1; cy++)
-      for (int cz = iz - 1; cz <= iz + 1; cz++) {
-        const int h = hash_coords(cx, cy, cz, k.table_size);
-        const int start = (int)cell_start[h];
-        if (start == -1) continue;
-        const int end = min((int)cell_end[h], start + k.max_neighbors);
-        for (int s = start; s < end; s++) {
-          const uint32_t nb = index[s];
-          if (nb == id) continue;
-          const f3 d = p - mk3(x[nb]);
-          if (!(dot3(d, d) < cell2)) continue;
-          const f3 dr = r - mk3(rest[nb]);
-          if (!(dot3(dr, dr) > diam2)) continue;
-          neighbors[ni] = nb;
-          ni += V;
-          if (ni >= limit) return;
-        }
+  // same cell order as the reference; the 9 cell ranges of a plane are fetched together so their
+  // latencies overlap (the kernel is a chain of dependent loads: hash -> range -> index -> position)
+  for (int cx = ix - 1; cx <= ix + 1; cx++) {
+    int st[9], en[9];
+#pragma unroll
+    for (int j = 0; j < 9; j++) {
+      const int h = hash_coords(cx, iy - 1 + j / 3, iz - 1 + j % 3, k.table_size);
+      st[j] = (int)cell_start[h];
+      en[j] = (int)cell_end[h];  // meaningless where the cell is empty; not used then
+    }
+#pragma unroll
+    for (int j = 0; j < 9; j++) {
+      const int start = st[j];
+      if (start == -1) continue;
+      const int end = min(en[j], start + k.max_neighbors);
+      for (int s = start; s < end; s++) {
+        const uint32_t nb = index[s];
+        if (nb == id) continue;
+        const f3 d = p - mk3(x[nb]);
+        if (!(dot3(d, d) < cell2)) continue;
+        const f3 dr = r - mk3(rest[nb]);
+        if (!(dot3(dr, dr) > diam2)) continue;
+        neighbors[ni] = nb;
+        ni += V;
+        if (ni >= limit) return;
       }
+    }
+  }
   if (ni < limit) neighbors[ni] = 0xFFFFFFFFu;
 }
 
