@@ -286,7 +286,7 @@ typedef struct xrt_stats {
 } xrt_stats;
 
 /* Deterministic greedy colouring (replaces GraphColoring::Paint's random
- * palette, graph_coloring/Base.cu:163-317, in O(n)).  arity 2 or 4. */
+ * palette, graph_coloring/Base.cu:163-317, in O(n)).  arity 2 (stretch), 3 (FEM strain: triangles) or 4 (bend). */
 int xrt_greedy_color(const uint32_t* idx, size_t n, int arity, uint32_t n_verts,
                      uint32_t* colors, uint32_t* n_colors);
 
@@ -298,6 +298,23 @@ int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts,
                              uint32_t* morton, uint32_t* sorted_object,
                              uint32_t* nodes, float* aabbs,
                              int32_t* esc_int, int32_t* esc_ext, float* build_ms);
+
+/* Quality-mode cloth model on the GPU: orthotropic StVK strain
+ * per triangle and isometric bending per hinge as coloured Gauss-Seidel passes,
+ * `iterations` times [every strain colour, then every bending colour], the inner
+ * loop of ClothSolverBase::SimulateQuality (ClothSolverBase.cpp:315-324).
+ * Replaces FEM::StrainSolver::Init/Solve and FEM::IsometricBendingSolver::Init/
+ * Solve (physics/dynamics/FEMSolver.cu:28-83, FEMHelper.cu:10-388).
+ * rest_pos / pos / out_pos: 3*n_verts floats; inv_mass: n_verts; tri: 3*n_faces;
+ * bend_idx: 4*n_bend (may be NULL with n_bend 0); material: xx, yy, xy
+ * stiffness, xy and yx Poisson ratio, bending stiffness; colors_*: one colour
+ * per constraint (any colouring: an improper one falls back to float atomics). */
+int xrt_fem_solve_standalone(const float* rest_pos, const float* pos, const float* inv_mass,
+                             uint32_t n_verts, const uint32_t* tri, uint32_t n_faces,
+                             const uint32_t* bend_idx, uint32_t n_bend, const float* material,
+                             const uint32_t* colors_strain, const uint32_t* colors_bend,
+                             int iterations, float dt, int device, float* out_pos,
+                             float* ms_per_iteration);
 
 /* Face-face broad phase between two triangle meshes (F_r == 0: the left mesh
  * against itself).  Replaces BVH::Traverse / TraverseSelf with

@@ -34,6 +34,9 @@ def _load():
                  ("esc_ext", i32p), ("pred", f32p)]:
         f = getattr(L, "oracle_bvh_" + n); f.argtypes = [vp]; f.restype = t
     L.oracle_bvh_used64.argtypes = [vp]; L.oracle_bvh_used64.restype = C.c_int
+    L.oracle_fem_solve.argtypes = [f32p, f32p, f32p, C.c_uint32, u32p, C.c_uint32, u32p, C.c_uint32, f32p, u32p, u32p,
+                                   C.c_int, C.c_float]
+    L.oracle_fem_solve.restype = None
     L.oracle_traverse_pairs.argtypes = [vp, vp, C.c_float, u32p, C.c_size_t]; L.oracle_traverse_pairs.restype = C.c_size_t
     L.oracle_nearest_point_f.argtypes = [f32p, f32p, f32p]; L.oracle_nearest_point_f.restype = C.c_float
     L.oracle_ray_intersect_f.argtypes = [f32p, f32p, C.c_float, f32p]; L.oracle_ray_intersect_f.restype = C.c_float
@@ -271,3 +274,13 @@ def rtri(indices, n_verts):
     out = np.zeros(F, np.uint32)
     L.oracle_rtri(_pu(tri), _pu(nb), _pu(prefix), F, _pu(out))
     return out
+
+
+def fem_solve(rest, pos, inv_mass, tri, bend_idx, material, colors_strain, colors_bend, iterations, dt):
+    """FEM strain + isometric bending (FEMHelper.cu) for `iterations` Quality-mode iterations; returns positions."""
+    rest, x, w = _f(rest).reshape(-1, 3), _f(pos).reshape(-1, 3).copy(), _f(inv_mass)
+    tri, bend = _u(tri).reshape(-1, 3), _u(bend_idx).reshape(-1, 4)
+    m, cs, cb = _f(material), _u(colors_strain), _u(colors_bend)
+    L.oracle_fem_solve(_pf(rest), _pf(x), _pf(w), len(x), _pu(tri), len(tri), _pu(bend), len(bend), _pf(m), _pu(cs),
+                       _pu(cb), int(iterations), float(dt))
+    return x

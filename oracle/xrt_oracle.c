@@ -330,6 +330,137 @@ size_t oracle_traverse_pairs(const OBvh* l, const OBvh* r, float thickness, uint
   return total;
 }
 
+/* ---- Quality-mode cloth model ------------------------------------------------
+ * FEM strain + isometric bending, physics/dynamics/FEMHelper.cu, in the order of
+ * ClothSolverBase::SimulateQuality (ClothSolverBase.cpp:315-324): per iteration every strain colour,
+ * then every bending colour; inside a colour in constraint order (a proper colouring makes that order
+ * irrelevant).  glm matrices are column-major: m[c][r]. */
+typedef struct { uint32_t i0, i1, i2; float area; float inv[2][2]; } OStrain;
+typedef struct { uint32_t i[4]; float Q[4][4]; } OIsoBend;
+
+/* ComputeStrainMeta + InitStrain_Kernel, FEMHelper.cu:10-84 */
+static OStrain fem_init_strain(const float* rest, const uint32_t* tri, uint32_t id) {
+  OStrain c;
+  c.i0 = tri[3 * id]; c.i1 = tri[3 * id + 1]; c.i2 = tri[3 * id + 2];
+  const v3 p0 = ld3(rest, c.i0), p1 = ld3(rest, c.i1), p2 = ld3(rest, c.i2);
+  const v3 n0 = cross(sub(p1, p0), sub(p2, p0));
+  c.area = 0.5f * len(n0);
+  const v3 a1 = normalize(sub(p1, p0));
+  const v3 a2 = normalize(cross(n0, a1));
+  const float u0 = dot(p0, a2), v0 = dot(p0, a1), u1 = dot(p1, a2), v1 = dot(p1, a1), u2 = dot(p2, a2), v2 = dot(p2, a1);
+  float P[2][2];
+  P[0][0] = u0 - u2; P[1][0] = v0 - v2; P[0][1] = u1 - u2; P[1][1] = v1 - v2;
+  const float det = P[0][0] * P[1][1] - P[1][0] * P[0][1]; /* glm::determinant(mat2) */
+  c.inv[0][0] = c.inv[0][1] = c.inv[1][0] = c.inv[1][1] = 0.0f;
+  if (fabsf(det) > EPS) { /* glm::inverse(mat2) */
+    const float ood = 1.0f / det;
+    c.inv[0][0] = P[1][1] * ood; c.inv[0][1] = -P[0][1] * ood;
+    c.inv[1][0] = -P[1][0] * ood; c.inv[1][1] = P[0][0] * ood;
+  }
+  return c;
+}
+static float cot_theta(v3 v, v3 w) { return dot(v, w) / len(cross(v, w)); } /* MathFunctions.cu:7-12 */
+/* ComputeHessianEnergy + InitIsometricBending_Kernel, FEMHelper.cu:221-305 */
+static OIsoBend fem_init_bend(const float* rest, const uint32_t* idx, uint32_t id) {
+  OIsoBend c;
+  for (int k = 0; k < 4; k++) c.i[k] = idx[4 * id + k];
+  const v3 p0 = ld3(rest, c.i[0]), p1 = ld3(rest, c.i[1]), p2 = ld3(rest, c.i[2]), p3 = ld3(rest, c.i[3]);
+  const v3 e0 = sub(p1, p0), e1 = sub(p2, p0), e2 = sub(p3, p0), e3 = sub(p2, p1), e4 = sub(p3, p1);
+  const float c01 = cot_theta(e0, e1), c02 = cot_theta(e0, e2), c03 = cot_theta(neg(e0), e3), c04 = cot_theta(neg(e0), e4);
+  const float A0 = 0.5f * len(cross(sub(p1, p0), sub(p2, p0))), A1 = 0.5f * len(cross(sub(p0, p1), sub(p3, p1)));
+  const float coeff = 3.0f / (A0 + A1);
+  const float K[4] = {c03 + c04, c01 + c02, -c01 - c03, -c02 - c04};
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) c.Q[j][i] = coeff * (K[i] * K[j]);
+  return c;
+}
+/* ComputeStrainCorrection + SolveStrain_Kernel, FEMHelper.cu:94-212 */
+static void fem_solve_strain(float* x, const float* w, const OStrain* c, const float* m) {
+  const v3 p0 = ld3(x, c->i0), p1 = ld3(x, c->i1), p2 = ld3(x, c->i2);
+  const float w0 = w[c->i0], w1 = w[c->i1], w2 = w[c->i2];
+  const float den = 1.0f - m[3] * m[4];
+  const float C00 = m[0] / den, C01 = m[0] * m[4] / den, C11 = m[1] / den, C10 = m[1] * m[3] / den, C22 = m[2];
+  const v3 p13 = sub(p0, p2), p23 = sub(p1, p2);
+  const float a[3] = {p13.x, p13.y, p13.z}, b[3] = {p23.x, p23.y, p23.z};
+  float F[3][2];
+  for (int i = 0; i < 3; i++) {
+    F[i][0] = a[i] * c->inv[0][0] + b[i] * c->inv[1][0];
+    F[i][1] = a[i] * c->inv[0][1] + b[i] * c->inv[1][1];
+  }
+  const float e00 = 0.5f * (F[0][0] * F[0][0] + F[1][0] * F[1][0] + F[2][0] * F[2][0] - 1.0f);
+  const float e11 = 0.5f * (F[0][1] * F[0][1] + F[1][1] * F[1][1] + F[2][1] * F[2][1] - 1.0f);
+  const float e01 = 0.5f * (F[0][0] * F[0][1] + F[1][0] * F[1][1] + F[2][0] * F[2][1]);
+  const float s00 = C00 * e00 + C01 * e11 + 0.0f * e01;
+  const float s11 = C10 * e00 + C11 * e11 + 0.0f * e01;
+  const float s01 = 0.0f * e00 + 0.0f * e11 + C22 * e01;
+  float pk[3][2];
+  for (int i = 0; i < 3; i++) {
+    pk[i][0] = s00 * F[i][0] + s01 * F[i][1];
+    pk[i][1] = s01 * F[i][0] + s11 * F[i][1];
+  }
+  float psi = 0.0f;
+  psi += e00 * s00; psi += e01 * s01; psi += e01 * s01; psi += e11 * s11;
+  psi = 0.5f * psi;
+  const float energy = c->area * psi;
+  float g0[3], g1[3];
+  for (int i = 0; i < 3; i++) {
+    g0[i] = (c->inv[0][0] * pk[i][0] + c->inv[0][1] * pk[i][1]) * c->area;
+    g1[i] = (c->inv[1][0] * pk[i][0] + c->inv[1][1] * pk[i][1]) * c->area;
+  }
+  const v3 G0 = V(g0[0], g0[1], g0[2]), G1 = V(g1[0], g1[1], g1[2]);
+  const v3 G2 = V(-G0.x - G1.x, -G0.y - G1.y, -G0.z - G1.z);
+  float sum = w0 * dot(G0, G0);
+  sum += w1 * dot(G1, G1);
+  sum += w2 * dot(G2, G2);
+  if (!(fabsf(sum) > EPS)) return;
+  const float s = energy / sum;
+  if (w0 > EPS) st3(x, c->i0, add(ld3(x, c->i0), mul(G0, -(s * w0))));
+  if (w1 > EPS) st3(x, c->i1, add(ld3(x, c->i1), mul(G1, -(s * w1))));
+  if (w2 > EPS) st3(x, c->i2, add(ld3(x, c->i2), mul(G2, -(s * w2))));
+}
+/* SolveIsometricBending_Kernel, FEMHelper.cu:317-388 */
+static void fem_solve_bend(float* x, const float* w, const OIsoBend* c, float* lambda, float stiffness, float dt, int iter) {
+  if (iter == 0) *lambda = 0.0f;
+  v3 p[4];
+  float wi[4];
+  for (int k = 0; k < 4; k++) { p[k] = ld3(x, c->i[k]); wi[k] = w[c->i[k]]; }
+  float energy = 0.0f;
+  for (int k = 0; k < 4; k++)
+    for (int j = 0; j < 4; j++) energy += c->Q[j][k] * dot(p[k], p[j]);
+  energy *= 0.5f;
+  if (fabsf(energy) < EPS) return;
+  v3 d[4] = {V(0, 0, 0), V(0, 0, 0), V(0, 0, 0), V(0, 0, 0)};
+  for (int i = 0; i < 4; i++)
+    for (int j = 0; j < 4; j++) d[j] = add(d[j], mul(p[i], c->Q[j][i]));
+  const float n0 = dot(d[0], d[0]), n1 = dot(d[1], d[1]), n2 = dot(d[2], d[2]), n3 = dot(d[3], d[3]);
+  const float division = (wi[0] * n0 + wi[1] * n1) + (wi[2] * n2 + wi[3] * n3); /* glm::dot(vec4, vec4) */
+  const float alpha = 1.0f / (stiffness * dt * dt);
+  const float dl = (-energy - alpha * *lambda) / (division + alpha);
+  for (int k = 0; k < 4; k++) st3(x, c->i[k], add(ld3(x, c->i[k]), mul(d[k], dl * wi[k])));
+  *lambda += dl;
+}
+/* x: [3 nv] in/out.  material: xx, yy, xy stiffness, xy / yx Poisson ratio, bending stiffness. */
+void oracle_fem_solve(const float* rest, float* x, const float* inv_mass, uint32_t nv, const uint32_t* tri, uint32_t F,
+                      const uint32_t* bend, uint32_t B, const float* material, const uint32_t* col_s,
+                      const uint32_t* col_b, int iterations, float dt) {
+  (void)nv;
+  OStrain* cs = (OStrain*)malloc(sizeof(OStrain) * (F ? F : 1));
+  OIsoBend* cb = (OIsoBend*)malloc(sizeof(OIsoBend) * (B ? B : 1));
+  float* lam = (float*)calloc(B ? B : 1, sizeof(float));
+  uint32_t ncs = 0, ncb = 0;
+  for (uint32_t i = 0; i < F; i++) { cs[i] = fem_init_strain(rest, tri, i); if (col_s[i] + 1 > ncs) ncs = col_s[i] + 1; }
+  for (uint32_t i = 0; i < B; i++) { cb[i] = fem_init_bend(rest, bend, i); if (col_b[i] + 1 > ncb) ncb = col_b[i] + 1; }
+  for (int it = 0; it < iterations; it++) {
+    for (uint32_t c = 0; c < ncs; c++)
+      for (uint32_t i = 0; i < F; i++)
+        if (col_s[i] == c) fem_solve_strain(x, inv_mass, &cs[i], material);
+    for (uint32_t c = 0; c < ncb; c++)
+      for (uint32_t i = 0; i < B; i++)
+        if (col_b[i] == c) fem_solve_bend(x, inv_mass, &cb[i], &lam[i], material[5], dt, it);
+  }
+  free(cs); free(cb); free(lam);
+}
+
 /* accessors for ctypes */
 uint32_t* oracle_bvh_morton(OBvh* b) { return b->morton; }
 uint32_t* oracle_bvh_object(OBvh* b) { return b->object; }

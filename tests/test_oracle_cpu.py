@@ -295,3 +295,93 @@ def test_pair_traversal_disjoint_and_single_face():
     one = np.array([[0, 1, 2]], np.uint32)
     p3 = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
     np.testing.assert_array_equal(O.Bvh(p3, one).pairs(None, 0.0), [[0, 0]])
+
+
+# ---- Quality-mode cloth model (row a25): FEM strain + isometric bending --------------------------
+MATERIAL = np.array([5000.0, 5000.0, 1000.0, 0.3, 0.3, 1e-3], np.float32)  # xx, yy, xy, nu_xy, nu_yx, bending
+
+
+def _fem_case(n=9):
+    pos, tri = scene.grid_cloth(n, 0.5, 0.0, 1e-4)
+    bend_idx, _ = scene.bend_constraints(pos, tri)
+    cs, _ = X.greedy_color(tri, len(pos))
+    cb, _ = X.greedy_color(bend_idx, len(pos))
+    return pos, tri, bend_idx, cs, cb
+
+
+def _strain_energy(rest, x, tri):
+    # Green strain energy with unit isotropic stiffness: a scale-free progress measure for the tests
+    e = 0.0
+    for t in tri:
+        R = np.stack([rest[t[1]] - rest[t[0]], rest[t[2]] - rest[t[0]]], 1).astype(np.float64)
+        D = np.stack([x[t[1]] - x[t[0]], x[t[2]] - x[t[0]]], 1).astype(np.float64)
+        q, r = np.linalg.qr(R)
+        Fm = D @ np.linalg.inv(r)
+        G = 0.5 * (Fm.T @ Fm - np.eye(2))
+        e += 0.5 * abs(np.linalg.det(r)) * (G * G).sum()
+    return e
+
+
+def test_fem_rest_state_is_a_fixed_point():
+    # FEMHelper.cu:94-175: zero Green strain -> zero energy -> zero correction; a flat sheet has zero
+    # isometric bending energy (Q x = 0), so the early exit at :343 is taken
+    pos, tri, bend_idx, cs, cb = _fem_case()
+    w = np.ones(len(pos), np.float32)
+    out = O.fem_solve(pos, pos, w, tri, bend_idx, MATERIAL, cs, cb, 3, 1.0 / 60)
+    np.testing.assert_allclose(out, pos, rtol=0, atol=2e-6)
+
+
+def test_fem_strain_pulls_a_stretched_sheet_back_and_respects_pins():
+    pos, tri, bend_idx, cs, cb = _fem_case()
+    x = pos.copy()
+    x[:, 0] *= 1.2                      # 20 % stretch along x
+    w = np.ones(len(pos), np.float32)
+    w[:3] = 0.0                          # pinned vertices
+    e0 = _strain_energy(pos, x, tri)
+    mid = O.fem_solve(pos, x, w, tri, bend_idx, MATERIAL, cs, cb, 5, 1.0 / 60)
+    out = O.fem_solve(pos, x, w, tri, bend_idx, MATERIAL, cs, cb, 20, 1.0 / 60)
+    assert np.isfinite(out).all()
+    # the constraint is the element's energy itself (C = A psi, step = C / |grad C|^2): monotone, not fast
+    assert _strain_energy(pos, out, tri) < _strain_energy(pos, mid, tri) < e0
+    assert _strain_energy(pos, out, tri) < 0.5 * e0
+    np.testing.assert_array_equal(out[:3], x[:3])
+
+
+def test_fem_is_invariant_under_rigid_motion():
+    pos, tri, bend_idx, cs, cb = _fem_case(7)
+    rng = np.random.default_rng(3)
+    x = pos + rng.normal(0, 5e-3, pos.shape).astype(np.float32)
+    w = np.ones(len(pos), np.float32)
+    a = 0.7
+    R = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]], np.float32)
+    t = np.array([0.3, -0.2, 0.5], np.float32)
+    out = O.fem_solve(pos, x, w, tri, bend_idx, MATERIAL, cs, cb, 4, 1.0 / 60)
+    out_r = O.fem_solve(pos, x @ R.T + t, w, tri, bend_idx, MATERIAL, cs, cb, 4, 1.0 / 60)
+    np.testing.assert_allclose(out_r, out @ R.T + t, rtol=0, atol=5e-5)
+
+
+def test_fem_bending_flattens_a_fold():
+    pos, tri, bend_idx, cs, cb = _fem_case()
+    x = pos.copy()
+    right = x[:, 0] > x[:, 0].mean()
+    x[right, 1] += (x[right, 0] - x[:, 0].mean()) * 0.8   # fold the right half up (an isometry of each half)
+    x[right, 0] = x[:, 0].mean() + (x[right, 0] - x[:, 0].mean()) * 0.6
+    w = np.ones(len(pos), np.float32)
+    stiff = MATERIAL.copy()
+    stiff[5] = 10.0
+    def fold_angle(p):
+        # largest dihedral angle over the hinges ([0],[1] shared edge, [2],[3] opposite vertices)
+        a, b, c, d = (p[bend_idx[:, k]].astype(np.float64) for k in range(4))
+        n1, n2 = np.cross(b - a, c - a), np.cross(d - a, b - a)
+        cosang = (n1 * n2).sum(1) / np.linalg.norm(n1, axis=1) / np.linalg.norm(n2, axis=1)
+        return np.arccos(np.clip(cosang, -1, 1)).max()
+
+    one = O.fem_solve(pos, x, w, tri, bend_idx, stiff, cs, cb, 1, 1.0 / 60)
+    out = O.fem_solve(pos, x, w, tri, bend_idx, stiff, cs, cb, 30, 1.0 / 60)
+    assert np.isfinite(out).all()
+    assert fold_angle(out) < fold_angle(one) < fold_angle(x)
+    # one iteration moves the vertices of the hinges across the fold, the rest only by the 1e-4 jitter's worth
+    # (each half is an isometry of its rest shape)
+    far = np.abs(pos[:, 0] - pos[:, 0].mean()) > 0.15
+    move = np.linalg.norm(one - x, axis=1)
+    assert move[far].max() < 0.1 * move[~far].max(), (move[far].max(), move[~far].max())

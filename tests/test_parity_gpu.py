@@ -83,6 +83,54 @@ def test_pair_traversal_edge_cases():
     np.testing.assert_array_equal(X.traverse_pairs(pd, td, thickness=1e-3, fast_div=0), O.Bvh(pd, td).pairs(None, 1e-3))
 
 
+FEM_MATERIAL = np.array([5000.0, 5000.0, 1000.0, 0.3, 0.25, 0.5], np.float32)
+
+
+def _fem_case(n, seed=11):
+    pos, tri = scene.grid_cloth(n, 1.0, 0.0, 1e-4)
+    bend_idx, _ = scene.bend_constraints(pos, tri)
+    cs, _ = X.greedy_color(tri, len(pos))
+    cb, _ = X.greedy_color(bend_idx, len(pos))
+    rng = np.random.default_rng(seed)
+    x = pos.copy()
+    x[:, 0] *= 1.1                                                     # stretched
+    x[:, 1] += 0.03 * np.sin(6 * x[:, 0]).astype(np.float32)           # wrinkled
+    x += rng.normal(0, 1e-3, x.shape).astype(np.float32)
+    w = np.ones(len(pos), np.float32)
+    w[:n] = 0.0                                                        # one pinned border row
+    return pos, tri, bend_idx, cs, cb, x, w
+
+
+@pytest.mark.parametrize("n,iters", [(6, 1), (40, 5), (120, 10)])
+def test_fem_strain_and_isometric_bending_match_the_oracle(n, iters):
+    # row a25: FEMHelper.cu:94-212 (strain) and :317-388 (bending), colour by colour as SimulateQuality runs them
+    pos, tri, bend_idx, cs, cb, x, w = _fem_case(n)
+    want = O.fem_solve(pos, x, w, tri, bend_idx, FEM_MATERIAL, cs, cb, iters, 1.0 / 60)
+    got = X.fem_solve(pos, x, w, tri, bend_idx, FEM_MATERIAL, cs, cb, iters, 1.0 / 60)
+    assert np.isfinite(got).all()
+    assert rel_rms(got, want) <= 1e-6, rel_rms(got, want)   # IEEE arithmetic in the same order: rounding only
+    assert np.abs(got - x).max() > 1e-4                     # the solve did move the sheet
+    np.testing.assert_array_equal(got[:n], x[:n])           # pinned row untouched
+
+
+def test_fem_improper_colouring_uses_atomics_and_edge_cases():
+    pos, tri, bend_idx, cs, cb, x, w = _fem_case(20)
+    # everything in one colour: races resolved by float atomics -> same answer to summation-order rounding only
+    # when the colouring is proper; here only finiteness and the pins are gated
+    got = X.fem_solve(pos, x, w, tri, bend_idx, FEM_MATERIAL, np.zeros_like(cs), np.zeros_like(cb), 3, 1.0 / 60)
+    assert np.isfinite(got).all()
+    np.testing.assert_array_equal(got[:20], x[:20])
+    # no hinges, zero iterations, out-of-range index
+    got = X.fem_solve(pos, x, w, tri, np.zeros((0, 4), np.uint32), FEM_MATERIAL, cs, np.zeros(0, np.uint32), 2, 1.0 / 60)
+    want = O.fem_solve(pos, x, w, tri, np.zeros((0, 4), np.uint32), FEM_MATERIAL, cs, np.zeros(0, np.uint32), 2, 1.0 / 60)
+    assert rel_rms(got, want) <= 1e-6
+    np.testing.assert_array_equal(X.fem_solve(pos, x, w, tri, bend_idx, FEM_MATERIAL, cs, cb, 0, 1.0 / 60), x)
+    bad = tri.copy()
+    bad[0, 0] = len(pos)
+    with pytest.raises(X.XrtError):
+        X.fem_solve(pos, x, w, bad, bend_idx, FEM_MATERIAL, cs, cb, 1, 1.0 / 60)
+
+
 def test_refit_midstep_bit_exact_boxes(small):
     s, o = pair(small)
     tgt = scene.sphere_motion(small.obs_pos, 7)

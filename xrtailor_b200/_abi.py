@@ -52,7 +52,7 @@ SYMBOLS = [
     "xrt_set_cloth_state", "xrt_set_cloth_predicted", "xrt_bvh_build_obstacle", "xrt_bvh_refit_obstacle", "xrt_generate_contacts",
     "xrt_hash_particles", "xrt_predict", "xrt_solve_iteration", "xrt_finalize", "xrt_debug_get",
     "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone", "xrt_persist_info", "xrt_batch_profile_substep", "xrt_add_binding",
-    "xrt_traverse_pairs_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
+    "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
     "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
 ]
@@ -102,6 +102,8 @@ def _load():
                                      i32p, i32p, f32p],
         "xrt_traverse_pairs_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, f32p, C.c_uint32, u32p, C.c_uint32,
                                           C.c_float, C.c_int, C.c_int, u32p, C.c_size_t, C.POINTER(C.c_size_t), f32p],
+        "xrt_fem_solve_standalone": [f32p, f32p, f32p, C.c_uint32, u32p, C.c_uint32, u32p, C.c_uint32, f32p, u32p, u32p,
+                                     C.c_int, C.c_float, C.c_int, f32p, f32p],
         "xrt_batch_create": [C.POINTER(vp), C.c_int, C.c_int, C.c_int, C.POINTER(vp)],
         "xrt_batch_step_frame_async": [vp],
         "xrt_batch_sync": [vp],

@@ -257,7 +257,7 @@ extern "C" int xrt_set_colors(xrt_solver* s, int kind, const uint32_t* colors, s
 // Gauss-Seidel order, and the reference's own order is random per run (F9).
 extern "C" int xrt_greedy_color(const uint32_t* idx, size_t n, int arity, uint32_t n_verts, uint32_t* colors,
                                 uint32_t* n_colors) {
-  if ((n && (!idx || !colors)) || (arity != 2 && arity != 4)) return XRT_ERR_INVALID;
+  if ((n && (!idx || !colors)) || (arity < 2 || arity > 4)) return XRT_ERR_INVALID;
   std::vector<uint64_t> lo(n_verts, 0), hi(n_verts, 0);
   uint32_t used = 0;
   for (size_t c = 0; c < n; c++) {

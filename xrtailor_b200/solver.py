@@ -383,3 +383,19 @@ def traverse_pairs(positions, indices, other_positions=None, other_indices=None,
     if rc:
         raise XrtError(rc, "pair traversal failed")
     return (out, ms.value) if timing else out
+
+
+def fem_solve(rest, pos, inv_mass, tri, bend_idx, material, colors_strain, colors_bend, iterations, dt, device=0,
+              timing=False):
+    """FEM::StrainSolver + FEM::IsometricBendingSolver (FEMSolver.cu) for `iterations` Quality-mode iterations on
+    the GPU; returns the positions."""
+    rest, x, w = _f32(rest).reshape(-1, 3), _f32(pos).reshape(-1, 3), _f32(inv_mass)
+    tri, bend = _u32(tri).reshape(-1, 3), _u32(bend_idx).reshape(-1, 4)
+    m, cs, cb = _f32(material), _u32(colors_strain), _u32(colors_bend)
+    out, ms = np.empty_like(x), C.c_float()
+    rc = lib.xrt_fem_solve_standalone(_pf(rest), _pf(x), _pf(w), len(x), _pu(tri), len(tri), _pu(bend), len(bend),
+                                      _pf(m), _pu(cs), _pu(cb), int(iterations), float(dt), device, _pf(out),
+                                      C.byref(ms))
+    if rc:
+        raise XrtError(rc, "FEM solve failed (no CUDA device? there is no CPU fallback)")
+    return (out, ms.value) if timing else out
