@@ -21,6 +21,7 @@
 #include <xrtailor/physics/broad_phase/spatial_hash/SpatialHashGPU.cuh>
 #include <xrtailor/physics/dynamics/BasicSolver.cuh>
 #include <xrtailor/physics/dynamics/BindingConstraint.cuh>
+#include <xrtailor/physics/dynamics/FEMSolver.cuh>
 #include <xrtailor/physics/dynamics/LongRangeAttachments.cuh>
 #include <xrtailor/physics/pbd_collision/Constraint.cuh>
 #include <xrtailor/physics/representative_triangle/RTriangle.cuh>
@@ -407,6 +408,42 @@ void ref_generate_contacts(void* h) {
 void ref_get_rtri(void* h, uint* out, int n) {
   auto* s = (RefSolver*)h;
   thrust::copy_n(s->obstacle_rtri->r_tris.begin(), n, out);
+}
+
+// Quality-mode cloth model on the handle's cloth (row a25): the reference's own FEM::StrainSolver and
+// FEM::IsometricBendingSolver, set up as ClothSolverBase::SetupInternalDynamics does
+// (pipeline/base/ClothSolverBase.cpp:468-486) and iterated as SimulateQuality does (:315-324), from the
+// predicted positions `pos`.  The solvers colour themselves with a random palette; the given colours
+// overwrite GraphColoring::colors / n_colors so both sides sweep in the same order.
+// material: xx, yy, xy stiffness, xy / yx Poisson ratio, bending stiffness.
+int ref_fem_solve(void* h, const float* pos, const float* material, const uint* bend_idx, int nb, const uint* col_s,
+                  int ncs, const uint* col_b, int ncb, int iterations, float dt, float* out_pos) {
+  auto* s = (RefSolver*)h;
+  const int F = s->cloth->NumFaces();
+  ref_set_cloth_state(h, nullptr, pos, nullptr);
+  FEM::StrainSolver strain(pointer(s->cloth->faces), F, 1234u);
+  strain.Init(pointer(s->pool->initial_positions), pointer(s->cloth->faces), material[0], material[1], material[2],
+              material[3], material[4]);
+  thrust::copy_n(col_s, F, strain.Coloring()->colors.begin());
+  strain.Coloring()->n_colors = ncs;
+  FEM::IsometricBendingSolver bend;
+  if (nb) {
+    std::vector<uint> bi(bend_idx, bend_idx + 4 * (size_t)nb);
+    std::vector<Scalar> ba(nb, 0.0f);
+    bend.AddCloth(bi, ba);
+    bend.SetupGraphColoring(1234u);
+    bend.Init(pointer(s->pool->initial_positions), material[5]);
+    thrust::copy_n(col_b, nb, bend.Coloring()->colors.begin());
+    bend.Coloring()->n_colors = ncb;
+  }
+  for (int it = 0; it < iterations; it++) {
+    for (int c = 0; c < ncs; c++) strain.Solve(pointer(s->cloth->nodes), c);
+    if (nb)
+      for (int c = 0; c < ncb; c++) bend.Solve(pointer(s->cloth->nodes), c, it, dt);
+  }
+  if (cudaDeviceSynchronize() != cudaSuccess) return 1;
+  ref_get_state(h, 0, nullptr, out_pos, nullptr, nullptr);
+  return 0;
 }
 
 void ref_destroy(void* h) {

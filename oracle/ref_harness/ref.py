@@ -44,6 +44,8 @@ def lib():
         L.ref_get_contacts.argtypes = [vp, i32p, f32p, i32p, f32p, f32p]; L.ref_get_contacts.restype = None
         L.ref_generate_contacts.argtypes = [vp]; L.ref_generate_contacts.restype = None
         L.ref_get_rtri.argtypes = [vp, u32p, C.c_int]; L.ref_get_rtri.restype = None
+        L.ref_fem_solve.argtypes = [vp, f32p, f32p, u32p, C.c_int, u32p, C.c_int, u32p, C.c_int, C.c_int, C.c_float, f32p]
+        L.ref_fem_solve.restype = C.c_int
         L.ref_destroy.argtypes = [vp]; L.ref_destroy.restype = None
         _lib = L
     return _lib
@@ -138,6 +140,18 @@ class RefSolver:
         ee = np.zeros((self.E, 12), np.float32)
         lib().ref_get_contacts(self.h, _pi(vi), _pf(vq), _pi(ri), _pf(rq), _pf(ee))
         return dict(vf_idx=vi, vf_q=vq, rt_idx=ri, rt_q=rq, ee=ee)
+
+    def fem_solve(self, pos, material, bend_idx, colors_strain, colors_bend, iterations, dt):
+        """The reference's FEM::StrainSolver + FEM::IsometricBendingSolver on this solver's cloth, from predicted
+        positions `pos`, with the given colours injected (row a25)."""
+        pos, m = _f(pos).reshape(-1, 3), _f(material)
+        bend, cs, cb = _u(bend_idx).reshape(-1, 4), _u(colors_strain), _u(colors_bend)
+        out = np.zeros_like(pos)
+        rc = lib().ref_fem_solve(self.h, _pf(pos), _pf(m), _pu(bend), len(bend), _pu(cs), int(cs.max()) + 1, _pu(cb),
+                                 (int(cb.max()) + 1) if len(cb) else 0, int(iterations), float(dt), _pf(out))
+        if rc:
+            raise RuntimeError("ref_fem_solve failed")
+        return out
 
     def rtri(self):
         out = np.zeros(self.Fo, np.uint32)

@@ -207,3 +207,57 @@ def test_c2_bindings_against_the_reference():
     assert np.abs(r.state(0)["x0"][ring, 1] - sc.cloth_pos[ring, 1]).max() < 0.08
     assert max(errs) <= 1e-3   # 1e-3 m RMS over 10 frames
     s.close(); r.close()
+
+
+def test_fem_cloth_model_against_the_reference(trio):
+    """Row a25 pinned on the reference's own code: FEM::StrainSolver + FEM::IsometricBendingSolver
+    (FEMSolver.cu, FEMHelper.cu) through the harness, colours injected, against the product's CUDA passes and
+    the CPU oracle.  Runs last: it overwrites the shared reference solver's predicted positions."""
+    sc, r, p, _ = trio
+    pos, tri = sc.cloth_pos, sc.cloth_tri
+    bend_idx = sc.bend_idx
+    cs, _n = X.greedy_color(tri, len(pos))
+    cb, _n = X.greedy_color(bend_idx, len(pos))
+    no_b, no_c = np.zeros((0, 4), np.uint32), np.zeros(0, np.uint32)
+    material = np.array([5000.0, 5000.0, 1000.0, 0.3, 0.25, 0.5], np.float32)
+    rng = np.random.default_rng(5)
+    x = pos.copy()
+    x[:, 0] *= 1.08
+    x[:, 1] += 0.02 * np.sin(7 * x[:, 0]).astype(np.float32)
+    x += rng.normal(0, 5e-4, x.shape).astype(np.float32)
+    w = sc.inv_mass.astype(np.float32)
+    # strain: agrees with the reference's --use_fast_math build to rounding
+    for iters in (1, 5):
+        ref = r.fem_solve(x, material, no_b, cs, no_c, iters, 1.0 / 60)
+        got = X.fem_solve(pos, x, w, tri, no_b, material, cs, no_c, iters, 1.0 / 60)
+        cpu = O.fem_solve(pos, x, w, tri, no_b, material, cs, no_c, iters, 1.0 / 60)
+        assert np.isfinite(ref).all() and np.abs(ref - x).max() > 1e-4      # the reference did move the sheet
+        print("strain %d it: product vs reference %.2e, oracle vs reference %.2e (relative RMS)"
+              % (iters, rel_rms(got, ref), rel_rms(cpu, ref)))
+        assert rel_rms(got, ref) <= 1e-6, rel_rms(got, ref)
+        assert rel_rms(cpu, ref) <= 1e-6, rel_rms(cpu, ref)     # pins the restatement
+    # bending: the reference evaluates the hinge energy as sum Q_jk x_j.x_k in single precision on metre-sized
+    # coordinates -- terms of order 1e3 cancelling to 1e-3 -- so its own result carries a rounding floor of
+    # ~5e-6 m per pass (a flat sheet "moves" by that much); the FMA contraction of its build lands elsewhere
+    # on that floor than IEEE arithmetic does.  Gate: absolute difference at the floor for a gently bent sheet,
+    # relative difference of the displacement <= 1 % once the sheet is bent enough to rise above it.
+    soft = np.array([1e-6, 1e-6, 1e-6, 0.3, 0.3, 0.5], np.float32)
+    for amp, rel_tol in ((0.002, None), (0.03, 1e-2)):
+        xb = pos.copy()
+        xb[:, 1] += (amp * np.sin(40 * xb[:, 0]) * np.cos(33 * xb[:, 2])).astype(np.float32)
+        for iters in (1, 3):
+            ref = r.fem_solve(xb, soft, bend_idx, cs, cb, iters, 1.0 / 60)
+            got = X.fem_solve(pos, xb, w, tri, bend_idx, soft, cs, cb, iters, 1.0 / 60)
+            cpu = O.fem_solve(pos, xb, w, tri, bend_idx, soft, cs, cb, iters, 1.0 / 60)
+            for name, mine in (("product", got), ("oracle", cpu)):
+                d = rms(mine, ref)
+                rel = d / max(rms(ref, xb), 1e-30)
+                print("bending amp %.3f %d it: %s vs reference %.2e m RMS (%.1e of the displacement)"
+                      % (amp, iters, name, d, rel))
+                assert d <= 2e-5, d
+                if rel_tol:
+                    assert rel <= rel_tol, rel
+    # both together, the configuration of the first block
+    ref = r.fem_solve(x, material, bend_idx, cs, cb, 5, 1.0 / 60)
+    got = X.fem_solve(pos, x, w, tri, bend_idx, material, cs, cb, 5, 1.0 / 60)
+    assert rms(got, ref) <= 5e-5, rms(got, ref)
