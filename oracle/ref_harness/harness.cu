@@ -446,6 +446,41 @@ int ref_fem_solve(void* h, const float* pos, const float* material, const uint* 
   return 0;
 }
 
+// Face-face broad phase (row a16) by the reference's own BVH::UpdateData + Construct + Traverse
+// (BVH.cu:565-573,618-722,1315-1340) on the cloth's and the obstacle's current positions (x0).
+// self != 0: the cloth tree against itself.  Writes at most cap pairs (face indices local to each
+// mesh); returns the number found.
+__global__ void PairIndex_Kernel(const PairFF* p, uint* out, int n, int off_l, int off_r) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[2 * i] = (uint)(p[i].first->index - off_l);
+  out[2 * i + 1] = (uint)(p[i].second->index - off_r);
+}
+long long ref_traverse_pairs(void* h, int self, float thickness, uint* out, long long cap) {
+  auto* s = (RefSolver*)h;
+  auto cloth_bvh = std::make_shared<BVH>();
+  cloth_bvh->UpdateData(pointer(s->cloth->faces), 0.0f, false, s->cloth->NumFaces());
+  cloth_bvh->Construct();
+  auto rhs = cloth_bvh;
+  if (!self) {
+    rhs = std::make_shared<BVH>();
+    rhs->UpdateData(pointer(s->obstacle->faces), 0.0f, false, s->obstacle->NumFaces());
+    rhs->Construct();
+  }
+  Scalar th = thickness;
+  thrust::device_vector<PairFF> pairs =
+      Traverse(cloth_bvh, rhs, pointer(s->cloth->faces), pointer(self ? s->cloth->faces : s->obstacle->faces), th);
+  const long long n = (long long)pairs.size();
+  if (n && n <= cap) {
+    thrust::device_vector<uint> idx(2 * (size_t)n);
+    // Face::index is local to its mesh (PhysicsMeshHelper.cu:52)
+    PairIndex_Kernel<<<(unsigned)((n + 255) / 256), 256>>>(pointer(pairs), pointer(idx), (int)n, 0, 0);
+    cudaDeviceSynchronize();
+    thrust::copy(idx.begin(), idx.end(), out);
+  }
+  return n;
+}
+
 void ref_destroy(void* h) {
   auto* s = (RefSolver*)h;
   cudaFree(s->d_tmp);

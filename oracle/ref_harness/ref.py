@@ -46,6 +46,8 @@ def lib():
         L.ref_get_rtri.argtypes = [vp, u32p, C.c_int]; L.ref_get_rtri.restype = None
         L.ref_fem_solve.argtypes = [vp, f32p, f32p, u32p, C.c_int, u32p, C.c_int, u32p, C.c_int, C.c_int, C.c_float, f32p]
         L.ref_fem_solve.restype = C.c_int
+        L.ref_traverse_pairs.argtypes = [vp, C.c_int, C.c_float, u32p, C.c_longlong]
+        L.ref_traverse_pairs.restype = C.c_longlong
         L.ref_destroy.argtypes = [vp]; L.ref_destroy.restype = None
         _lib = L
     return _lib
@@ -151,6 +153,15 @@ class RefSolver:
                                  (int(cb.max()) + 1) if len(cb) else 0, int(iterations), float(dt), _pf(out))
         if rc:
             raise RuntimeError("ref_fem_solve failed")
+        return out
+
+    def traverse_pairs(self, self_mode=False, thickness=0.0):
+        """BVH::UpdateData + Construct + Traverse on the current cloth / obstacle positions (row a16): rows
+        (cloth face, other face) in the reference's order."""
+        n = lib().ref_traverse_pairs(self.h, int(self_mode), float(thickness), None, 0)
+        out = np.zeros((n, 2), np.uint32)
+        if n:
+            lib().ref_traverse_pairs(self.h, int(self_mode), float(thickness), _pu(out), n)
         return out
 
     def rtri(self):

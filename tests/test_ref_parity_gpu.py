@@ -209,6 +209,24 @@ def test_c2_bindings_against_the_reference():
     s.close(); r.close()
 
 
+def test_pair_lists_against_the_reference(trio):
+    """Row a16 pinned on the reference's own BVH::Traverse (CountPairs + inclusive_scan + FindPairs,
+    BVH.cu:1149-1340) on the meshes as they stand after the frames above: same pairs in the same order."""
+    sc, r, p, _ = trio
+    cx, ox = r.state(0)["x0"], r.state(1)["x0"]
+    for th in (1e-3, 1e-2):
+        ref = r.traverse_pairs(False, th)
+        got = X.traverse_pairs(cx, sc.cloth_tri, ox, sc.obs_tri, thickness=th, fast_div=1)
+        print("cloth vs obstacle, thickness %g: %d pairs" % (th, len(ref)))
+        assert ref[:, 0].max(initial=0) < len(sc.cloth_tri) and ref[:, 1].max(initial=0) < len(sc.obs_tri)
+        np.testing.assert_array_equal(got, ref)
+    ref = r.traverse_pairs(True, 1e-3)
+    got = X.traverse_pairs(cx, sc.cloth_tri, thickness=1e-3, fast_div=1)
+    print("cloth self traversal: %d pairs" % len(ref))
+    assert len(ref) > len(sc.cloth_tri)
+    np.testing.assert_array_equal(got, ref)
+
+
 def test_fem_cloth_model_against_the_reference(trio):
     """Row a25 pinned on the reference's own code: FEM::StrainSolver + FEM::IsometricBendingSolver
     (FEMSolver.cu, FEMHelper.cu) through the harness, colours injected, against the product's CUDA passes and
