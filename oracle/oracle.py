@@ -74,6 +74,30 @@ def _load():
                  ("neighbors", u32p), ("p_hash", u32p), ("p_index", u32p)]:
         f = getattr(L, "oracle_scene_" + n); f.argtypes = [vp]; f.restype = t
     L.oracle_scene_cnt.argtypes = [vp, C.c_int]; L.oracle_scene_cnt.restype = u32p
+    # ---- Quality mode (xrt_oracle_quality.c) ----
+    szp = C.POINTER(C.c_size_t)
+    L.oracle_scene_set_quality.argtypes = [vp, i32p, f32p, u32p, C.c_uint32, u32p]; L.oracle_scene_set_quality.restype = None
+    for n in ["oracle_step_frame_quality", "oracle_imminent_generate", "oracle_rep_update_pairs", "oracle_rep_solve",
+              "oracle_quality_begin_frame"]:
+        f = getattr(L, n); f.argtypes = [vp]; f.restype = None
+    L.oracle_imminent_solve.argtypes = [vp, C.c_float]; L.oracle_imminent_solve.restype = None
+    L.oracle_collision_step.argtypes = [vp, C.c_float]; L.oracle_collision_step.restype = None
+    L.oracle_quality_iteration.argtypes = [vp, C.c_float, C.c_int]; L.oracle_quality_iteration.restype = None
+    L.oracle_find_impacts.argtypes = [vp, C.c_float, u32p, f32p, C.c_size_t, szp]; L.oracle_find_impacts.restype = C.c_size_t
+    L.oracle_independent_impacts.argtypes = [vp, u32p, f32p, C.c_size_t, C.c_int, u32p, f32p]
+    L.oracle_independent_impacts.restype = C.c_size_t
+    L.oracle_isolate_zones.argtypes = [vp, u32p, C.c_size_t, i32p]; L.oracle_isolate_zones.restype = C.c_int
+    L.oracle_optimize_zones.argtypes = [vp, u32p, f32p, i32p, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, i32p]
+    L.oracle_optimize_zones.restype = None
+    L.oracle_quality_num_quads.argtypes = [vp]; L.oracle_quality_num_quads.restype = C.c_size_t
+    L.oracle_quality_get_quads.argtypes = [vp, u32p, f32p]; L.oracle_quality_get_quads.restype = None
+    L.oracle_quality_num_rep_pairs.argtypes = [vp]; L.oracle_quality_num_rep_pairs.restype = C.c_size_t
+    L.oracle_quality_rep_pairs.argtypes = [vp]; L.oracle_quality_rep_pairs.restype = u32p
+    L.oracle_quality_stats.argtypes = [vp, i32p]; L.oracle_quality_stats.restype = None
+    L.oracle_quality_cloth_rtri.argtypes = [vp]; L.oracle_quality_cloth_rtri.restype = u32p
+    L.oracle_scene_ox.argtypes = [vp]; L.oracle_scene_ox.restype = f32p
+    L.oracle_bvh_update.argtypes = [vp, f32p, f32p, u32p, C.c_int]; L.oracle_bvh_update.restype = None
+    L.oracle_solve_cubic.argtypes = [C.c_float] * 4 + [f32p]; L.oracle_solve_cubic.restype = C.c_int
     return L
 
 
@@ -257,10 +281,100 @@ class Scene:
         return (_arr(L.oracle_scene_p_hash(self.h), self.V, np.uint32),
                 _arr(L.oracle_scene_p_index(self.h), self.V, np.uint32))
 
+    # ---- Quality mode (SimulateQuality, ClothSolverBase.cpp:263-362) ----
+    def set_quality(self, sc, q, strain_colors):
+        """q: any object with the xrt_quality_params fields; strain_colors: one colour per cloth face."""
+        qp = np.array([q.enable_imminent_repulsion, q.enable_pbd_repulsion], np.int32)
+        qf = np.array([q.xx_stiffness, q.yy_stiffness, q.xy_stiffness, q.xy_poisson_ratio, q.yx_poisson_ratio,
+                       q.bending_stiffness, q.imminent_thickness, q.pbd_thickness, q.relaxation_rate, q.obstacle_mass,
+                       q.impact_zone_thickness], np.float32)
+        oe = _u(sc.obs_edges) if self.Vo else None
+        self.F = len(sc.cloth_tri)
+        L.oracle_scene_set_quality(self.h, qp.ctypes.data_as(_i32p), _pf(qf), _pu(oe), 0 if oe is None else len(oe),
+                                   _pu(_u(strain_colors)))
+
+    def step_frame_quality(self):
+        L.oracle_step_frame_quality(self.h)
+
+    def quality_begin_frame(self):
+        L.oracle_quality_begin_frame(self.h)
+
+    def quality_iteration(self, it):
+        L.oracle_quality_iteration(self.h, self.dt, it)
+
+    def collision_step(self):
+        L.oracle_collision_step(self.h, self.dt)
+
+    def collision_stats(self):
+        out = np.zeros(4, np.int32)
+        L.oracle_quality_stats(self.h, out.ctypes.data_as(_i32p))
+        return dict(rounds=int(out[0]), success=int(out[1]), impacts=int(out[2]), deform=int(out[3]))
+
+    def find_impacts(self, thickness):
+        """FindImpacts with fresh ccd trees: (nodes[n,4] global ids, twn[n,9] = t, w[4], n[3], is_vf, n_pairs)."""
+        npairs = C.c_size_t(0)
+        n = L.oracle_find_impacts(self.h, thickness, None, None, 0, C.byref(npairs))
+        nodes, twn = np.zeros((n, 4), np.uint32), np.zeros((n, 9), np.float32)
+        if n:
+            L.oracle_find_impacts(self.h, thickness, _pu(nodes), _pf(twn), n, C.byref(npairs))
+        return nodes, twn, int(npairs.value)
+
+    def independent_impacts(self, nodes, twn, deform=0):
+        nodes, twn = _u(nodes).reshape(-1, 4), _f(twn).reshape(-1, 9)
+        on, ot = np.zeros_like(nodes), np.zeros_like(twn)
+        m = L.oracle_independent_impacts(self.h, _pu(nodes), _pf(twn), len(nodes), deform, _pu(on), _pf(ot))
+        return on[:m].copy(), ot[:m].copy()
+
+    def isolate_zones(self, nodes):
+        nodes = _u(nodes).reshape(-1, 4)
+        col = np.zeros(len(nodes), np.int32)
+        nc = L.oracle_isolate_zones(self.h, _pu(nodes), len(nodes), col.ctypes.data_as(_i32p))
+        return col, nc
+
+    def optimize_zones(self, nodes, twn, colors, deform, thickness, obstacle_mass):
+        nodes, twn, colors = _u(nodes).reshape(-1, 4), _f(twn).reshape(-1, 9), np.ascontiguousarray(colors, np.int32)
+        st = np.zeros(3, np.int32)
+        L.oracle_optimize_zones(self.h, _pu(nodes), _pf(twn), colors.ctypes.data_as(_i32p), len(nodes),
+                                int(colors.max()) + 1 if len(colors) else 0, deform, thickness, obstacle_mass,
+                                st.ctypes.data_as(_i32p))
+        return dict(outer=int(st[0]), line_search=int(st[1]), converged=int(st[2]))
+
+    def imminent_generate(self):
+        L.oracle_imminent_generate(self.h)
+        n = L.oracle_quality_num_quads(self.h)
+        nodes, bary = np.zeros((n, 4), np.uint32), np.zeros((n, 4), np.float32)
+        if n:
+            L.oracle_quality_get_quads(self.h, _pu(nodes), _pf(bary))
+        return nodes, bary
+
+    def imminent_solve(self):
+        L.oracle_imminent_solve(self.h, self.dt)
+
+    def rep_update_pairs(self):
+        L.oracle_rep_update_pairs(self.h)
+        n = L.oracle_quality_num_rep_pairs(self.h)
+        return _arr(L.oracle_quality_rep_pairs(self.h), 2 * n, np.uint32).reshape(-1, 2)
+
+    def rep_solve(self):
+        L.oracle_rep_solve(self.h)
+
+    def cloth_rtri(self):
+        return _arr(L.oracle_quality_cloth_rtri(self.h), self.F, np.uint32)
+
+    def obstacle_predicted(self):
+        return _arr(L.oracle_scene_ox(self.h), 3 * self.Vo, np.float32).reshape(-1, 3)
+
     def __del__(self):
         if getattr(self, "h", None):
             L.oracle_scene_free(self.h)
             self.h = None
+
+
+def solve_cubic(a, b, c, d):
+    """MathFunctions::SolveCubic (math/MathFunctions.cu:122-146): roots of a t^3 + b t^2 + c t + d."""
+    x = np.zeros(3, np.float32)
+    n = L.oracle_solve_cubic(a, b, c, d, _pf(x))
+    return x[:n].copy()
 
 
 def rtri(indices, n_verts):

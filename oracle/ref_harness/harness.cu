@@ -11,6 +11,7 @@
 // rebuild (src/pipeline/impl/smpl/ClothSolver.cpp:257-261) for a moving obstacle.
 #include <map>
 #include <memory>
+#include <set>
 #include <vector>
 
 #include <xrtailor/core/Global.hpp>
@@ -25,7 +26,26 @@
 #include <xrtailor/physics/dynamics/LongRangeAttachments.cuh>
 #include <xrtailor/physics/pbd_collision/Constraint.cuh>
 #include <xrtailor/physics/representative_triangle/RTriangle.cuh>
+#include <xrtailor/physics/impact_zone/Entry.cuh>
+#include <xrtailor/physics/impact_zone/ImpactHelper.cuh>
+#include <xrtailor/physics/impact_zone/ImpactZoneHelper.cuh>
+#include <xrtailor/physics/impact_zone/ParallelImpactZoneOptimizer.cuh>
+// the harness reads the solvers' quadrature / pair lists for the parity tests (no accessor exists)
+#define private public
+#include <xrtailor/physics/repulsion/ImminentRepulsion.cuh>
+#include <xrtailor/physics/repulsion/PBDRepulsion.cuh>
+#undef private
 #include <xrtailor/utils/Timer.hpp>
+
+namespace XRTailor {
+// the reference's own Morton kernel (broad_phase/lbvh/BVH.cu:464-481), launched by ref_get_mortons
+__global__ void ComputeMortons_Kernel(Primitive* objects, Bounds* aabbs, Bounds aabb_whole, uint* mortons,
+                                      uint num_internal_nodes, uint num_objects);
+namespace ImpactZoneOptimization {
+// defined in impact_zone/Entry.cu:25, not declared in a header
+thrust::device_vector<Impact> independentImpacts(const thrust::device_vector<Impact>& impacts, int deform);
+}  // namespace ImpactZoneOptimization
+}  // namespace XRTailor
 
 using namespace XRTailor;
 
@@ -76,7 +96,7 @@ std::vector<uint> FaceEdgeIndices(const uint* tri, int F, const uint* edges, int
 struct RefSolver {
   std::shared_ptr<MemoryPool> pool;
   std::shared_ptr<PhysicsMesh> cloth, obstacle;
-  std::shared_ptr<BVH> obstacle_bvh;
+  std::shared_ptr<XRTailor::BVH> obstacle_bvh;
   std::shared_ptr<BasicConstraint::StretchSolver> stretch;
   std::shared_ptr<BasicConstraint::BendSolver> bend;
   std::shared_ptr<BindingConstraint> binding;
@@ -87,11 +107,34 @@ struct RefSolver {
   std::shared_ptr<SpatialHashGPU> hash;
   int interleaved_hash = 3;
   bool target_pending = false;
+  // Quality mode (ClothSolverBase members, pipeline/base/ClothSolverBase.hpp)
+  std::shared_ptr<XRTailor::BVH> cloth_bvh;
+  std::shared_ptr<RTriangle> cloth_rtri;
+  std::shared_ptr<ImminentRepulsion> imminent;
+  std::shared_ptr<PBDRepulsionSolver> pbd;
+  std::shared_ptr<FEM::StrainSolver> fem_strain;
+  std::shared_ptr<FEM::IsometricBendingSolver> fem_bend;
+  bool imminent_on = true, pbd_on = true;
+  float imminent_thickness = 1e-3f, pbd_thickness = 1e-4f, relaxation_rate = 0.75f, obstacle_mass = 1e3f,
+        iz_thickness = 1e-4f;
+  int frame_index = 0;
+  thrust::device_vector<Impact> last_impacts;
+  SimParams sp;  // this solver's copy of the process-wide Global::sim_params, re-installed by use()
   float* d_tmp = nullptr;
   size_t tmp_floats = 0;
 };
 
 Timer* g_timer = nullptr;
+
+// The reference keeps its parameters in process globals (Global::sim_params and the __constant__ copy uploaded
+// by SetSimulationParams), so two solvers alive in one process overwrite each other's.  Every entry point
+// re-installs the handle's own copy first.
+RefSolver* use(void* h) {
+  auto* s = use(h);
+  Global::sim_params = s->sp;
+  SetSimulationParams(&Global::sim_params);
+  return s;
+}
 }  // namespace
 
 // Timer::CurrentTime() needs it (utils/Timer.hpp:64); no GLFW on this box
@@ -129,7 +172,7 @@ void* ref_create(const int* ip, const float* fp, const float* cpos, const float*
   s->pool = std::make_shared<MemoryPool>();
   s->cloth = std::make_shared<PhysicsMesh>(s->pool);
   s->obstacle = std::make_shared<PhysicsMesh>(s->pool);
-  s->obstacle_bvh = std::make_shared<BVH>();
+  s->obstacle_bvh = std::make_shared<XRTailor::BVH>();
   s->stretch = std::make_shared<BasicConstraint::StretchSolver>();
   s->bend = std::make_shared<BasicConstraint::BendSolver>();
   s->binding = std::make_shared<BindingConstraint>();
@@ -197,6 +240,7 @@ void* ref_create(const int* ip, const float* fp, const float* cpos, const float*
   s->stretch->SetupGraphColoring(pointer(s->cloth->edges), s->cloth->NumEdges(), seed);
   if (sp.solve_bending) s->bend->SetupGraphColoring(seed);
   cudaDeviceSynchronize();
+  s->sp = sp;
   return s;
 }
 
@@ -204,7 +248,7 @@ void* ref_create(const int* ip, const float* fp, const float* cpos, const float*
 // anchors (what ClothSolverSMPL::Start does with the garment's skin weights and bind_* lists)
 void ref_set_bindings(void* h, const uint* idx, const uint* tri3, const float* bary3, const float* stiff,
                       const float* dist, int n) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   const int V = s->cloth->NumNodes();
   thrust::host_vector<SkinParam> sk(V);
   for (int i = 0; i < V; i++) sk[i] = SkinParam{0, 0, 0, 0.f, 0.f, 0.f};
@@ -223,7 +267,7 @@ void ref_set_bindings(void* h, const uint* idx, const uint* tri3, const float* b
 }
 
 void ref_set_obstacle_target(void* h, const float* xyz) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   int n = s->obstacle->NumNodes();
   cudaMemcpy(s->d_tmp, xyz, 3 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice);
   SetTarget_Kernel<<<(n + 255) / 256, 256>>>(pointer(s->obstacle->nodes), s->d_tmp, n);
@@ -232,7 +276,7 @@ void ref_set_obstacle_target(void* h, const float* xyz) {
 
 // ClothSolverBase::SimulateSwift, pipeline/base/ClothSolverBase.cpp:171-261; returns Solver_Total in ms
 float ref_step_frame(void* h) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   SimParams& sp = Global::sim_params;
   Timer::StartTimerGPU("Solver_Total");
   Scalar substep_time = Timer::FixedDeltaTime() / sp.num_substeps;
@@ -302,7 +346,7 @@ float ref_step_frame(void* h) {
 
 // which: 0 cloth, 1 obstacle; any pointer may be null
 void ref_get_state(void* h, int which, float* x0, float* x, float* v, float* nrm) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   auto& mesh = which == 0 ? s->cloth : s->obstacle;
   int n = mesh->NumNodes();
   float* d = s->d_tmp;
@@ -316,7 +360,7 @@ void ref_get_state(void* h, int which, float* x0, float* x, float* v, float* nrm
 }
 
 void ref_set_cloth_state(void* h, const float* x0, const float* x, const float* v) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   int n = s->cloth->NumNodes();
   float* d = s->d_tmp;
   size_t st = s->tmp_floats;
@@ -329,12 +373,12 @@ void ref_set_cloth_state(void* h, const float* x0, const float* x, const float* 
 }
 
 int ref_num_colors(void* h, int kind) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   return kind == 0 ? s->stretch->Coloring()->n_colors : s->bend->Coloring()->n_colors;
 }
 // GraphColoring::colors (graph_coloring/Base.cuh:36), for injection into the product (F9)
 void ref_get_colors(void* h, int kind, uint* out, int n) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   if (kind == 0) thrust::copy_n(s->stretch->Coloring()->colors.begin(), n, out);
   else thrust::copy_n(s->bend->Coloring()->colors.begin(), n, out);
 }
@@ -343,7 +387,7 @@ void ref_get_colors(void* h, int kind, uint* out, int n) {
 // implementations can be driven with the same PROPER colouring (the reference's own randomized colouring
 // leaves vertex conflicts inside colours, which makes its result depend on atomic timing)
 void ref_set_colors(void* h, int kind, const uint* colors, int n, int n_colors) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   if (kind == 0) {
     thrust::copy_n(colors, n, s->stretch->Coloring()->colors.begin());
     s->stretch->Coloring()->n_colors = n_colors;
@@ -355,7 +399,7 @@ void ref_set_colors(void* h, int kind, const uint* colors, int n, int n_colors) 
 
 // the reference's own host accessors, BVH.cu:579-602
 void ref_get_bvh(void* h, uint* morton_unused, uint* nodes, float* aabbs, int* esc_int, int* esc_ext, float* pred9) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   (void)morton_unused;
   auto hn = s->obstacle_bvh->NodesHost();
   auto hb = s->obstacle_bvh->AABBsHost();
@@ -380,7 +424,7 @@ void ref_get_bvh(void* h, uint* morton_unused, uint* nodes, float* aabbs, int* e
 
 // contacts as the reference stores them (pbd_collision/Contact.cuh)
 void ref_get_contacts(void* h, int* vf_idx, float* vf_q, int* rt_idx, float* rt_q, float* ee12) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   thrust::host_vector<VFContact> a = s->vf_dcd->contacts;
   thrust::host_vector<RTContact> b = s->vf_ccd->contacts;
   thrust::host_vector<EEContact> c = s->ee_dcd->contacts;
@@ -397,7 +441,7 @@ void ref_get_contacts(void* h, int* vf_idx, float* vf_q, int* rt_idx, float* rt_
 }
 
 void ref_generate_contacts(void* h) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   SetSimulationParams(&Global::sim_params);
   s->vf_dcd->Generate(pointer(s->cloth->nodes), s->obstacle_bvh);
   s->vf_ccd->Generate(pointer(s->cloth->nodes), s->obstacle_bvh);
@@ -405,8 +449,33 @@ void ref_generate_contacts(void* h) {
   cudaDeviceSynchronize();
 }
 
+// BVH::UpdateData(0, false) + Construct on the obstacle's current x0 (what ref_step_frame does for a moved obstacle)
+void ref_build_obstacle_bvh(void* h) {
+  auto* s = use(h);
+  s->obstacle_bvh->UpdateData(pointer(s->obstacle->faces), 0.0f, false, s->obstacle->NumFaces());
+  s->obstacle_bvh->Construct();
+  cudaDeviceSynchronize();
+}
+// Morton codes of the obstacle tree's leaves in sorted order: the reference's own ComputeMortons_Kernel run on
+// the tree's leaf boxes (sorted with the keys, BVH.cu:666) and root box, i.e. the keys Construct sorted.  Valid
+// right after a Construct (a refit grows the leaf boxes).
+void ref_get_mortons(void* h, uint* out) {
+  auto* s = use(h);
+  auto dev = s->obstacle_bvh->GetDeviceRepr();
+  const uint F = (uint)s->obstacle->NumFaces();
+  thrust::device_vector<uint> m(F);
+  ComputeMortons_Kernel<<<(F + 255) / 256, 256>>>(dev.objects, dev.aabbs, s->obstacle_bvh->GetRootAABB(), pointer(m), F - 1, F);
+  cudaDeviceSynchronize();
+  thrust::copy(m.begin(), m.end(), out);
+}
+// ClothSolverBase::AddGeodesic (ClothSolverBase.cpp:527-532)
+void ref_add_geodesics(void* h, const uint* src, const uint* tgt, const float* rest, int n) {
+  auto* s = use(h);
+  for (int i = 0; i < n; i++) s->pool->AddGeodesic(src[i], tgt[i], rest[i]);
+}
+
 void ref_get_rtri(void* h, uint* out, int n) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   thrust::copy_n(s->obstacle_rtri->r_tris.begin(), n, out);
 }
 
@@ -418,7 +487,7 @@ void ref_get_rtri(void* h, uint* out, int n) {
 // material: xx, yy, xy stiffness, xy / yx Poisson ratio, bending stiffness.
 int ref_fem_solve(void* h, const float* pos, const float* material, const uint* bend_idx, int nb, const uint* col_s,
                   int ncs, const uint* col_b, int ncb, int iterations, float dt, float* out_pos) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   const int F = s->cloth->NumFaces();
   ref_set_cloth_state(h, nullptr, pos, nullptr);
   FEM::StrainSolver strain(pointer(s->cloth->faces), F, 1234u);
@@ -457,13 +526,13 @@ __global__ void PairIndex_Kernel(const PairFF* p, uint* out, int n, int off_l, i
   out[2 * i + 1] = (uint)(p[i].second->index - off_r);
 }
 long long ref_traverse_pairs(void* h, int self, float thickness, uint* out, long long cap) {
-  auto* s = (RefSolver*)h;
-  auto cloth_bvh = std::make_shared<BVH>();
+  auto* s = use(h);
+  auto cloth_bvh = std::make_shared<XRTailor::BVH>();
   cloth_bvh->UpdateData(pointer(s->cloth->faces), 0.0f, false, s->cloth->NumFaces());
   cloth_bvh->Construct();
   auto rhs = cloth_bvh;
   if (!self) {
-    rhs = std::make_shared<BVH>();
+    rhs = std::make_shared<XRTailor::BVH>();
     rhs->UpdateData(pointer(s->obstacle->faces), 0.0f, false, s->obstacle->NumFaces());
     rhs->Construct();
   }
@@ -481,8 +550,286 @@ long long ref_traverse_pairs(void* h, int self, float thickness, uint* out, long
   return n;
 }
 
+// ---------------------------------------------------------------------------------------------
+// Quality mode.  ref_setup_quality restates what ClothSolverBase::Start (ClothSolverBase.cpp:129-139),
+// ClothSolverUniversal::Start (impl/universal/ClothSolver.cpp:66-79: SetupRTriangle, EF adjacency) and
+// SetupInternalDynamics (ClothSolverBase.cpp:468-486) do for SOLVER_MODE::QUALITY.
+// qp: imminent_on, pbd_on, n strain colours, n bend colours; qf: material xx, yy, xy, poisson xy, yx, bending,
+// imminent_thickness, pbd_thickness, relaxation_rate, obstacle_mass, impact-zone thickness.
+static void EFAdjacency(const uint* tri, int F, const uint* edges, int E, std::vector<std::set<uint>>& out) {
+  std::vector<uint> fe = FaceEdgeIndices(tri, F, edges, E);
+  out.assign(E, std::set<uint>());
+  for (int f = 0; f < F; f++)
+    for (int j = 0; j < 3; j++) out[fe[3 * f + j]].insert((uint)f);
+}
+void ref_setup_quality(void* h, const int* qp, const float* qf, const uint* ctri, const uint* cedge, const uint* otri,
+                       const uint* oedge, int Eo, const uint* bidx, int nb, const uint* col_s, const uint* col_b) {
+  auto* s = use(h);
+  SimParams& sp = Global::sim_params;
+  sp.solver_mode = SOLVER_MODE::QUALITY;
+  sp.imminent_repulsion = qp[0] != 0;
+  sp.pbd_repulsion = qp[1] != 0;
+  s->imminent_on = qp[0] != 0; s->pbd_on = qp[1] != 0;
+  s->imminent_thickness = qf[6]; s->pbd_thickness = qf[7]; s->relaxation_rate = qf[8];
+  s->obstacle_mass = qf[9]; s->iz_thickness = qf[10];
+  const int F = s->cloth->NumFaces(), E = s->cloth->NumEdges(), Fo = s->obstacle->NumFaces();
+  // SetupRTriangle (ClothSolverBase.cpp:487-521): both meshes, registered on the faces
+  if (Fo) s->obstacle->RegisterRTris(s->obstacle_rtri->r_tris);
+  BuildVFAdjacency(s->cloth, s->pool->cloth_nb_vf, s->pool->cloth_nb_vf_prefix);
+  s->cloth_rtri = std::make_shared<RTriangle>();
+  s->cloth_rtri->Init(s->cloth->DeviceIndices(), s->pool->cloth_nb_vf, s->pool->cloth_nb_vf_prefix);
+  s->cloth->RegisterRTris(s->cloth_rtri->r_tris);
+  // EF adjacency (BuildEFAdjacency + BuildDeviceEFAdjacency + RegisterEFAdjacency)
+  std::vector<std::set<uint>> ef;
+  EFAdjacency(ctri, F, cedge, E, ef);
+  BuildDeviceEFAdjacency(ef, s->pool->cloth_nb_ef, s->pool->cloth_nb_ef_prefix);
+  s->cloth->RegisterEFAdjacency(s->pool->cloth_nb_ef, s->pool->cloth_nb_ef_prefix);
+  if (Fo) {
+    EFAdjacency(otri, Fo, oedge, Eo, ef);
+    BuildDeviceEFAdjacency(ef, s->pool->obstacle_nb_ef, s->pool->obstacle_nb_ef_prefix);
+    s->obstacle->RegisterEFAdjacency(s->pool->obstacle_nb_ef, s->pool->obstacle_nb_ef_prefix);
+  }
+  s->cloth_bvh = std::make_shared<XRTailor::BVH>();
+  s->imminent = std::make_shared<ImminentRepulsion>();
+  s->imminent->InitializeDeltas(s->cloth->NumNodes());
+  s->pbd = std::make_shared<PBDRepulsionSolver>(s->cloth.get());
+  // FEM solvers with the caller's colours (the reference colours them randomly)
+  s->fem_strain = std::make_shared<FEM::StrainSolver>(pointer(s->cloth->faces), F, 1234u);
+  s->fem_strain->Init(pointer(s->pool->initial_positions), pointer(s->cloth->faces), qf[0], qf[1], qf[2], qf[3], qf[4]);
+  thrust::copy_n(col_s, F, s->fem_strain->Coloring()->colors.begin());
+  s->fem_strain->Coloring()->n_colors = qp[2];
+  s->fem_bend = std::make_shared<FEM::IsometricBendingSolver>();
+  if (nb && sp.solve_bending) {
+    std::vector<uint> bi(bidx, bidx + 4 * (size_t)nb);
+    std::vector<Scalar> ba(nb, 0.0f);
+    s->fem_bend->AddCloth(bi, ba);
+    s->fem_bend->SetupGraphColoring(1234u);
+    s->fem_bend->Init(pointer(s->pool->initial_positions), qf[5]);
+    thrust::copy_n(col_b, nb, s->fem_bend->Coloring()->colors.begin());
+    s->fem_bend->Coloring()->n_colors = qp[3];
+  }
+  cudaDeviceSynchronize();
+  s->sp = sp;
+}
+
+// ClothSolverBase::SimulateQuality, pipeline/base/ClothSolverBase.cpp:263-362 (icm_enable is off: the ICM object
+// the reference allocates per frame and GIADetangleStep are left out); returns Solver_Total in ms
+float ref_step_frame_quality(void* h) {
+  auto* s = use(h);
+  SimParams& sp = Global::sim_params;
+  Timer::StartTimerGPU("Solver_Total");
+  Scalar substep_time = Timer::FixedDeltaTime() / sp.num_substeps;
+  SetSimulationParams(&sp);
+  if (s->target_pending) {  // UpdateObstacleAnimationFrame, impl/smpl/ClothSolver.cpp:257-261
+    ScopedTimerGPU timer("Solver_UpdateBVH");
+    s->obstacle_bvh->UpdateData(pointer(s->obstacle->faces), 0.0f, false, s->obstacle->NumFaces());
+    s->obstacle_bvh->Construct();
+    s->target_pending = false;
+  }
+  s->cloth_bvh->UpdateData(pointer(s->cloth->faces), 0.0f, false, s->cloth->NumFaces());
+  s->cloth_bvh->Construct();
+  if (s->imminent_on) {
+    s->imminent->UpdateProximity(s->cloth.get(), s->obstacle.get(), s->cloth_bvh.get(), s->obstacle_bvh.get(), 1e-6f);
+    s->imminent->Generate();
+  }
+  s->obstacle_bvh->Update(pointer(s->obstacle->faces), true);
+  for (int substep = 0; substep < sp.num_substeps; substep++) {
+    PredictPositions(pointer(s->cloth->nodes), substep_time, s->cloth->NumNodes());
+    for (int iteration = 0; iteration < sp.num_iterations; iteration++) {
+      if (s->imminent_on)
+        s->imminent->Solve(s->cloth.get(), s->imminent_thickness, true, s->relaxation_rate, substep_time, s->frame_index,
+                           iteration);
+      if (s->pbd_on) {
+        if (iteration % 10 == 0)
+          s->pbd->UpdatePairs(s->cloth.get(), s->obstacle.get(), s->cloth_bvh.get(), s->obstacle_bvh.get(), 1e-6f);
+        s->pbd->SolveNoProximity(s->cloth.get(), s->pbd_thickness, s->relaxation_rate, substep_time, s->frame_index,
+                                 iteration);
+      }
+      for (int c = 0; c < s->fem_strain->Coloring()->n_colors; c++) s->fem_strain->Solve(pointer(s->cloth->nodes), c);
+      if (sp.solve_bending && s->fem_bend->Coloring())
+        for (int c = 0; c < s->fem_bend->Coloring()->n_colors; c++)
+          s->fem_bend->Solve(pointer(s->cloth->nodes), c, iteration, substep_time);
+      {
+        ScopedTimerGPU timer("Solver_SolveLRA");
+        if (sp.geodesic_LRA)
+          SolveGeodesicLRA(pointer(s->cloth->nodes), pointer(s->pool->geodesic_src_indices),
+                           pointer(s->pool->geodesic_tgt_indices), pointer(s->pool->geodesic_rest_length),
+                           s->pool->NumGeodesics(), sp.long_range_stretchiness);
+      }
+      s->binding->Solve(pointer(s->cloth->nodes), pointer(s->obstacle->nodes));
+    }
+    Timer::StartTimerGPU("Solver_CollisionStep");
+    ImpactZoneOptimization::CollisionStep(s->cloth, s->obstacle, s->pool, s->frame_index, substep_time, s->obstacle_mass,
+                                          s->iz_thickness);
+    Timer::EndTimerGPU("Solver_CollisionStep");
+    Finalize(pointer(s->cloth->nodes), substep_time);
+  }
+  s->obstacle->PredictedToPositions();
+  s->cloth->UpdateNormals();
+  s->obstacle->UpdateNormals();
+  Timer::EndTimerGPU("Solver_Total");
+  checkCudaErrors(cudaDeviceSynchronize());
+  Timer::NextFrame();
+  s->frame_index++;
+  return (float)Timer::GetTimerGPU("Solver_Total");
+}
+
+// -- pieces, for the parity tests ------------------------------------------------------------------
+__global__ void SnapshotX1_Kernel(Node** nodes, int n, float dt, int obstacle) {  // SetupNode / SetupObstacleNode, Entry.cu:110-124
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  nodes[i]->x1 = nodes[i]->x;
+  if (obstacle) {
+    nodes[i]->is_free = false;
+    nodes[i]->v = (nodes[i]->x - nodes[i]->x0) / dt;
+    nodes[i]->removed = false;
+  }
+}
+__global__ void ImpactRows_Kernel(const Impact* imp, int n, int V, uint* nodes, float* twn) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int j = 0; j < 4; j++) nodes[4 * i + j] = (uint)(imp[i].nodes[j]->index + (imp[i].nodes[j]->is_cloth ? 0 : V));
+  float* o = twn + 9 * i;
+  o[0] = imp[i].t;
+  for (int j = 0; j < 4; j++) o[1 + j] = imp[i].w[j];
+  for (int j = 0; j < 3; j++) o[5 + j] = imp[i].n[j];
+  o[8] = imp[i].is_vf ? 1.0f : 0.0f;
+}
+static long long ImpactsOut(RefSolver* s, const thrust::device_vector<Impact>& imp, uint* nodes, float* twn, long long cap) {
+  const long long n = (long long)imp.size();
+  if (n && n <= cap && nodes) {
+    thrust::device_vector<uint> dn(4 * (size_t)n);
+    thrust::device_vector<float> dt(9 * (size_t)n);
+    ImpactRows_Kernel<<<(unsigned)((n + 255) / 256), 256>>>(pointer(imp), (int)n, s->cloth->NumNodes(), pointer(dn), pointer(dt));
+    cudaDeviceSynchronize();
+    thrust::copy(dn.begin(), dn.end(), nodes);
+    thrust::copy(dt.begin(), dt.end(), twn);
+  }
+  return n;
+}
+// FindImpacts (ImpactHelper.cu:216-243) on the current x0 / x with the two fresh ccd trees CollisionStep builds
+// (Entry.cu:146-155).  Rows: 4 global node ids (obstacle ids offset by V) | t, w[4], n[3], is_vf.  The list is
+// kept for ref_independent_impacts.
+long long ref_find_impacts(void* h, float thickness, float dt, uint* nodes, float* twn, long long cap, long long* n_pairs) {
+  auto* s = use(h);
+  const int V = s->cloth->NumNodes(), Vo = s->obstacle->NumNodes();
+  SnapshotX1_Kernel<<<(V + 255) / 256, 256>>>(pointer(s->cloth->nodes), V, dt, 0);
+  if (Vo) SnapshotX1_Kernel<<<(Vo + 255) / 256, 256>>>(pointer(s->obstacle->nodes), Vo, dt, 1);
+  auto cb = std::make_shared<XRTailor::BVH>();
+  auto ob = std::make_shared<XRTailor::BVH>();
+  cb->UpdateData(pointer(s->cloth->faces), 0.0f, true, s->cloth->NumFaces());
+  cb->Construct(0.0f);
+  ob->UpdateData(pointer(s->obstacle->faces), 0.0f, true, s->obstacle->NumFaces());
+  ob->Construct(0.0f);
+  if (n_pairs) {
+    Scalar th = thickness;
+    *n_pairs = (long long)Traverse(cb, ob, pointer(s->cloth->faces), pointer(s->obstacle->faces), th).size() +
+               (long long)Traverse(cb, cb, pointer(s->cloth->faces), pointer(s->cloth->faces), th).size();
+  }
+  s->last_impacts = FindImpacts(cb, ob, pointer(s->cloth->faces), pointer(s->obstacle->faces), thickness, 0, 0);
+  cudaDeviceSynchronize();
+  return ImpactsOut(s, s->last_impacts, nodes, twn, cap);
+}
+// independentImpacts (Entry.cu:25-70) on the list ref_find_impacts kept
+long long ref_independent_impacts(void* h, int deform, uint* nodes, float* twn, long long cap) {
+  auto* s = use(h);
+  thrust::device_vector<Impact> ind = ImpactZoneOptimization::independentImpacts(s->last_impacts, deform);
+  cudaDeviceSynchronize();
+  return ImpactsOut(s, ind, nodes, twn, cap);
+}
+// CollisionStep (Entry.cu:140-256) on the current state
+void ref_collision_step(void* h, float dt) {
+  auto* s = use(h);
+  ImpactZoneOptimization::CollisionStep(s->cloth, s->obstacle, s->pool, s->frame_index, dt, s->obstacle_mass, s->iz_thickness);
+  cudaDeviceSynchronize();
+}
+// cloth_bvh UpdateData+Construct, ImminentRepulsion::UpdateProximity + Generate (ClothSolverBase.cpp:277-284);
+// returns the number of quadratures; rows: 4 global node ids | 4 barycentric weights
+__global__ void QuadRows_Kernel(const Quadrature* q, int n, int V, uint* nodes, float* bary) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int j = 0; j < 4; j++) {
+    nodes[4 * i + j] = (uint)(q[i].nodes[j]->index + (q[i].nodes[j]->is_cloth ? 0 : V));
+    bary[4 * i + j] = q[i].bary[j];
+  }
+}
+long long ref_imminent_generate(void* h, uint* nodes, float* bary, long long cap) {
+  auto* s = use(h);
+  SetSimulationParams(&Global::sim_params);
+  s->cloth_bvh->UpdateData(pointer(s->cloth->faces), 0.0f, false, s->cloth->NumFaces());
+  s->cloth_bvh->Construct();
+  s->imminent->UpdateProximity(s->cloth.get(), s->obstacle.get(), s->cloth_bvh.get(), s->obstacle_bvh.get(), 1e-6f);
+  s->imminent->Generate();
+  cudaDeviceSynchronize();
+  const long long n = (long long)s->imminent->quads_.size();
+  if (n && n <= cap && nodes) {
+    thrust::device_vector<uint> dn(4 * (size_t)n);
+    thrust::device_vector<float> db(4 * (size_t)n);
+    QuadRows_Kernel<<<(unsigned)((n + 255) / 256), 256>>>(pointer(s->imminent->quads_), (int)n, s->cloth->NumNodes(), pointer(dn), pointer(db));
+    cudaDeviceSynchronize();
+    thrust::copy(dn.begin(), dn.end(), nodes);
+    thrust::copy(db.begin(), db.end(), bary);
+  }
+  return n;
+}
+void ref_imminent_solve(void* h, float dt, int iteration) {
+  auto* s = use(h);
+  s->imminent->Solve(s->cloth.get(), s->imminent_thickness, true, s->relaxation_rate, dt, s->frame_index, iteration);
+  cudaDeviceSynchronize();
+}
+// PBDRepulsionSolver::UpdatePairs (PBDRepulsion.cu:22-33) -> number of pairs; rows (cloth face, other face; obstacle
+// faces offset by F)
+__global__ void PairRows_Kernel(const PairFF* p, int n, int F, uint* out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  out[2 * i] = (uint)p[i].first->index;
+  const bool cloth = p[i].second->nodes[0]->is_cloth;
+  out[2 * i + 1] = (uint)(p[i].second->index + (cloth ? 0 : F));
+}
+long long ref_rep_update_pairs(void* h, uint* out, long long cap) {
+  auto* s = use(h);
+  s->pbd->UpdatePairs(s->cloth.get(), s->obstacle.get(), s->cloth_bvh.get(), s->obstacle_bvh.get(), 1e-6f);
+  cudaDeviceSynchronize();
+  const long long n = (long long)s->pbd->pairs_.size();
+  if (n && n <= cap && out) {
+    thrust::device_vector<uint> d(2 * (size_t)n);
+    PairRows_Kernel<<<(unsigned)((n + 255) / 256), 256>>>(pointer(s->pbd->pairs_), (int)n, s->cloth->NumFaces(), pointer(d));
+    cudaDeviceSynchronize();
+    thrust::copy(d.begin(), d.end(), out);
+  }
+  return n;
+}
+void ref_rep_solve(void* h, float dt, int iteration) {
+  auto* s = use(h);
+  s->pbd->SolveNoProximity(s->cloth.get(), s->pbd_thickness, s->relaxation_rate, dt, s->frame_index, iteration);
+  cudaDeviceSynchronize();
+}
+// BVH::Update(ccd = true) on the obstacle tree (ClothSolverBase.cpp:291)
+void ref_obstacle_bvh_update(void* h) {
+  auto* s = use(h);
+  s->obstacle_bvh->Update(pointer(s->obstacle->faces), true);
+  cudaDeviceSynchronize();
+}
+void ref_get_cloth_rtri(void* h, uint* out, int n) {
+  auto* s = use(h);
+  thrust::copy_n(s->cloth_rtri->r_tris.begin(), n, out);
+}
+// obstacle state (x0, x, v), for the tests that load one state into three implementations
+void ref_set_obstacle_state(void* h, const float* x0, const float* x, const float* v) {
+  auto* s = use(h);
+  int n = s->obstacle->NumNodes();
+  float* d = s->d_tmp;
+  size_t st = s->tmp_floats;
+  if (x0) cudaMemcpy(d, x0, 3 * (size_t)n * 4, cudaMemcpyHostToDevice);
+  if (x) cudaMemcpy(d + st, x, 3 * (size_t)n * 4, cudaMemcpyHostToDevice);
+  if (v) cudaMemcpy(d + 2 * st, v, 3 * (size_t)n * 4, cudaMemcpyHostToDevice);
+  SetState_Kernel<<<(n + 255) / 256, 256>>>(pointer(s->obstacle->nodes), x0 ? d : nullptr, x ? d + st : nullptr,
+                                            v ? d + 2 * st : nullptr, n);
+  cudaDeviceSynchronize();
+}
+
 void ref_destroy(void* h) {
-  auto* s = (RefSolver*)h;
+  auto* s = use(h);
   cudaFree(s->d_tmp);
   s->cloth->Destroy();
   s->obstacle->Destroy();

@@ -10,7 +10,9 @@ import time
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO = os.path.join(_HERE, "..", "_ref", "libxrt_ref.so")
+# XRT_REF_NO_TIMERS=1 selects the build with the reference's per-kernel GPU timers stubbed (Makefile NT=1)
+SO = os.path.join(_HERE, "..", "_ref",
+                  "libxrt_ref_nt.so" if os.environ.get("XRT_REF_NO_TIMERS") == "1" else "libxrt_ref.so")
 _lib = None
 
 
@@ -49,6 +51,23 @@ def lib():
         L.ref_traverse_pairs.argtypes = [vp, C.c_int, C.c_float, u32p, C.c_longlong]
         L.ref_traverse_pairs.restype = C.c_longlong
         L.ref_destroy.argtypes = [vp]; L.ref_destroy.restype = None
+        ll, llp = C.c_longlong, C.POINTER(C.c_longlong)
+        L.ref_setup_quality.argtypes = [vp, i32p, f32p, u32p, u32p, u32p, u32p, C.c_int, u32p, C.c_int, u32p, u32p]
+        L.ref_setup_quality.restype = None
+        L.ref_step_frame_quality.argtypes = [vp]; L.ref_step_frame_quality.restype = C.c_float
+        L.ref_find_impacts.argtypes = [vp, C.c_float, C.c_float, u32p, f32p, ll, llp]; L.ref_find_impacts.restype = ll
+        L.ref_independent_impacts.argtypes = [vp, C.c_int, u32p, f32p, ll]; L.ref_independent_impacts.restype = ll
+        L.ref_collision_step.argtypes = [vp, C.c_float]; L.ref_collision_step.restype = None
+        L.ref_imminent_generate.argtypes = [vp, u32p, f32p, ll]; L.ref_imminent_generate.restype = ll
+        L.ref_imminent_solve.argtypes = [vp, C.c_float, C.c_int]; L.ref_imminent_solve.restype = None
+        L.ref_rep_update_pairs.argtypes = [vp, u32p, ll]; L.ref_rep_update_pairs.restype = ll
+        L.ref_rep_solve.argtypes = [vp, C.c_float, C.c_int]; L.ref_rep_solve.restype = None
+        L.ref_obstacle_bvh_update.argtypes = [vp]; L.ref_obstacle_bvh_update.restype = None
+        L.ref_get_cloth_rtri.argtypes = [vp, u32p, C.c_int]; L.ref_get_cloth_rtri.restype = None
+        L.ref_set_obstacle_state.argtypes = [vp, f32p, f32p, f32p]; L.ref_set_obstacle_state.restype = None
+        L.ref_build_obstacle_bvh.argtypes = [vp]; L.ref_build_obstacle_bvh.restype = None
+        L.ref_get_mortons.argtypes = [vp, u32p]; L.ref_get_mortons.restype = None
+        L.ref_add_geodesics.argtypes = [vp, u32p, u32p, f32p, C.c_int]; L.ref_add_geodesics.restype = None
         _lib = L
     return _lib
 
@@ -167,6 +186,85 @@ class RefSolver:
     def rtri(self):
         out = np.zeros(self.Fo, np.uint32)
         lib().ref_get_rtri(self.h, _pu(out), self.Fo)
+        return out
+
+    def build_obstacle_bvh(self):
+        lib().ref_build_obstacle_bvh(self.h)
+
+    def mortons(self):
+        """Sorted Morton codes of the obstacle tree, from the reference's own ComputeMortons_Kernel."""
+        out = np.zeros(self.Fo, np.uint32)
+        lib().ref_get_mortons(self.h, _pu(out))
+        return out
+
+    def add_geodesics(self, src, tgt, rest):
+        k = [_u(src), _u(tgt), _f(rest)]
+        lib().ref_add_geodesics(self.h, _pu(k[0]), _pu(k[1]), _pf(k[2]), len(k[0]))
+
+    def set_obstacle_state(self, x0=None, x=None, v=None):
+        a = [None if t is None else _f(t) for t in (x0, x, v)]
+        lib().ref_set_obstacle_state(self.h, *[_pf(t) for t in a])
+
+    # ---- Quality mode ----
+    def setup_quality(self, sc, q, strain_colors, bend_colors):
+        """q: xrt_quality_params-like object.  Colours are injected into the reference's FEM solvers."""
+        cs, cb = _u(strain_colors), _u(bend_colors)
+        qp = np.array([q.enable_imminent_repulsion, q.enable_pbd_repulsion, int(cs.max()) + 1,
+                       (int(cb.max()) + 1) if len(cb) else 0], np.int32)
+        qf = np.array([q.xx_stiffness, q.yy_stiffness, q.xy_stiffness, q.xy_poisson_ratio, q.yx_poisson_ratio,
+                       q.bending_stiffness, q.imminent_thickness, q.pbd_thickness, q.relaxation_rate, q.obstacle_mass,
+                       q.impact_zone_thickness], np.float32)
+        keep = [_u(sc.cloth_tri), _u(sc.cloth_edges), _u(sc.obs_tri), _u(sc.obs_edges), _u(sc.bend_idx)]
+        lib().ref_setup_quality(self.h, _pi(qp), _pf(qf), _pu(keep[0]), _pu(keep[1]), _pu(keep[2]), _pu(keep[3]),
+                                len(keep[3]), _pu(keep[4]), len(keep[4]), _pu(cs), _pu(cb))
+
+    def step_frame_quality(self):
+        return lib().ref_step_frame_quality(self.h)
+
+    def find_impacts(self, thickness, dt):
+        npairs = C.c_longlong(0)
+        n = lib().ref_find_impacts(self.h, thickness, dt, None, None, 0, C.byref(npairs))
+        nodes, twn = np.zeros((n, 4), np.uint32), np.zeros((n, 9), np.float32)
+        if n:
+            lib().ref_find_impacts(self.h, thickness, dt, _pu(nodes), _pf(twn), n, C.byref(npairs))
+        return nodes, twn, int(npairs.value)
+
+    def independent_impacts(self, deform=0):
+        n = lib().ref_independent_impacts(self.h, deform, None, None, 0)
+        nodes, twn = np.zeros((n, 4), np.uint32), np.zeros((n, 9), np.float32)
+        if n:
+            lib().ref_independent_impacts(self.h, deform, _pu(nodes), _pf(twn), n)
+        return nodes, twn
+
+    def collision_step(self, dt):
+        lib().ref_collision_step(self.h, dt)
+
+    def imminent_generate(self):
+        n = lib().ref_imminent_generate(self.h, None, None, 0)
+        nodes, bary = np.zeros((n, 4), np.uint32), np.zeros((n, 4), np.float32)
+        if n:
+            lib().ref_imminent_generate(self.h, _pu(nodes), _pf(bary), n)
+        return nodes, bary
+
+    def imminent_solve(self, dt, iteration=0):
+        lib().ref_imminent_solve(self.h, dt, iteration)
+
+    def rep_update_pairs(self):
+        n = lib().ref_rep_update_pairs(self.h, None, 0)
+        out = np.zeros((n, 2), np.uint32)
+        if n:
+            lib().ref_rep_update_pairs(self.h, _pu(out), n)
+        return out
+
+    def rep_solve(self, dt, iteration=0):
+        lib().ref_rep_solve(self.h, dt, iteration)
+
+    def obstacle_bvh_update(self):
+        lib().ref_obstacle_bvh_update(self.h)
+
+    def cloth_rtri(self):
+        out = np.zeros(self.F, np.uint32)
+        lib().ref_get_cloth_rtri(self.h, _pu(out), self.F)
         return out
 
     def close(self):

@@ -692,6 +692,7 @@ void oracle_rtri(const uint32_t* indices, const uint32_t* nb_vf, const uint32_t*
 /* Scene state + the Swift frame                                              */
 /* ------------------------------------------------------------------------- */
 
+typedef struct OQuality OQuality; /* Quality-mode state, xrt_oracle_quality.c */
 typedef struct {
   /* params: SimParams (core/Common.hpp:31-116) + swift self-contact config */
   int S, N, C, max_nb, interleaved, self_collision, bending, lra_on;
@@ -724,7 +725,9 @@ typedef struct {
   /* spatial hash */
   uint32_t *p_hash, *p_index, *cell_start, *cell_end, *neighbors;
   int table_size;
+  OQuality* q; /* NULL in Swift mode */
 } OScene;
+static void oracle_quality_free(OScene* s);
 
 static void* dup_mem(const void* p, size_t bytes) {
   void* r = malloc(bytes ? bytes : 1);
@@ -1279,6 +1282,7 @@ void oracle_scene_set_state(OScene* s, const float* x0, const float* v) {
 
 void oracle_scene_free(OScene* s) {
   if (!s) return;
+  oracle_quality_free(s);
   free(s->x0); free(s->x); free(s->v); free(s->invm); free(s->n); free(s->rest); free(s->tri); free(s->edge);
   free(s->s_idx); free(s->s_color); free(s->b_idx); free(s->b_color); free(s->l_src); free(s->l_tgt);
   free(s->s_rest); free(s->s_lambda); free(s->b_theta); free(s->l_rest);
@@ -1290,3 +1294,5 @@ void oracle_scene_free(OScene* s) {
   free(s->p_hash); free(s->p_index); free(s->cell_start); free(s->cell_end); free(s->neighbors);
   free(s);
 }
+
+#include "xrt_oracle_quality.c"

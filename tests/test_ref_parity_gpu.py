@@ -279,3 +279,206 @@ def test_fem_cloth_model_against_the_reference(trio):
     ref = r.fem_solve(x, material, bend_idx, cs, cb, 5, 1.0 / 60)
     got = X.fem_solve(pos, x, w, tri, bend_idx, material, cs, cb, 5, 1.0 / 60)
     assert rms(got, ref) <= 5e-5, rms(got, ref)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Parity at the benchmarked sizes, at the contact level, Morton codes, long-range attachments
+# ---------------------------------------------------------------------------------------------------
+
+def _proper_colors(sc):
+    gs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
+    gb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+    return gs, gb
+
+
+def _full_size_case(sc, motion, bindings, frames=10):
+    """One substep from rest and `frames` frames, product (per-stage graph, one persistent CTA, shared launch of 4)
+    against the reference's CUDA with the same proper colouring injected on both sides."""
+    colors = _proper_colors(sc)
+    out = {}
+    # (i) one substep from identical state
+    p = X.default_params()
+    p.particle_diameter = sc.particle_diameter()
+    p.num_substeps = 1
+    r = R.RefSolver(sc, p)
+    r.set_colors(*colors)
+    if bindings is not None:
+        r.set_bindings(*bindings)
+    r.step_frame()
+    ref1 = r.state(0)["x0"]
+    r.close()
+    for shape in (0, 1):
+        s = scene.make_solver(sc, colors=colors, bindings=bindings, morton_fast_div=1, num_substeps=1, persist_cluster=shape)
+        s.SimulateSwift()
+        out["substep_shape%d" % shape] = rel_rms(s.GetPositions(0), ref1)
+        s.close()
+    # (ii) `frames` frames with the moving obstacle
+    p.num_substeps = 4
+    r = R.RefSolver(sc, p)
+    r.set_colors(*colors)
+    if bindings is not None:
+        r.set_bindings(*bindings)
+    ss = [scene.make_solver(sc, colors=colors, bindings=bindings, morton_fast_div=1, persist_cluster=c) for c in (0, 1)]
+    batch_members = [scene.make_solver(sc, colors=colors, bindings=bindings, morton_fast_div=1, persist_cluster=1)
+                     for _ in range(4)]
+    b = X.Batch(batch_members, groups=1, workers=1)
+    errs = {0: [], 1: [], "batch": []}
+    for f in range(frames):
+        tgt = motion(f)
+        r.set_obstacle_target(tgt)
+        r.step_frame()
+        want = r.state(0)["x0"]
+        for c, s in zip((0, 1), ss):
+            s.UpdateObstacleAnimationFrame(tgt)
+            s.SimulateSwift()
+            errs[c].append(rms(s.GetPositions(0), want))
+        b.UpdateObstacleAnimationFrames(np.concatenate([tgt] * 4))
+        b.SimulateSwiftAsync()
+        g = b.GetPositions(0).reshape(4, -1, 3)
+        errs["batch"].append(max(rms(g[k], want) for k in range(4)))
+    # contact statistics at the end (north star: matching penetration-count statistics)
+    rc = r.contacts()
+    vf, rt, ee = ss[0].contacts()
+    out["contacts"] = (int((rc["vf_idx"] >= 0).sum()), int((vf["index"] >= 0).sum()))
+    out["frames"] = errs
+    b.close()
+    for s in ss + batch_members:
+        s.close()
+    r.close()
+    return out
+
+
+@pytest.mark.parametrize("which", ["c2_30k", "c1m_50k"])
+def test_full_size_parity_against_the_reference(which):
+    """The benchmarked configurations themselves (C2 at scale 1.0: 30 050 vertices, the bench default; C1m: the
+    50 176-vertex grid the >= 3x target names) against the reference's CUDA: <= 1e-5 relative RMS after one
+    substep, <= 1e-3 m RMS over 10 frames, for the per-stage graph, the persistent one-SM shape and a shared launch."""
+    if which == "c2_30k":
+        sc, body, bind = scene.body_scene(1.0)
+        motion = lambda f: body.pose(f + 1)  # noqa: E731
+    else:
+        sc, bind = scene.drop_scene(224), None
+        motion = lambda f: scene.sphere_motion(sc.obs_pos, f + 1)  # noqa: E731
+    out = _full_size_case(sc, motion, bind)
+    print(which, "verts", len(sc.cloth_pos), "one substep rel rms:", {k: "%.2e" % v for k, v in out.items() if k.startswith("substep")})
+    for k, v in out["frames"].items():
+        print(which, "rms vs reference per frame, shape", k, ["%.1e" % e for e in v])
+    print(which, "VF contacts after 10 frames (reference, product):", out["contacts"])
+    assert out["substep_shape0"] <= 1e-5 and out["substep_shape1"] <= 1e-5
+    for k, v in out["frames"].items():
+        assert max(v) <= 1e-3, (k, v)
+    n_ref, n_got = out["contacts"]
+    assert abs(n_ref - n_got) <= max(5, 0.05 * n_ref), out["contacts"]
+
+
+def test_contacts_index_for_index_against_the_reference(trio):
+    """One generation pass (VFConstraint / RTConstraint / EEConstraint::Generate, PBDCollision.cu:17-47,100-153,
+    236-268) from ONE state loaded into the product, the CPU oracle and a fresh reference solver: contact indices,
+    contact points and the live edge-contact set, index for index against the REFERENCE."""
+    sc, _, p0, _ = trio
+    p = X.default_params()
+    p.particle_diameter = p0.particle_diameter
+    colors = _proper_colors(sc)
+    settle = R.RefSolver(sc, p)
+    settle.set_colors(*colors)
+    for _ in range(12):
+        settle.step_frame()          # static sphere: the cloth drapes over it
+    st = settle.state(0)
+    settle.close()
+    dt = np.float32(p.frame_dt / p.num_substeps)
+    v1 = (st["v"] + np.array(p.gravity[:], np.float32) * dt).astype(np.float32)
+    x1 = (st["x0"] + v1 * dt).astype(np.float32)         # PredictPositions, identical bits on all three
+    r = R.RefSolver(sc, p)
+    r.set_cloth_state(st["x0"], x1, v1)
+    r.generate_contacts()
+    rc = r.contacts()
+    s = scene.make_solver(sc, colors=colors, morton_fast_div=1)
+    s.SetClothState(st["x0"], v1)
+    s.SetClothPredicted(x1)
+    s.GenerateContacts()
+    vf, rt, ee = s.contacts()
+    o = O.Scene(sc, s.params, colors)
+    o.set_state(st["x0"], v1)
+    o.set_predicted(x1)
+    o.generate_contacts()
+    oc = o.contacts()
+    n_vf, n_rt = int((rc["vf_idx"] >= 0).sum()), int((rc["rt_idx"] >= 0).sum())
+    live_ref = rc["ee"][:, 0] < 1e30
+    print("reference contacts: VF %d, RT %d, EE %d of %d edges" % (n_vf, n_rt, int(live_ref.sum()), len(live_ref)))
+    assert n_vf > 100 and live_ref.sum() > 100
+    for name, vi, vq, ri, rq, live, eerec in (
+            ("product", vf["index"], vf["q"], rt["index"], rt["q"], ee[:, 0] < 1e30, ee),
+            ("oracle", oc["vf_idx"], oc["vf_q"], oc["rt_idx"], oc["rt_q"], oc["ee"][:, 0] < 1e30, oc["ee"][:, :12])):
+        mism_vf, mism_rt = int((vi != rc["vf_idx"]).sum()), int((ri != rc["rt_idx"]).sum())
+        mism_ee = int((live != live_ref).sum())
+        print("%s vs reference: VF index mismatches %d, RT %d, EE live-set %d" % (name, mism_vf, mism_rt, mism_ee))
+        assert mism_vf == 0 and mism_rt == 0 and mism_ee == 0
+        hit = rc["vf_idx"] >= 0
+        np.testing.assert_allclose(vq[hit], rc["vf_q"][hit], atol=1e-6)
+        hit = rc["rt_idx"] >= 0
+        np.testing.assert_allclose(rq[hit], rc["rt_q"][hit], atol=2e-6)
+        np.testing.assert_allclose(eerec[live_ref][:, 1:12], rc["ee"][live_ref][:, 1:12], atol=2e-6)
+    s.close(); r.close()
+
+
+def test_morton_codes_against_the_reference(trio):
+    """Sorted Morton codes of the obstacle tree, bit for bit against the reference's own ComputeMortons_Kernel
+    (BVH.cu:464-487) run on the reference's tree, for the small scene and for the benchmark body (13.8k faces)."""
+    sc, r, p, colors = trio
+    for scn in (sc, scene.body_scene(0.05)[0]):
+        if scn is sc:
+            rr = r
+            rr.build_obstacle_bvh()
+        else:
+            pp = X.default_params()
+            pp.particle_diameter = scn.particle_diameter()
+            rr = R.RefSolver(scn, pp)
+        want = rr.mortons()
+        s = scene.make_solver(scn, colors=_proper_colors(scn), morton_fast_div=1)
+        got = s.bvh()["morton"]
+        assert (np.diff(want.astype(np.int64)) >= 0).all()           # the reference's keys come out sorted
+        np.testing.assert_array_equal(got, want)
+        print("morton codes equal: %d faces, %d distinct" % (len(want), len(np.unique(want))))
+        s.close()
+        if rr is not r:
+            rr.close()
+
+
+def test_long_range_attachments_against_the_reference():
+    """Row a7 (SolveGeodesicLRA_Kernel, LongRangeAttachments.cu:5-26): a sheet pinned at two corners, every free
+    vertex tethered to the nearer pin (one slot per vertex, so the reference's non-atomic += cannot race), with a
+    stretchiness below 1 so every tether is active from the first iteration."""
+    n = 48
+    sc = scene.drop_scene(n, sphere=(12, 24), fixed=(0, n - 1))
+    lra = scene.corner_tethers(sc, (0, n - 1))
+    colors = _proper_colors(sc)
+    kw = dict(geodesic_lra=1, long_range_stretchiness=0.97)
+    for S, frames, gate in ((1, 1, 1e-5), (4, 10, None)):
+        p = X.default_params()
+        p.particle_diameter = sc.particle_diameter()
+        p.num_substeps = S
+        p.geodesic_lra = 1
+        p.long_range_stretchiness = 0.97
+        r = R.RefSolver(sc, p)
+        r.set_colors(*colors)
+        r.add_geodesics(*lra)
+        s = scene.make_solver(sc, colors=colors, lra=lra, morton_fast_div=1, num_substeps=S, **kw)
+        s0 = scene.make_solver(sc, colors=colors, morton_fast_div=1, num_substeps=S, geodesic_lra=0)
+        o = O.Scene(sc, s.params, colors)
+        o.set_lra(*lra)
+        for f in range(frames):
+            r.step_frame(); s.SimulateSwift(); s0.SimulateSwift(); o.step_frame()
+        want, got, free_run = r.state(0)["x0"], s.GetPositions(0), s0.GetPositions(0)
+        print("LRA S=%d %d frame(s): product vs reference rel %.2e / %.2e m, oracle vs reference %.2e m, tethers moved "
+              "the sheet by %.2e m" % (S, frames, rel_rms(got, want), rms(got, want), rms(o.positions(), want),
+                                        rms(got, free_run)))
+        assert rms(got, free_run) > 1e-4                      # the tethers do something
+        if gate:
+            assert rel_rms(got, want) <= gate
+            assert rel_rms(o.positions(), want) <= gate       # pins the oracle's restatement
+        else:
+            assert rms(got, want) <= 1e-3
+        # tethers hold: no target farther than rest * stretchiness (+ what one iteration of the other constraints adds)
+        d = np.linalg.norm(got[lra[1]] - got[lra[0]], axis=1)
+        assert (d <= lra[2] * 0.97 * 1.05 + 1e-4).all()
+        s.close(); s0.close(); r.close()

@@ -185,6 +185,35 @@ def drop_scene(n=224, sphere=(64, 128), y=None, seed=SEED, fixed=()):
     return Scene(cp, ct, op, ot, fixed)
 
 
+def layered_scene(n=24, layers=2, gap=4e-3, sphere=(12, 24), y=None, side=0.5, seed=SEED, fixed=()):
+    """Quality-mode test scene: `layers` n x n sheets stacked `gap` apart above a UV sphere, as ONE cloth mesh
+    (the reference merges garments into one PhysicsMesh).  With a downward initial velocity the sheets hit the
+    sphere and each other inside one frame, which exercises the VF / EE CCD of both kinds of pairs."""
+    r = 0.3
+    if y is None:
+        y = r + 0.01
+    pos, tri = [], []
+    for k in range(layers):
+        p, t = grid_cloth(n, side, y + k * gap, 1e-4, seed + k)
+        tri.append(t + len(p) * k)
+        pos.append(p)
+    op, ot = uv_sphere(r, sphere[0], sphere[1])
+    return Scene(np.concatenate(pos), np.concatenate(tri), op, ot, fixed)
+
+
+def corner_tethers(scene, pins):
+    """Geodesic long-range attachments (ClothObjectBase::GenerateLongRangeConstraints,
+    pipeline/base/ClothObjectBase.cpp:70-94) with ONE slot per vertex: every free vertex is tethered to the
+    nearest of the pinned vertices `pins`, rest length = straight-line distance at setup (on a flat sheet that is
+    the geodesic distance).  Returns (src, tgt, rest)."""
+    pins = np.asarray(pins, np.int64)
+    pos = scene.cloth_pos
+    d = np.sqrt(((pos[:, None, :] - pos[pins][None, :, :]) ** 2).sum(-1, dtype=np.float32))
+    k = d.argmin(1)
+    tgt = np.setdiff1d(np.arange(len(pos)), pins)
+    return pins[k[tgt]].astype(np.uint32), tgt.astype(np.uint32), d[tgt, k[tgt]].astype(np.float32)
+
+
 def sphere_motion(obs_pos, frame, amp=0.05, hz=1.0, fps=60.0):
     """Synthetic body motion: the obstacle bobs vertically and breathes."""
     t = frame / fps
@@ -194,7 +223,7 @@ def sphere_motion(obs_pos, frame, amp=0.05, hz=1.0, fps=60.0):
     return out.astype(np.float32)
 
 
-def make_solver(scene, colors=None, bindings=None, **params):
+def make_solver(scene, colors=None, bindings=None, lra=None, **params):
     """Reference call order: AddCloth, AddObstacle, constraints, (colours), Start."""
     from .solver import ClothSolver
     if "particle_diameter" not in params:
@@ -207,6 +236,8 @@ def make_solver(scene, colors=None, bindings=None, **params):
     s.SetBend(scene.bend_idx, scene.bend_theta)
     if bindings is not None:
         s.AddBinding(*bindings)
+    if lra is not None:
+        s.AddGeodesic(*lra)
     if colors is not None:
         s.SetColors(0, colors[0])
         s.SetColors(1, colors[1])
