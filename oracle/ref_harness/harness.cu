@@ -130,7 +130,7 @@ Timer* g_timer = nullptr;
 // by SetSimulationParams), so two solvers alive in one process overwrite each other's.  Every entry point
 // re-installs the handle's own copy first.
 RefSolver* use(void* h) {
-  auto* s = use(h);
+  auto* s = (RefSolver*)h;
   Global::sim_params = s->sp;
   SetSimulationParams(&Global::sim_params);
   return s;

@@ -27,8 +27,8 @@ def qparams(**kw):
     return q
 
 
-def setup(n, layers, gap, sphere, N=20, q=None, S=1):
-    sc = scene.layered_scene(n, layers, gap=gap, sphere=sphere)
+def setup(n, layers, gap, sphere, N=20, q=None, S=1, wave=0.0):
+    sc = scene.layered_scene(n, layers, gap=gap, sphere=sphere, wave=wave)
     p = X.default_params()
     p.num_substeps, p.num_iterations, p.enable_self_collision = S, N, 0
     p.particle_diameter = sc.particle_diameter()
@@ -126,7 +126,7 @@ def main():
         r.close()
 
     # ---------------- B: imminent repulsion + PBD repulsion from one state ----------------
-    sc, p, q, r, o, cols = setup(24, 2, 6e-4, (12, 24), q=qparams(pbd_thickness=2e-3))
+    sc, p, q, r, o, cols = setup(24, 2, 1e-3, (12, 24), q=qparams(pbd_thickness=2e-3), wave=1e-3)
     dt = np.float32(p.frame_dt / p.num_substeps)
     x0 = sc.cloth_pos.copy()
     v = velocities(sc, 2, -0.2, -0.6)
@@ -137,7 +137,7 @@ def main():
     oqn, oqb = o.imminent_generate()
     print(f"[imminent] quadratures: reference {len(rqn)}, oracle {len(oqn)}; same rows "
           f"{rqn.shape == oqn.shape and bool((rqn == oqn).all())}")
-    if rqn.shape == oqn.shape and (rqn == oqn).all():
+    if len(rqn) and rqn.shape == oqn.shape and (rqn == oqn).all():
         print(f"[imminent] max |bary diff| {np.abs(rqb - oqb).max():.2e}")
     else:
         rs, os_ = set(map(tuple, rqn.tolist())), set(map(tuple, oqn.tolist()))

@@ -185,16 +185,20 @@ def drop_scene(n=224, sphere=(64, 128), y=None, seed=SEED, fixed=()):
     return Scene(cp, ct, op, ot, fixed)
 
 
-def layered_scene(n=24, layers=2, gap=4e-3, sphere=(12, 24), y=None, side=0.5, seed=SEED, fixed=()):
+def layered_scene(n=24, layers=2, gap=4e-3, sphere=(12, 24), y=None, side=0.5, seed=SEED, fixed=(), wave=0.0):
     """Quality-mode test scene: `layers` n x n sheets stacked `gap` apart above a UV sphere, as ONE cloth mesh
     (the reference merges garments into one PhysicsMesh).  With a downward initial velocity the sheets hit the
-    sphere and each other inside one frame, which exercises the VF / EE CCD of both kinds of pairs."""
+    sphere and each other inside one frame, which exercises the VF / EE CCD of both kinds of pairs.  wave > 0
+    ripples every odd layer by wave * sin(6 pi x / side), so neighbouring layers come within `gap - wave` of each
+    other in stripes (proximity pairs for the repulsion stages without any motion)."""
     r = 0.3
     if y is None:
         y = r + 0.01
     pos, tri = [], []
     for k in range(layers):
         p, t = grid_cloth(n, side, y + k * gap, 1e-4, seed + k)
+        if wave and k % 2:
+            p[:, 1] += np.float32(wave) * np.sin(6.0 * np.pi * p[:, 0] / side).astype(np.float32)
         tri.append(t + len(p) * k)
         pos.append(p)
     op, ot = uv_sphere(r, sphere[0], sphere[1])
