@@ -334,6 +334,89 @@ int xrt_traverse_pairs_standalone(const float* pos_l, uint32_t nv_l,
                                   int device, uint32_t* pairs, size_t capacity,
                                   size_t* n_pairs, float* traverse_ms);
 
+/* ------------------------------------------------------------------------------------------------
+ * Quality mode: ClothSolverBase::SimulateQuality (pipeline/base/ClothSolverBase.cpp:263-362).
+ * A handle on which xrt_set_quality was called before xrt_finalize_setup steps Quality frames:
+ * xrt_step_frame then runs   cloth BVH build -> imminent-repulsion proximity + quadratures ->
+ * obstacle BVH Update(ccd) -> per substep [predict; num_iterations x (imminent solve, PBD
+ * repulsion with pairs refreshed every 10th iteration, FEM strain colours, isometric-bending
+ * colours, LRA, binding); CollisionStep (cubic CCD, independent impacts, impact zones, augmented-
+ * Lagrangian zone optimiser); finalize].  num_substeps / num_iterations / gravity / damping come
+ * from the xrt_params struct, which stands for quality.solver of the reference's config (1 substep, 200 iterations).
+ * ---------------------------------------------------------------------------------------------- */
+
+/* QualityModeSettings (include/xrtailor/config/Base.hpp:47-57,108-127) */
+typedef struct xrt_quality_params {
+  float xx_stiffness, yy_stiffness, xy_stiffness;  /* FEMFabricSettings                        */
+  float xy_poisson_ratio, yx_poisson_ratio;
+  float bending_stiffness;
+  int32_t enable_imminent_repulsion;               /* RepulsionSettings                        */
+  float imminent_thickness;
+  int32_t enable_pbd_repulsion;
+  float pbd_thickness;
+  float relaxation_rate;
+  float obstacle_mass;                             /* ImpactZoneSettings                       */
+  float impact_zone_thickness;
+  /* arena sizes (every list of the collision path lives in preallocated device memory; an overflow
+   * makes the call fail with XRT_ERR_FACE_POOL and names the arena).  0 = default.               */
+  uint32_t max_pairs;       /* face-face pairs of one broad phase; default max(1 << 20, 128 F)    */
+  uint32_t max_candidates;  /* narrow-phase candidates (<= 15 per pair); default 4 * max_pairs    */
+  uint32_t max_impacts;     /* impacts / quadratures / repulsion items; default max_pairs         */
+} xrt_quality_params;
+int xrt_default_quality_params(xrt_quality_params* q);
+
+/* Turns the handle into a Quality-mode solver.  Before xrt_finalize_setup, after xrt_add_cloth and
+ * xrt_set_bend (the hinges double as the isometric-bending elements, like the reference builds both
+ * from GenerateBendingElements; bend colours are the ones of xrt_set_colors(kind 1)).
+ * strain_colors: one colour per cloth face for FEM::StrainSolver (graph_coloring/impl/
+ * FEMStrainColoring.cu), or NULL for the deterministic greedy colouring. */
+int xrt_set_quality(xrt_solver* s, const xrt_quality_params* q, const uint32_t* strain_colors);
+
+/* Result of the last CollisionStep (impact_zone/Entry.cu:140-256) */
+typedef struct xrt_collision_stats {
+  int32_t rounds;          /* FindImpacts rounds that found something                            */
+  int32_t success;         /* ended with no impact left                                          */
+  int32_t total_impacts;   /* independent impacts handed to the zones                            */
+  int32_t deform;          /* 1: the rigid pass failed and the obstacle was allowed to deform    */
+  int32_t n_pairs;         /* face pairs of the last broad phase                                 */
+  int32_t n_candidates;    /* narrow-phase tests that passed the box filters, last round         */
+  int32_t outer_iterations, line_search_steps; /* of the last zone solve (slowest zone)          */
+} xrt_collision_stats;
+
+/* The stages of a Quality frame one by one, for parity tests; each is the device code xrt_step_frame
+ * runs.  Impacts travel as rows: nodes uint32[4n] (cloth node i = i, obstacle node j = V + j) and
+ * twn float[9n] = t, w[4], n[3], is_vf. */
+int xrt_quality_begin_frame(xrt_solver* s);  /* cloth BVH UpdateData(ccd=false)+Construct, ClothSolverBase.cpp:277-278 */
+/* ImminentRepulsion::UpdateProximity + Generate (repulsion/ImminentRepulsion.cu:21-98).  nodes/bary may be
+ * NULL; *n_quads is always the full count. */
+int xrt_quality_imminent_generate(xrt_solver* s, uint32_t* nodes, float* bary, size_t capacity, size_t* n_quads);
+int xrt_quality_imminent_solve(xrt_solver* s);                      /* ImminentRepulsion::Solve, :153-169   */
+/* PBDRepulsionSolver::UpdatePairs (repulsion/PBDRepulsion.cu:22-33): pairs uint32[2n] (cloth face, other
+ * face; obstacle faces offset by F) */
+int xrt_quality_rep_update_pairs(xrt_solver* s, uint32_t* pairs, size_t capacity, size_t* n_pairs);
+int xrt_quality_rep_solve(xrt_solver* s);                           /* SolveNoProximity, :470-516           */
+int xrt_quality_obstacle_bvh_update(xrt_solver* s);                 /* obstacle_bvh_->Update(ccd), BVH.cu:836 */
+int xrt_quality_iteration(xrt_solver* s, int iteration);            /* ClothSolverBase.cpp:296-328          */
+/* FindImpacts on fresh ccd trees (impact_zone/ImpactHelper.cu:216-243, Entry.cu:146-155) */
+int xrt_quality_find_impacts(xrt_solver* s, float thickness, uint32_t* nodes, float* twn, size_t capacity,
+                             size_t* n_impacts, size_t* n_pairs, size_t* n_candidates);
+/* independentImpacts (Entry.cu:25-70) on a caller-supplied list; returns the kept rows in sorted order */
+int xrt_quality_independent_impacts(xrt_solver* s, const uint32_t* nodes, const float* twn, size_t n, int deform,
+                                    uint32_t* out_nodes, float* out_twn, size_t* n_out);
+/* IsolateImpacts (impact_zone/ImpactZoneHelper.cu:227-334): zone colour per impact, -1 beyond 100 zones */
+int xrt_quality_isolate_zones(xrt_solver* s, const uint32_t* nodes, size_t n, int32_t* colors, int32_t* n_zones);
+/* ParallelImpactZoneOptimizer ctor + ParallelOptimizer::Solve (ParallelOptimizer.cu:513-890) on a caller-
+ * supplied impact list with ascending zone colours; moves the predicted positions.  stats: outer iterations
+ * and line-search steps of the slowest zone, all zones converged. */
+int xrt_quality_optimize_zones(xrt_solver* s, const uint32_t* nodes, const float* twn, const int32_t* colors,
+                               size_t n, int n_zones, int deform, float thickness, float obstacle_mass,
+                               int32_t* stats3);
+int xrt_quality_collision_step(xrt_solver* s, xrt_collision_stats* stats);  /* CollisionStep, Entry.cu:140-256 */
+/* uint32[F] representative-triangle masks of the cloth (ClothSolverBase::SetupRTriangle) */
+int xrt_quality_cloth_rtri(xrt_solver* s, uint32_t* out, size_t n_faces);
+/* obstacle predicted positions (Node::x), float[3 Vo]: the deform pass of CollisionStep moves them */
+int xrt_quality_get_obstacle_predicted(xrt_solver* s, float* xyz);
+
 #ifdef __cplusplus
 }
 #endif

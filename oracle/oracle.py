@@ -89,6 +89,7 @@ def _load():
     L.oracle_isolate_zones.argtypes = [vp, u32p, C.c_size_t, i32p]; L.oracle_isolate_zones.restype = C.c_int
     L.oracle_optimize_zones.argtypes = [vp, u32p, f32p, i32p, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, i32p]
     L.oracle_optimize_zones.restype = None
+    L.oracle_rep_contributions.argtypes = [vp, C.c_int, i32p, f32p, C.c_int]; L.oracle_rep_contributions.restype = C.c_int
     L.oracle_quality_num_quads.argtypes = [vp]; L.oracle_quality_num_quads.restype = C.c_size_t
     L.oracle_quality_get_quads.argtypes = [vp, u32p, f32p]; L.oracle_quality_get_quads.restype = None
     L.oracle_quality_num_rep_pairs.argtypes = [vp]; L.oracle_quality_num_rep_pairs.restype = C.c_size_t
@@ -357,6 +358,11 @@ class Scene:
 
     def rep_solve(self):
         L.oracle_rep_solve(self.h)
+
+    def rep_contributions(self, vertex, cap=256):
+        rows, corr = np.zeros((cap, 6), np.int32), np.zeros((cap, 3), np.float32)
+        n = L.oracle_rep_contributions(self.h, int(vertex), rows.ctypes.data_as(_i32p), _pf(corr), cap)
+        return rows[:min(n, cap)], corr[:min(n, cap)]
 
     def cloth_rtri(self):
         return _arr(L.oracle_quality_cloth_rtri(self.h), self.F, np.uint32)

@@ -35,12 +35,17 @@
 #include <xrtailor/physics/repulsion/ImminentRepulsion.cuh>
 #include <xrtailor/physics/repulsion/PBDRepulsion.cuh>
 #undef private
+#include <xrtailor/physics/repulsion/Impulse.cuh>
 #include <xrtailor/utils/Timer.hpp>
 
 namespace XRTailor {
 // the reference's own Morton kernel (broad_phase/lbvh/BVH.cu:464-481), launched by ref_get_mortons
 __global__ void ComputeMortons_Kernel(Primitive* objects, Bounds* aabbs, Bounds aabb_whole, uint* mortons,
                                       uint num_internal_nodes, uint num_objects);
+// defined in repulsion/PBDRepulsion.cu:329,411, not declared in a header (ref_rep_contributions calls them)
+__host__ __device__ bool EvaluateVFProximity(Node* node, Face* face, const Scalar& h, Impulse* impulse);
+__host__ __device__ bool EvaluateEEProximity(Edge* edge0, Edge* edge1, const Scalar& h, Impulse* impulse);
+__global__ void EvaluateRep_Kernel(PairFF* pairs, Vector3* deltas, int* delta_counts, Scalar thickness, int n_pairs);
 namespace ImpactZoneOptimization {
 // defined in impact_zone/Entry.cu:25, not declared in a header
 thrust::device_vector<Impact> independentImpacts(const thrust::device_vector<Impact>& impacts, int deform);
@@ -803,6 +808,66 @@ void ref_rep_solve(void* h, float dt, int iteration) {
   auto* s = use(h);
   s->pbd->SolveNoProximity(s->cloth.get(), s->pbd_thickness, s->relaxation_rate, dt, s->frame_index, iteration);
   cudaDeviceSynchronize();
+}
+// Every contribution of one SolveNoProximity pass to cloth vertex `vertex`, evaluated by the reference's own
+// EvaluateVFProximity / EvaluateEEProximity over the solver's pair list in EvaluateRep_Kernel's order
+// (PBDRepulsion.cu:470-500).  rows: pair, slot (0-2 VF, 3-11 EE), 4 global node ids | corr xyz of that vertex.
+__global__ void RepContrib_Kernel(const PairFF* pairs, int n_pairs, Scalar h, int vertex, int V, int* n_out, int* rows, float* corr, int cap) {
+  for (int pid = 0; pid < n_pairs; pid++) {
+    Face* face0 = pairs[pid].first;
+    Face* face1 = pairs[pid].second;
+    for (int slot = 0; slot < 12; slot++) {
+      Impulse impulse;
+      bool hit = false;
+      if (slot < 3) {
+        if (!RTriVertex(face0->r_tri, slot)) continue;
+        hit = EvaluateVFProximity(face0->nodes[slot], face1, h, &impulse);
+      } else {
+        const int i = (slot - 3) / 3, j = (slot - 3) % 3;
+        if (!RTriEdge(face0->r_tri, i) || !RTriEdge(face1->r_tri, j)) continue;
+        hit = EvaluateEEProximity(face0->edges[i], face1->edges[j], h, &impulse);
+      }
+      if (!hit) continue;
+      for (int k = 0; k < 4; k++) {
+        Node* nd = impulse.nodes[k];
+        if (!nd->is_cloth || nd->index != vertex) continue;
+        if (glm::length(impulse.corrs[k]) < EPSILON || !nd->is_free) continue;
+        const int at = (*n_out)++;
+        if (at < cap) {
+          rows[6 * at] = pid; rows[6 * at + 1] = slot;
+          for (int q = 0; q < 4; q++) rows[6 * at + 2 + q] = impulse.nodes[q]->index + (impulse.nodes[q]->is_cloth ? 0 : V);
+          for (int q = 0; q < 3; q++) corr[3 * at + q] = impulse.corrs[k][q];
+        }
+      }
+    }
+  }
+}
+// the reference's EvaluateRep_Kernel alone (no apply): the Jacobi sums and counts it leaves behind (debug)
+void ref_rep_evaluate_only(void* h, float* deltas, int* counts) {
+  auto* s = use(h);
+  const int V = s->cloth->NumNodes();
+  const int n_pairs = (int)s->pbd->pairs_.size();
+  thrust::device_vector<Vector3> d(V, Vector3(0));
+  thrust::device_vector<int> c(V, 0);
+  EvaluateRep_Kernel<<<(n_pairs + 255) / 256, 256>>>(pointer(s->pbd->pairs_), pointer(d), pointer(c), s->pbd_thickness, n_pairs);
+  cudaDeviceSynchronize();
+  thrust::host_vector<Vector3> hd = d;
+  thrust::host_vector<int> hc = c;
+  for (int i = 0; i < V; i++) {
+    for (int k = 0; k < 3; k++) deltas[3 * i + k] = hd[i][k];
+    counts[i] = hc[i];
+  }
+}
+int ref_rep_contributions(void* h, int vertex, int* rows, float* corr, int cap) {
+  auto* s = use(h);
+  thrust::device_vector<int> n(1, 0), dr(6 * (size_t)cap);
+  thrust::device_vector<float> dc(3 * (size_t)cap);
+  RepContrib_Kernel<<<1, 1>>>(pointer(s->pbd->pairs_), (int)s->pbd->pairs_.size(), s->pbd_thickness, vertex, s->cloth->NumNodes(),
+                              pointer(n), pointer(dr), pointer(dc), cap);
+  cudaDeviceSynchronize();
+  thrust::copy(dr.begin(), dr.end(), rows);
+  thrust::copy(dc.begin(), dc.end(), corr);
+  return n[0];
 }
 // BVH::Update(ccd = true) on the obstacle tree (ClothSolverBase.cpp:291)
 void ref_obstacle_bvh_update(void* h) {

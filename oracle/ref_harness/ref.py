@@ -58,6 +58,8 @@ def lib():
         L.ref_find_impacts.argtypes = [vp, C.c_float, C.c_float, u32p, f32p, ll, llp]; L.ref_find_impacts.restype = ll
         L.ref_independent_impacts.argtypes = [vp, C.c_int, u32p, f32p, ll]; L.ref_independent_impacts.restype = ll
         L.ref_collision_step.argtypes = [vp, C.c_float]; L.ref_collision_step.restype = None
+        L.ref_rep_evaluate_only.argtypes = [vp, f32p, i32p]; L.ref_rep_evaluate_only.restype = None
+        L.ref_rep_contributions.argtypes = [vp, C.c_int, i32p, f32p, C.c_int]; L.ref_rep_contributions.restype = C.c_int
         L.ref_imminent_generate.argtypes = [vp, u32p, f32p, ll]; L.ref_imminent_generate.restype = ll
         L.ref_imminent_solve.argtypes = [vp, C.c_float, C.c_int]; L.ref_imminent_solve.restype = None
         L.ref_rep_update_pairs.argtypes = [vp, u32p, ll]; L.ref_rep_update_pairs.restype = ll
@@ -258,6 +260,18 @@ class RefSolver:
 
     def rep_solve(self, dt, iteration=0):
         lib().ref_rep_solve(self.h, dt, iteration)
+
+    def rep_evaluate_only(self):
+        V = self.V if hasattr(self, "V") else len(self.state(0)["x"])
+        d, c = np.zeros((V, 3), np.float32), np.zeros(V, np.int32)
+        lib().ref_rep_evaluate_only(self.h, _pf(d), _pi(c))
+        return d, c
+
+    def rep_contributions(self, vertex, cap=256):
+        """(rows[n,6] = pair, slot, 4 node ids; corr[n,3]) of every PBD repulsion term on one cloth vertex (debug)"""
+        rows, corr = np.zeros((cap, 6), np.int32), np.zeros((cap, 3), np.float32)
+        n = lib().ref_rep_contributions(self.h, int(vertex), _pi(rows), _pf(corr), cap)
+        return rows[:min(n, cap)], corr[:min(n, cap)]
 
     def obstacle_bvh_update(self):
         lib().ref_obstacle_bvh_update(self.h)

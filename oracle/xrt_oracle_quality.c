@@ -1347,6 +1347,41 @@ void oracle_optimize_zones(OScene* s, const uint32_t* nodes, const float* twn, c
   free(in);
 }
 
+/* debug twin of ref_rep_contributions (oracle/ref_harness/harness.cu): every term of one oracle_rep_solve pass on
+ * cloth vertex `vertex`; rows: pair, slot (0-2 VF, 3-11 EE), 4 global node ids | corr xyz */
+int oracle_rep_contributions(OScene* s, int vertex, int* rows, float* corr_out, int cap) {
+  OQuality* q = s->q;
+  const float h = q->pbd_thickness;
+  int n = 0;
+  for (size_t p = 0; p < q->n_rep_pairs; p++) {
+    const uint32_t f0 = q->rep_pairs[2 * p], f1 = q->rep_pairs[2 * p + 1];
+    for (int slot = 0; slot < 12; slot++) {
+      uint32_t nodes[4];
+      v3 corr[4];
+      int hit;
+      if (slot < 3) {
+        if (!rtri_vertex(q_face_rtri(s, f0), slot)) continue;
+        hit = q_rep_vf(s, q_face_node(s, f0, slot), f1, h, nodes, corr);
+      } else {
+        const int i = (slot - 3) / 3, j = (slot - 3) % 3;
+        if (!rtri_edge(q_face_rtri(s, f0), i) || !rtri_edge(q_face_rtri(s, f1), j)) continue;
+        hit = q_rep_ee(s, q_face_edge(s, f0, i), q_face_edge(s, f1, j), h, nodes, corr);
+      }
+      if (!hit) continue;
+      for (int k = 0; k < 4; k++) {
+        if ((int)nodes[k] != vertex || len(corr[k]) < EPS || !q_free(s, nodes[k])) continue;
+        if (n < cap) {
+          rows[6 * n] = (int)p; rows[6 * n + 1] = slot;
+          for (int t = 0; t < 4; t++) rows[6 * n + 2 + t] = (int)nodes[t];
+          corr_out[3 * n] = corr[k].x; corr_out[3 * n + 1] = corr[k].y; corr_out[3 * n + 2] = corr[k].z;
+        }
+        n++;
+      }
+    }
+  }
+  return n;
+}
+
 size_t oracle_quality_num_quads(OScene* s) { return s->q->n_quads; }
 void oracle_quality_get_quads(OScene* s, uint32_t* nodes, float* bary) {
   for (size_t i = 0; i < s->q->n_quads; i++) { memcpy(nodes + 4 * i, s->q->quads[i].n, 16); memcpy(bary + 4 * i, s->q->quads[i].bary, 16); }

@@ -44,6 +44,25 @@ class XrtStats(C.Structure):
     ]
 
 
+class XrtQualityParams(C.Structure):
+    _fields_ = [
+        ("xx_stiffness", C.c_float), ("yy_stiffness", C.c_float), ("xy_stiffness", C.c_float),
+        ("xy_poisson_ratio", C.c_float), ("yx_poisson_ratio", C.c_float), ("bending_stiffness", C.c_float),
+        ("enable_imminent_repulsion", C.c_int32), ("imminent_thickness", C.c_float),
+        ("enable_pbd_repulsion", C.c_int32), ("pbd_thickness", C.c_float), ("relaxation_rate", C.c_float),
+        ("obstacle_mass", C.c_float), ("impact_zone_thickness", C.c_float),
+        ("max_pairs", C.c_uint32), ("max_candidates", C.c_uint32), ("max_impacts", C.c_uint32),
+    ]
+
+
+class XrtCollisionStats(C.Structure):
+    _fields_ = [
+        ("rounds", C.c_int32), ("success", C.c_int32), ("total_impacts", C.c_int32), ("deform", C.c_int32),
+        ("n_pairs", C.c_int32), ("n_candidates", C.c_int32), ("outer_iterations", C.c_int32),
+        ("line_search_steps", C.c_int32),
+    ]
+
+
 # every symbol include/xrt_b200.h declares
 SYMBOLS = [
     "xrt_default_params", "xrt_create", "xrt_destroy", "xrt_last_error", "xrt_add_cloth", "xrt_add_obstacle",
@@ -55,6 +74,11 @@ SYMBOLS = [
     "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
     "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
+    "xrt_default_quality_params", "xrt_set_quality", "xrt_quality_begin_frame", "xrt_quality_imminent_generate",
+    "xrt_quality_imminent_solve", "xrt_quality_rep_update_pairs", "xrt_quality_rep_solve",
+    "xrt_quality_obstacle_bvh_update", "xrt_quality_iteration", "xrt_quality_find_impacts",
+    "xrt_quality_independent_impacts", "xrt_quality_isolate_zones", "xrt_quality_optimize_zones",
+    "xrt_quality_collision_step", "xrt_quality_cloth_rtri", "xrt_quality_get_obstacle_predicted",
 ]
 
 
@@ -113,6 +137,23 @@ def _load():
         "xrt_batch_set_obstacle_targets": [vp, f32p, C.c_size_t],
         "xrt_batch_launches_per_frame": [vp, C.c_int, u32p],
         "xrt_batch_set_readback": [vp, C.c_int],
+        "xrt_default_quality_params": [C.POINTER(XrtQualityParams)],
+        "xrt_set_quality": [vp, C.POINTER(XrtQualityParams), u32p],
+        "xrt_quality_begin_frame": [vp],
+        "xrt_quality_imminent_generate": [vp, u32p, f32p, C.c_size_t, C.POINTER(C.c_size_t)],
+        "xrt_quality_imminent_solve": [vp],
+        "xrt_quality_rep_update_pairs": [vp, u32p, C.c_size_t, C.POINTER(C.c_size_t)],
+        "xrt_quality_rep_solve": [vp],
+        "xrt_quality_obstacle_bvh_update": [vp],
+        "xrt_quality_iteration": [vp, C.c_int],
+        "xrt_quality_find_impacts": [vp, C.c_float, u32p, f32p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t),
+                                     C.POINTER(C.c_size_t)],
+        "xrt_quality_independent_impacts": [vp, u32p, f32p, C.c_size_t, C.c_int, u32p, f32p, C.POINTER(C.c_size_t)],
+        "xrt_quality_isolate_zones": [vp, u32p, C.c_size_t, i32p, i32p],
+        "xrt_quality_optimize_zones": [vp, u32p, f32p, i32p, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, i32p],
+        "xrt_quality_collision_step": [vp, C.POINTER(XrtCollisionStats)],
+        "xrt_quality_cloth_rtri": [vp, u32p, C.c_size_t],
+        "xrt_quality_get_obstacle_predicted": [vp, f32p],
     }
     for name, args in sig.items():
         fn = getattr(L, name)
@@ -128,6 +169,14 @@ def _load():
 
 
 lib = _load()
+
+
+def default_quality_params() -> XrtQualityParams:
+    q = XrtQualityParams()
+    rc = lib.xrt_default_quality_params(C.byref(q))
+    if rc:
+        raise XrtError(rc)
+    return q
 
 
 def default_params() -> XrtParams:

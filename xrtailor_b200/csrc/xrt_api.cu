@@ -3,7 +3,7 @@
 // (xrtailor/src/pipeline/base/ClothSolverBase.cpp:171-261) as one CUDA graph
 // per frame.  No CPU fallback lives here: without a CUDA device xrt_create fails.
 #include "../../include/xrt_b200.h"
-#include "xrt_persist.cuh"
+#include "xrt_handle.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -20,82 +20,6 @@
 // two waves).  Ask for the maximum before the CUDA context exists; a value the caller set wins,
 // and if the host application created the context earlier this is a no-op.
 __attribute__((constructor)) static void xrt_request_hw_queues() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
-
-struct xrt_solver {
-  xrt_params p{};
-  char err[512] = {0};
-  cudaStream_t st = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  bool finalized = false;
-  // host staging (caller data is copied, never retained)
-  std::vector<float> c_pos, c_invm, o_pos, o_invm;
-  std::vector<uint32_t> c_tri, c_edge, o_tri, o_edge;
-  std::vector<uint32_t> s_idx, b_idx, s_color, b_color, l_src, l_tgt;
-  std::vector<float> s_rest, b_theta, l_rest;
-  std::vector<uint32_t> bd_vert, bd_tri;
-  std::vector<float> bd_bary, bd_k, bd_dist;
-  bool s_color_set = false, b_color_set = false;
-  // colour ranges over the permuted constraint arrays
-  std::vector<uint32_t> s_off, b_off;
-  uint32_t *d_s_off = nullptr, *d_b_off = nullptr;
-  bool atomic_s = false, atomic_b = false;
-  // device state
-  ClothDev c;
-  ObstacleDev o;
-  DevBVH bvh{};
-  BvhWork bw;
-  StepConst k{};
-  bool target_pending = false;  // xrt_set_obstacle_target called since the last frame
-  cudaGraphExec_t graph[2] = {nullptr, nullptr};  // [obstacle moved?]
-  // shared-launch batches: this garment's own work before substep `sub` ([2 * sub + moved]; null = nothing to do)
-  // and after the last substep ([moved]), each one graph launch
-  std::vector<cudaGraphExec_t> pre_graph;
-  cudaGraphExec_t post_graph[2] = {nullptr, nullptr};
-  cudaEvent_t batch_ev = nullptr;  // a batch enqueued work on this garment: the handle's stream joins it on next use
-  bool touched = true;             // the handle's own stream has work the batch has not joined yet
-  uint32_t launches[2] = {0, 0};
-  uint32_t launch_counter = 0;
-  float4* stage = nullptr;  // pinned host staging for obstacle targets / readback
-  size_t stage_elems = 0;
-  float4* d_stage = nullptr;
-  // per-frame transfers: raw float3 arrays through pinned memory, converted on the device
-  float *h_up = nullptr, *d_up = nullptr;  // [3 Vo] obstacle target upload
-  float *h_dn = nullptr, *d_dn = nullptr;  // [6 max(V, Vo)] positions + normals download
-  cudaEvent_t ev_up = nullptr;             // upload buffer free again
-  float4* d_seq = nullptr;  // pre-staged obstacle animation [seq_frames][Vo]
-  size_t seq_frames = 0, seq_cursor = 0;
-  cudaEvent_t ev_join = nullptr;
-  int cluster = 0;  // resolved persist_cluster (0: per-stage launches)
-  unsigned long long* d_grid_bar = nullptr;  // grid-wide barrier counter (persist_cluster -2)
-  unsigned long long* d_prof = nullptr;  // [16] per-phase-kind ns of the persistent kernel (XRT_PERSIST_PROF=1)
-};
-
-static void xrt_set_error(xrt_solver* s, const char* fmt, ...) {
-  if (!s) return;
-  va_list ap;
-  va_start(ap, fmt);
-  vsnprintf(s->err, sizeof(s->err), fmt, ap);
-  va_end(ap);
-}
-
-#define XRT_REQUIRE(cond, msg)          \
-  do {                                  \
-    if (!(cond)) {                      \
-      xrt_set_error(s, "%s", msg);      \
-      return XRT_ERR_INVALID;           \
-    }                                   \
-  } while (0)
-
-template <class T>
-static cudaError_t dev_alloc(T** p, size_t n) {
-  return cudaMalloc((void**)p, (n ? n : 1) * sizeof(T));
-}
-template <class T>
-static cudaError_t dev_upload(T** p, const std::vector<T>& h) {
-  cudaError_t e = dev_alloc(p, h.size());
-  if (e == cudaSuccess && !h.empty()) e = cudaMemcpy(*p, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice);
-  return e;
-}
 
 extern "C" int xrt_default_params(xrt_params* p) {
   if (!p) return XRT_ERR_INVALID;
@@ -311,7 +235,7 @@ static void color_ranges(const std::vector<uint32_t>& idx, int arity, const std:
 
 // vertex -> (face << 2 | corner) CSR, faces ascending per vertex
 // (BuildVFAdjacency, physics/ClothSolverHelper.cu:377-401 uses std::set<uint>)
-static void build_vf(const std::vector<uint32_t>& tri, uint32_t V, std::vector<uint32_t>& off,
+void xrt_build_vf(const std::vector<uint32_t>& tri, uint32_t V, std::vector<uint32_t>& off,
                      std::vector<uint32_t>& idx) {
   const size_t F = tri.size() / 3;
   off.assign(V + 1, 0);
@@ -327,7 +251,7 @@ static void build_vf(const std::vector<uint32_t>& tri, uint32_t V, std::vector<u
 // host: bit i   = this face is the lowest-index face on its vertex i,
 //       bit 3+i = this face owns edge (i, i+1): no other face shares it, or
 //                 the lowest-index other face sharing it has a larger index.
-static void build_rtri(const std::vector<uint32_t>& tri, const std::vector<uint32_t>& vf_off,
+void xrt_build_rtri(const std::vector<uint32_t>& tri, const std::vector<uint32_t>& vf_off,
                        const std::vector<uint32_t>& vf_idx, std::vector<uint32_t>& rtri) {
   const size_t F = tri.size() / 3;
   rtri.assign(F, 0);
@@ -444,7 +368,7 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
   for (uint32_t i = 0; i < c.E; i++) he[i] = make_uint2(s->c_edge[2 * i], s->c_edge[2 * i + 1]);
   XRT_CUDA_OK(dev_upload(&c.edge, he));
   std::vector<uint32_t> vfo, vfi;
-  build_vf(s->c_tri, c.V, vfo, vfi);
+  xrt_build_vf(s->c_tri, c.V, vfo, vfi);
   XRT_CUDA_OK(dev_upload(&c.vf_off, vfo));
   XRT_CUDA_OK(dev_upload(&c.vf_idx, vfi));
   XRT_CUDA_OK(dev_upload(&c.s_idx, hs));
@@ -493,8 +417,8 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
     XRT_CUDA_OK(dev_alloc(&o.n1, o.V));
     XRT_CUDA_OK(dev_upload(&o.tri, s->o_tri));
     std::vector<uint32_t> ovo, ovi, rt;
-    build_vf(s->o_tri, o.V, ovo, ovi);
-    build_rtri(s->o_tri, ovo, ovi, rt);  // ClothSolverBase::SetupRTriangle
+    xrt_build_vf(s->o_tri, o.V, ovo, ovi);
+    xrt_build_rtri(s->o_tri, ovo, ovi, rt);  // ClothSolverBase::SetupRTriangle
     XRT_CUDA_OK(dev_upload(&o.vf_off, ovo));
     XRT_CUDA_OK(dev_upload(&o.vf_idx, ovi));
     XRT_CUDA_OK(dev_upload(&o.rtri, rt));
@@ -569,6 +493,8 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
   launch_normals(c.x0, c.n, c.tri, c.vf_off, c.vf_idx, c.V, s->st);
   XRT_CUDA_OK(cudaStreamSynchronize(s->st));
   XRT_CUDA_OK(cudaGetLastError());
+  if (s->q)
+    if (int rc = xrt_quality_finalize(s)) return rc;
   s->finalized = true;
   return XRT_OK;
 }
@@ -714,22 +640,6 @@ static int ensure_graph(xrt_solver* s, int moved) {
   return XRT_OK;
 }
 
-// Work a shared-launch batch enqueued for this garment lives on the batch's streams; the
-// handle's own stream joins it lazily, on the first per-handle call (a wait parked in every
-// handle stream would sit in the shared hardware queues and couple unrelated batches).
-static cudaError_t join_batch(xrt_solver* s) {
-  s->touched = true;
-  if (!s->batch_ev) return cudaSuccess;
-  cudaEvent_t e = s->batch_ev;
-  s->batch_ev = nullptr;
-  return cudaStreamWaitEvent(s->st, e, 0);
-}
-#define XRT_READY()                                            \
-  if (!s) return XRT_ERR_INVALID;                              \
-  XRT_REQUIRE(s->finalized, "call xrt_finalize_setup first");  \
-  XRT_CUDA_OK(cudaSetDevice(s->p.device));                     \
-  XRT_CUDA_OK(join_batch(s))
-
 extern "C" int xrt_set_obstacle_target(xrt_solver* s, const float* xyz, size_t n_verts) {
   XRT_READY();
   XRT_REQUIRE(xyz && n_verts == s->o.V, "set_obstacle_target: vertex count differs from the obstacle");
@@ -774,6 +684,10 @@ static int take_sequence_frame(xrt_solver* s, cudaStream_t st) {
 
 extern "C" int xrt_step_frame_async(xrt_solver* s) {
   XRT_READY();
+  if (s->q) {  // a Quality frame synchronises inside CollisionStep: there is no enqueue-only form
+    if (int rc0 = take_sequence_frame(s, s->st)) return rc0;
+    return xrt_quality_step_frame(s, nullptr);
+  }
   if (int rc0 = take_sequence_frame(s, s->st)) return rc0;
   const int moved = s->target_pending ? 1 : 0;
   int rc = ensure_graph(s, moved);
@@ -792,6 +706,7 @@ extern "C" int xrt_sync(xrt_solver* s) {
 extern "C" int xrt_step_frame(xrt_solver* s, float* solver_ms) {
   XRT_READY();
   if (int rc0 = take_sequence_frame(s, s->st)) return rc0;
+  if (s->q) return xrt_quality_step_frame(s, solver_ms);  // ClothSolverBase::SimulateQuality
   const int moved = s->target_pending ? 1 : 0;
   int rc = ensure_graph(s, moved);
   if (rc) return rc;
@@ -1046,8 +961,8 @@ extern "C" int xrt_batch_create(xrt_solver** handles, int n, int groups, int wor
   XRT_READY();
   for (int i = 0; i < n; i++) {
     xrt_solver* h = handles[i];
-    if (!h || !h->finalized || h->p.device != s->p.device) {
-      xrt_set_error(s, "batch_create: handle %d is null, not finalized or on another device", i);
+    if (!h || !h->finalized || h->p.device != s->p.device || h->q) {
+      xrt_set_error(s, "batch_create: handle %d is null, not finalized, on another device or a Quality-mode handle", i);
       return XRT_ERR_INVALID;
     }
     if (h->cluster < 1 || h->cluster == XRT_PERSIST_GRID || h->cluster != s->cluster ||
@@ -1784,6 +1699,7 @@ extern "C" void xrt_destroy(xrt_solver* s) {
   }
   for (cudaGraphExec_t g : s->pre_graph)
     if (g) cudaGraphExecDestroy(g);
+  xrt_quality_destroy(s);
   ClothDev& c = s->c;
   void* ptrs[] = {c.x0, c.x, c.v, c.n, c.rest, c.tri, c.edge, c.vf_off, c.vf_idx, c.s_idx, c.s_rest, c.s_lambda,
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,

@@ -26,22 +26,32 @@ __global__ void scene_init_kernel(int* scene) {
 
 // UpdateObjects_Kernel + InitAABBs_Kernel + thrust::reduce (BVH.cu:382-462,642)
 // in one pass over the faces.
-__global__ void leaf_box_kernel(const float4* __restrict__ x, const uint32_t* __restrict__ tri,
-                                float4* __restrict__ pred, float* __restrict__ leaf_box,
-                                int* __restrict__ scene, uint32_t F) {
+__global__ void leaf_box_kernel(const float4* __restrict__ x, const float4* __restrict__ xp,
+                                const uint32_t* __restrict__ tri, float4* __restrict__ pred,
+                                float* __restrict__ leaf_box, int* __restrict__ scene, uint32_t F) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
   if (i < F) {
-    float4 a = x[tri[3 * i]], b = x[tri[3 * i + 1]], c = x[tri[3 * i + 2]];
-    pred[3 * i] = a;
-    pred[3 * i + 1] = b;
-    pred[3 * i + 2] = c;
+    const uint32_t i0 = tri[3 * i], i1 = tri[3 * i + 1], i2 = tri[3 * i + 2];
+    float4 a = x[i0], b = x[i1], c = x[i2];
     lo[0] = fminf(a.x, fminf(b.x, c.x));
     lo[1] = fminf(a.y, fminf(b.y, c.y));
     lo[2] = fminf(a.z, fminf(b.z, c.z));
     hi[0] = fmaxf(a.x, fmaxf(b.x, c.x));
     hi[1] = fmaxf(a.y, fmaxf(b.y, c.y));
     hi[2] = fmaxf(a.z, fmaxf(b.z, c.z));
+    if (xp) {  // ccd: pred = Node::x, box over v and pred (UpdateObjects_Kernel / InitAABBs_Kernel, BVH.cu:382-462)
+      a = xp[i0]; b = xp[i1]; c = xp[i2];
+      lo[0] = fminf(lo[0], fminf(a.x, fminf(b.x, c.x)));
+      lo[1] = fminf(lo[1], fminf(a.y, fminf(b.y, c.y)));
+      lo[2] = fminf(lo[2], fminf(a.z, fminf(b.z, c.z)));
+      hi[0] = fmaxf(hi[0], fmaxf(a.x, fmaxf(b.x, c.x)));
+      hi[1] = fmaxf(hi[1], fmaxf(a.y, fmaxf(b.y, c.y)));
+      hi[2] = fmaxf(hi[2], fmaxf(a.z, fmaxf(b.z, c.z)));
+    }
+    pred[3 * i] = a;
+    pred[3 * i + 1] = b;
+    pred[3 * i + 2] = c;
     float* o = leaf_box + 6 * (size_t)i;
     o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2];
     o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
@@ -211,6 +221,36 @@ __global__ void refit_kernel(TNode* tn, const BVNode* __restrict__ nodes, float4
   if (i < F) refit_item<false>(tn, nodes, pred, x1, n1, tri, tol, flags, F, i);
 }
 
+// BVH::Update (BVH.cu:820-852): Update_Kernel grows every leaf box by Face::ComputeBounds(ccd) (x, and x0 when
+// ccd) and sets pred = x; AssignAABBAtomic then merges upwards.  Leaves only grow, so "old box merged with the
+// children" equals the exact merge of the children, which is what the single bottom-up pass writes.
+__global__ void update_kernel(TNode* tn, const BVNode* __restrict__ nodes, float4* __restrict__ pred,
+                              const float4* __restrict__ x0, const float4* __restrict__ x,
+                              const uint32_t* __restrict__ tri, int ccd, int* flags, uint32_t F) {
+  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= F) return;
+  const uint32_t node = F - 1 + i;
+  const uint32_t o = nodes[node].object;
+  TNode* leaf = tn + tnode_slot(nodes, node);
+  float lo[3], hi[3];
+  tnode_load_box(leaf, lo, hi);
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    const uint32_t v = tri[3 * o + k];
+    const float4 p = x[v];
+    pred[3 * o + k] = p;
+    lo[0] = fminf(lo[0], p.x); lo[1] = fminf(lo[1], p.y); lo[2] = fminf(lo[2], p.z);
+    hi[0] = fmaxf(hi[0], p.x); hi[1] = fmaxf(hi[1], p.y); hi[2] = fmaxf(hi[2], p.z);
+    if (ccd) {
+      const float4 q = x0[v];
+      lo[0] = fminf(lo[0], q.x); lo[1] = fminf(lo[1], q.y); lo[2] = fminf(lo[2], q.z);
+      hi[0] = fmaxf(hi[0], q.x); hi[1] = fmaxf(hi[1], q.y); hi[2] = fmaxf(hi[2], q.z);
+    }
+  }
+  tnode_store_box(leaf, lo, hi);
+  walk_up<false>(tn, nodes, flags, node);
+}
+
 }  // namespace
 
 int bvh_alloc(DevBVH* b, BvhWork* w, uint32_t F) {
@@ -257,11 +297,24 @@ int bvh_refit_launches() { return 1; }
 
 void bvh_build(const DevBVH& b_, const BvhWork& w, const float4* x, const uint32_t* tri, uint32_t F,
                int fast_div, cudaStream_t st) {
+  bvh_build_ccd(b_, w, x, nullptr, tri, F, fast_div, st);
+}
+
+void bvh_update(const DevBVH& b, const BvhWork& w, const float4* x0, const float4* x, const uint32_t* tri, int ccd,
+                cudaStream_t st) {
+  const uint32_t F = b.n_obj;
+  if (F == 0) return;
+  cudaMemsetAsync(w.flags, 0, F * sizeof(int), st);
+  update_kernel<<<xrt_grid(F), XRT_BLOCK, 0, st>>>(b.tnodes, b.nodes, b.pred, x0, x, tri, ccd, w.flags, F);
+}
+
+void bvh_build_ccd(const DevBVH& b_, const BvhWork& w, const float4* x, const float4* xp, const uint32_t* tri,
+                   uint32_t F, int fast_div, cudaStream_t st) {
   DevBVH& b = const_cast<DevBVH&>(b_);
   if (F == 0) return;
   const unsigned g = xrt_grid(F);
   scene_init_kernel<<<1, 32, 0, st>>>(w.scene);
-  leaf_box_kernel<<<g, XRT_BLOCK, 0, st>>>(x, tri, b.pred, w.leaf_box, w.scene, F);
+  leaf_box_kernel<<<g, XRT_BLOCK, 0, st>>>(x, xp, tri, b.pred, w.leaf_box, w.scene, F);
   if (fast_div)
     morton_kernel<true><<<g, XRT_BLOCK, 0, st>>>(w.leaf_box, w.scene, w.key_a, w.val_a, F);
   else

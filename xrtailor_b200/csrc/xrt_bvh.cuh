@@ -22,6 +22,15 @@ void bvh_free(DevBVH* b, BvhWork* w);
 void bvh_build(const DevBVH& b, const BvhWork& w, const float4* x, const uint32_t* tri,
                uint32_t n_faces, int fast_div, cudaStream_t st);
 
+// BVH::UpdateData(tol=0, ccd=true) + Construct: leaf boxes over x (Node::x0) and xp (Node::x), pred = xp
+// (what CollisionStep builds, impact_zone/Entry.cu:146-155).  xp == nullptr is bvh_build.
+void bvh_build_ccd(const DevBVH& b, const BvhWork& w, const float4* x, const float4* xp, const uint32_t* tri,
+                   uint32_t n_faces, int fast_div, cudaStream_t st);
+
+// BVH::Update (BVH.cu:820-852): leaf boxes grow by x (and x0 when ccd), pred = x, internal boxes follow.
+void bvh_update(const DevBVH& b, const BvhWork& w, const float4* x0, const float4* x, const uint32_t* tri, int ccd,
+                cudaStream_t st);
+
 // BVH::RefitMidstep (BVH.cu:795-818): pred = x1 + tol*n1, leaf boxes grow,
 // internal boxes = exact merge of children.
 void bvh_refit_midstep(const DevBVH& b, const BvhWork& w, const float4* x1, const float4* n1,
@@ -30,3 +39,18 @@ void bvh_refit_midstep(const DevBVH& b, const BvhWork& w, const float4* x1, cons
 // number of kernels one call enqueues (for the launch count the bench reports)
 int bvh_build_launches();
 int bvh_refit_launches();
+
+// ---- face-face pair lists (xrt_pairs.cu): BVH::Traverse / TraverseSelf (BVH.cu:1149-1400) on preallocated scratch ----
+struct PairWork {
+  uint32_t cap = 0;  // left faces this scratch was sized for
+  int* num = nullptr;
+  void* scan_tmp = nullptr;
+  size_t scan_bytes = 0;
+};
+int pairs_alloc(PairWork* w, uint32_t F_left);
+void pairs_free(PairWork* w);
+// Appends the (left face, right face + right_off) rows of Traverse(L, R, thickness) to `pairs` at *count (a
+// device-side counter) in the reference's order and advances *count; rows beyond `cap` are dropped and bit 0 of
+// *overflow is set.  Three kernels and a scan, no allocation, no host synchronisation.
+void pairs_traverse(const DevBVH& L, const DevBVH& R, float thickness, const PairWork& w, uint2* pairs, uint32_t cap,
+                    uint32_t* count, uint32_t right_off, uint32_t* overflow, cudaStream_t st);

@@ -10,25 +10,18 @@
 // IEEE arithmetic (the file is built with -fmad=false) in the reference's evaluation order, so the
 // result matches the CPU oracle to rounding.
 #include "../../include/xrt_b200.h"
-#include "xrt_common.cuh"
+#include "xrt_fem.cuh"
 
 #include <algorithm>
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
-namespace {
+using Strain = FemStrain;
+using IsoBend = FemIsoBend;
+using Material = FemMaterial;
 
-struct Strain {  // FEM::StrainConstraint: rest area + inverse rest matrix (glm column-major: m[c][r])
-  uint32_t i0, i1, i2;
-  float area;
-  float inv[2][2];
-};
-struct IsoBend {  // FEM::IsometricBendingConstraint
-  uint32_t i[4];
-  float Q[4][4];
-};
-struct Material {
-  float xx, yy, xy, nu_xy, nu_yx, bend;
-};
+namespace {
 
 __device__ __forceinline__ f3 ld3(const float4* x, uint32_t i) { return mk3(x[i]); }
 
@@ -204,6 +197,66 @@ cudaError_t up(T** d, const T* h, size_t n) {
 
 }  // namespace
 
+int fem_setup(FemDev* f, const float4* rest, uint32_t n_verts, const uint32_t* d_tri, const uint32_t* h_tri,
+              uint32_t n_faces, const uint32_t* h_bend_idx, uint32_t n_bend, const uint32_t* colors_strain,
+              const uint32_t* colors_bend, const FemMaterial& m, cudaStream_t st) {
+  std::vector<uint32_t> ids_s, off_s, ids_b, off_b;
+  f->atomic_s = !sort_by_color(colors_strain, h_tri, 3, n_faces, n_verts, ids_s, off_s);
+  f->atomic_b = n_bend ? !sort_by_color(colors_bend, h_bend_idx, 4, n_bend, n_verts, ids_b, off_b) : false;
+  f->n_strain = n_faces;
+  f->n_bend = n_bend;
+  f->m = m;
+  f->nc_s = (uint32_t)off_s.size() - 1;
+  f->nc_b = n_bend ? (uint32_t)off_b.size() - 1 : 0;
+  f->off_s = (uint32_t*)malloc(sizeof(uint32_t) * off_s.size());
+  memcpy(f->off_s, off_s.data(), sizeof(uint32_t) * off_s.size());
+  if (n_bend) {
+    f->off_b = (uint32_t*)malloc(sizeof(uint32_t) * off_b.size());
+    memcpy(f->off_b, off_b.data(), sizeof(uint32_t) * off_b.size());
+  }
+  cudaError_t e = up(&f->ids_s, ids_s.data(), ids_s.size());
+  if (e == cudaSuccess) e = up(&f->ids_b, ids_b.data(), ids_b.size());
+  if (e == cudaSuccess) e = up(&f->bend_idx, h_bend_idx, 4 * (size_t)n_bend);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&f->strain, (size_t)(n_faces ? n_faces : 1) * sizeof(FemStrain));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&f->bend, (size_t)(n_bend ? n_bend : 1) * sizeof(FemIsoBend));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&f->lambda, (size_t)(n_bend ? n_bend : 1) * sizeof(float));
+  if (e == cudaSuccess) e = cudaMemsetAsync(f->lambda, 0, (size_t)(n_bend ? n_bend : 1) * sizeof(float), st);
+  if (e != cudaSuccess) return (int)e;
+  if (n_faces) init_strain_kernel<<<xrt_grid(n_faces), XRT_BLOCK, 0, st>>>(f->strain, rest, d_tri, n_faces);
+  if (n_bend) init_bend_kernel<<<xrt_grid(n_bend), XRT_BLOCK, 0, st>>>(f->bend, rest, f->bend_idx, n_bend);
+  return (int)cudaGetLastError();
+}
+
+void fem_free(FemDev* f) {
+  cudaFree(f->strain); cudaFree(f->bend); cudaFree(f->lambda);
+  cudaFree(f->ids_s); cudaFree(f->ids_b); cudaFree(f->bend_idx);
+  free(f->off_s); free(f->off_b);
+  *f = FemDev{};
+}
+
+void fem_reset_lambda(const FemDev& f, cudaStream_t st) {
+  if (f.n_bend) cudaMemsetAsync(f.lambda, 0, (size_t)f.n_bend * sizeof(float), st);
+}
+
+int fem_iteration(const FemDev& f, float4* x, float dt, bool bending, cudaStream_t st) {
+  int launches = 0;
+  for (uint32_t c = 0; c < f.nc_s; c++)
+    if (f.off_s[c + 1] > f.off_s[c]) {
+      solve_strain_kernel<<<xrt_grid(f.off_s[c + 1] - f.off_s[c]), XRT_BLOCK, 0, st>>>(x, f.strain, f.ids_s, f.off_s[c],
+                                                                                       f.off_s[c + 1], f.m, f.atomic_s);
+      launches++;
+    }
+  if (bending)
+    for (uint32_t c = 0; c < f.nc_b; c++)
+      if (f.off_b[c + 1] > f.off_b[c]) {
+        // iteration 1: lambda is reset by fem_reset_lambda at the start of the substep, not inside the kernel
+        solve_bend_kernel<<<xrt_grid(f.off_b[c + 1] - f.off_b[c]), XRT_BLOCK, 0, st>>>(x, f.bend, f.lambda, f.ids_b, f.off_b[c],
+                                                                                       f.off_b[c + 1], f.m.bend, dt, 1, f.atomic_b);
+        launches++;
+      }
+  return launches;
+}
+
 extern "C" int xrt_fem_solve_standalone(const float* rest_pos, const float* pos, const float* inv_mass,
                                         uint32_t n_verts, const uint32_t* tri, uint32_t n_faces,
                                         const uint32_t* bend_idx, uint32_t n_bend, const float* material,
@@ -222,47 +275,25 @@ extern "C" int xrt_fem_solve_standalone(const float* rest_pos, const float* pos,
     return XRT_ERR_CUDA;  // no CPU fallback
   }
   if (cudaSetDevice(device) != cudaSuccess) return XRT_ERR_CUDA;
-  std::vector<uint32_t> ids_s, off_s, ids_b, off_b;
-  const bool proper_s = sort_by_color(colors_strain, tri, 3, n_faces, n_verts, ids_s, off_s);
-  const bool proper_b = n_bend ? sort_by_color(colors_bend, bend_idx, 4, n_bend, n_verts, ids_b, off_b) : true;
   std::vector<float4> hx(n_verts), hr(n_verts);
   for (uint32_t i = 0; i < n_verts; i++) {
     hx[i] = make_float4(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], inv_mass[i]);
     hr[i] = make_float4(rest_pos[3 * i], rest_pos[3 * i + 1], rest_pos[3 * i + 2], 0.f);
   }
-  const Material m{material[0], material[1], material[2], material[3], material[4], material[5]};
+  const FemMaterial m{material[0], material[1], material[2], material[3], material[4], material[5]};
   float4 *dx = nullptr, *dr = nullptr;
-  uint32_t *dtri = nullptr, *dbi = nullptr, *dids_s = nullptr, *dids_b = nullptr;
-  Strain* dcs = nullptr;
-  IsoBend* dcb = nullptr;
-  float* dlam = nullptr;
+  uint32_t* dtri = nullptr;
+  FemDev fem;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   cudaError_t e = up(&dx, hx.data(), hx.size());
   if (e == cudaSuccess) e = up(&dr, hr.data(), hr.size());
   if (e == cudaSuccess) e = up(&dtri, tri, 3 * (size_t)n_faces);
-  if (e == cudaSuccess) e = up(&dbi, bend_idx, 4 * (size_t)n_bend);
-  if (e == cudaSuccess) e = up(&dids_s, ids_s.data(), ids_s.size());
-  if (e == cudaSuccess) e = up(&dids_b, ids_b.data(), ids_b.size());
-  if (e == cudaSuccess) e = cudaMalloc((void**)&dcs, (size_t)n_faces * sizeof(Strain));
-  if (e == cudaSuccess) e = cudaMalloc((void**)&dcb, (size_t)(n_bend ? n_bend : 1) * sizeof(IsoBend));
-  if (e == cudaSuccess) e = cudaMalloc((void**)&dlam, (size_t)(n_bend ? n_bend : 1) * sizeof(float));
-  if (e == cudaSuccess) e = cudaMemset(dlam, 0, (size_t)(n_bend ? n_bend : 1) * sizeof(float));
+  if (e == cudaSuccess) e = (cudaError_t)fem_setup(&fem, dr, n_verts, dtri, tri, n_faces, bend_idx, n_bend, colors_strain, colors_bend, m, 0);
   if (e == cudaSuccess) e = cudaEventCreate(&e0);
   if (e == cudaSuccess) e = cudaEventCreate(&e1);
   if (e == cudaSuccess) {
-    init_strain_kernel<<<xrt_grid(n_faces), XRT_BLOCK>>>(dcs, dr, dtri, n_faces);
-    if (n_bend) init_bend_kernel<<<xrt_grid(n_bend), XRT_BLOCK>>>(dcb, dr, dbi, n_bend);
     cudaEventRecord(e0, 0);
-    for (int it = 0; it < iterations; it++) {
-      for (size_t c = 0; c + 1 < off_s.size(); c++)
-        if (off_s[c + 1] > off_s[c])
-          solve_strain_kernel<<<xrt_grid(off_s[c + 1] - off_s[c]), XRT_BLOCK>>>(dx, dcs, dids_s, off_s[c], off_s[c + 1], m,
-                                                                                !proper_s);
-      for (size_t c = 0; c + 1 < off_b.size(); c++)
-        if (off_b[c + 1] > off_b[c])
-          solve_bend_kernel<<<xrt_grid(off_b[c + 1] - off_b[c]), XRT_BLOCK>>>(dx, dcb, dlam, dids_b, off_b[c], off_b[c + 1],
-                                                                              m.bend, dt, it, !proper_b);
-    }
+    for (int it = 0; it < iterations; it++) fem_iteration(fem, dx, dt, n_bend != 0, 0);
     cudaEventRecord(e1, 0);
     e = cudaDeviceSynchronize();
   }
@@ -279,8 +310,8 @@ extern "C" int xrt_fem_solve_standalone(const float* rest_pos, const float* pos,
   }
   if (e0) cudaEventDestroy(e0);
   if (e1) cudaEventDestroy(e1);
-  cudaFree(dx); cudaFree(dr); cudaFree(dtri); cudaFree(dbi); cudaFree(dids_s); cudaFree(dids_b);
-  cudaFree(dcs); cudaFree(dcb); cudaFree(dlam);
+  cudaFree(dx); cudaFree(dr); cudaFree(dtri);
+  fem_free(&fem);
   (void)cudaGetLastError();
   return e == cudaSuccess ? XRT_OK : XRT_ERR_CUDA;
 }

@@ -14,6 +14,7 @@
 #include "xrt_dev_contact.cuh"
 
 #include <cub/device/device_scan.cuh>
+#include <algorithm>
 #include <vector>
 
 namespace {
@@ -24,10 +25,14 @@ __device__ __forceinline__ bool overlap_box(const Box& r, const Box& q) {
   return !(r.lx > q.ux) && !(r.ux < q.lx) && !(r.ly > q.uy) && !(r.uy < q.ly) && !(r.lz > q.uz) && !(r.uz < q.lz);
 }
 
+// base: where this traversal's pairs start in the arena (a device-side count, so two traversals chain without a
+// host round trip); right_off is added to the right face id (global face numbering: cloth first); pairs beyond
+// `cap` are dropped and reported by pairs_commit_kernel.
 template <bool FILL>
 __global__ void pairs_kernel(const TNode* __restrict__ tl, const BVNode* __restrict__ nl, uint32_t Fl,
                              const TNode* __restrict__ tr, float thickness, int* __restrict__ num,
-                             uint2* __restrict__ pairs) {
+                             uint2* __restrict__ pairs, const uint32_t* __restrict__ base, uint32_t right_off,
+                             uint32_t cap) {
   const uint32_t id = blockIdx.x * blockDim.x + threadIdx.x;
   if (id >= Fl) return;
   const NodeView leaf = load_node<true>(tl, (int)tnode_slot(nl, Fl - 1 + id));
@@ -35,14 +40,18 @@ __global__ void pairs_kernel(const TNode* __restrict__ tl, const BVNode* __restr
   Box q = leaf.b;  // Bounds::Dilate, Bounds.cu:95-104
   q.lx -= thickness; q.ly -= thickness; q.lz -= thickness;
   q.ux += thickness; q.uy += thickness; q.uz += thickness;
-  int index = FILL ? num[id] - 1 : 0;  // inclusive scan: this leaf's pairs end at num[id]-1
+  // inclusive scan: this leaf's pairs end at num[id]-1 (the reference fills each leaf's range back to front)
+  long long index = FILL ? (long long)(base ? *base : 0u) + num[id] - 1 : 0;
   int n = 0;
   int node = 0;
   while (node != -1) {
     const NodeView r = load_node<true>(tr, node);
     if (overlap_box(r.b, q)) {
       if (r.hit < 0) {  // external node
-        if (FILL) pairs[index--] = make_uint2(obj_l, (uint32_t)~r.hit);
+        if (FILL) {
+          if (index < (long long)cap) pairs[index] = make_uint2(obj_l, (uint32_t)~r.hit + right_off);
+          index--;
+        }
         n++;
         node = r.miss;
       } else {
@@ -53,6 +62,17 @@ __global__ void pairs_kernel(const TNode* __restrict__ tl, const BVNode* __restr
     }
   }
   if (!FILL) num[id] = n;
+}
+
+__global__ void pairs_commit_kernel(const int* __restrict__ num, uint32_t Fl, uint32_t* count, uint32_t cap,
+                                    uint32_t* overflow) {
+  const unsigned long long total = (unsigned long long)*count + (unsigned long long)num[Fl - 1];
+  if (total > cap) {
+    atomicOr(overflow, 1u);
+    *count = cap;
+  } else {
+    *count = (uint32_t)total;
+  }
 }
 
 struct Tree {
@@ -82,6 +102,32 @@ void free_tree(Tree& t) {
 }
 
 }  // namespace
+
+int pairs_alloc(PairWork* w, uint32_t F_left) {
+  w->cap = F_left;
+  w->scan_bytes = 0;
+  cub::DeviceScan::InclusiveSum(nullptr, w->scan_bytes, w->num, w->num, (int)F_left, 0);
+  cudaError_t e = cudaMalloc((void**)&w->num, (size_t)(F_left ? F_left : 1) * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc(&w->scan_tmp, w->scan_bytes ? w->scan_bytes : 16);
+  return (int)e;
+}
+void pairs_free(PairWork* w) {
+  cudaFree(w->num);
+  cudaFree(w->scan_tmp);
+  *w = PairWork{};
+}
+void pairs_traverse(const DevBVH& L, const DevBVH& R, float thickness, const PairWork& w, uint2* pairs, uint32_t cap,
+                    uint32_t* count, uint32_t right_off, uint32_t* overflow, cudaStream_t st) {
+  const uint32_t Fl = L.n_obj;
+  if (!Fl || !R.n_obj) return;
+  pairs_kernel<false><<<xrt_grid(Fl), XRT_BLOCK, 0, st>>>(L.tnodes, L.nodes, Fl, R.tnodes, thickness, w.num, nullptr, nullptr,
+                                                         0u, 0u);
+  size_t bytes = w.scan_bytes;
+  cub::DeviceScan::InclusiveSum(w.scan_tmp, bytes, w.num, w.num, (int)Fl, st);
+  pairs_kernel<true><<<xrt_grid(Fl), XRT_BLOCK, 0, st>>>(L.tnodes, L.nodes, Fl, R.tnodes, thickness, w.num, pairs, count,
+                                                        right_off, cap);
+  pairs_commit_kernel<<<1, 1, 0, st>>>(w.num, Fl, count, cap, overflow);
+}
 
 extern "C" int xrt_traverse_pairs_standalone(const float* pos_l, uint32_t nv_l, const uint32_t* tri_l, uint32_t F_l,
                                              const float* pos_r, uint32_t nv_r, const uint32_t* tri_r, uint32_t F_r,
@@ -117,14 +163,15 @@ extern "C" int xrt_traverse_pairs_standalone(const float* pos_l, uint32_t nv_l, 
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     cudaEventRecord(e0, 0);
-    pairs_kernel<false><<<xrt_grid(F_l), XRT_BLOCK>>>(L.b.tnodes, L.b.nodes, F_l, Rt.b.tnodes, thickness, num, nullptr);
+    pairs_kernel<false><<<xrt_grid(F_l), XRT_BLOCK>>>(L.b.tnodes, L.b.nodes, F_l, Rt.b.tnodes, thickness, num, nullptr, nullptr, 0u, 0u);
     cub::DeviceScan::InclusiveSum(scan_tmp, scan_bytes, num, num, (int)F_l, 0);
     int last = 0;
     if (cudaMemcpy(&last, num + (F_l - 1), sizeof(int), cudaMemcpyDeviceToHost) != cudaSuccess) rc = XRT_ERR_CUDA;
     total = (size_t)(last < 0 ? 0 : last);
     if (rc == XRT_OK && total && cudaMalloc((void**)&d_pairs, total * sizeof(uint2)) != cudaSuccess) rc = XRT_ERR_CUDA;
     if (rc == XRT_OK && total)
-      pairs_kernel<true><<<xrt_grid(F_l), XRT_BLOCK>>>(L.b.tnodes, L.b.nodes, F_l, Rt.b.tnodes, thickness, num, d_pairs);
+      pairs_kernel<true><<<xrt_grid(F_l), XRT_BLOCK>>>(L.b.tnodes, L.b.nodes, F_l, Rt.b.tnodes, thickness, num, d_pairs, nullptr, 0u,
+                                                         (uint32_t)std::min<size_t>(total, 0xFFFFFFFFu));
     cudaEventRecord(e1, 0);
     if (cudaDeviceSynchronize() != cudaSuccess) rc = XRT_ERR_CUDA;
     if (rc == XRT_OK && traverse_ms) cudaEventElapsedTime(traverse_ms, e0, e1);

@@ -227,7 +227,7 @@ def sphere_motion(obs_pos, frame, amp=0.05, hz=1.0, fps=60.0):
     return out.astype(np.float32)
 
 
-def make_solver(scene, colors=None, bindings=None, lra=None, **params):
+def make_solver(scene, colors=None, bindings=None, lra=None, quality=None, strain_colors=None, **params):
     """Reference call order: AddCloth, AddObstacle, constraints, (colours), Start."""
     from .solver import ClothSolver
     if "particle_diameter" not in params:
@@ -245,6 +245,8 @@ def make_solver(scene, colors=None, bindings=None, lra=None, **params):
     if colors is not None:
         s.SetColors(0, colors[0])
         s.SetColors(1, colors[1])
+    if quality is not None:  # Quality-mode handle (quality: XrtQualityParams-like, True for the defaults)
+        s.SetQuality(None if quality is True else quality, strain_colors)
     s.Start()
     return s
 

@@ -11,7 +11,8 @@ import ctypes as C
 
 import numpy as np
 
-from ._abi import XrtError, XrtMeshDesc, XrtParams, XrtStats, default_params, lib
+from ._abi import (XrtCollisionStats, XrtError, XrtMeshDesc, XrtParams, XrtQualityParams, XrtStats, default_params,
+                   default_quality_params, lib)
 
 DBG = dict(MORTON=0, SORTED_OBJECT=1, NODES=2, AABBS=3, ESCAPE_INT=4, ESCAPE_EXT=5, VF_CONTACTS=6, RT_CONTACTS=7,
            EE_CONTACTS=8, PREDICTED=9, VELOCITY=10, COLORS_STRETCH=11, COLORS_BEND=12, NEIGHBORS=13, RTRI=14,
@@ -176,6 +177,104 @@ class ClothSolver:
     def SetClothPredicted(self, xyz):
         x = _f32(xyz).reshape(-1, 3)
         self._ck(lib.xrt_set_cloth_predicted(self._h, _pf(x)))
+
+    # -- Quality mode (ClothSolverBase::SimulateQuality, ClothSolverBase.cpp:263-362) ---------------
+    def SetQuality(self, q=None, strain_colors=None, **overrides):
+        """Before Start: the handle steps Quality frames.  q: XrtQualityParams or any object with its fields."""
+        qp = default_quality_params()
+        if q is not None:
+            for name, _ in XrtQualityParams._fields_:
+                if hasattr(q, name):
+                    setattr(qp, name, getattr(q, name))
+        for k, v in overrides.items():
+            setattr(qp, k, v)
+        self.quality = qp
+        c = _u32(strain_colors) if strain_colors is not None else None
+        self._ck(lib.xrt_set_quality(self._h, C.byref(qp), _pu(c)))
+
+    def SimulateQuality(self):
+        return self.SimulateSwift()  # xrt_step_frame runs the mode the handle was set up for
+
+    def QualityBeginFrame(self):
+        self._ck(lib.xrt_quality_begin_frame(self._h))
+
+    def ImminentGenerate(self):
+        n = C.c_size_t(0)
+        self._ck(lib.xrt_quality_imminent_generate(self._h, None, None, 0, C.byref(n)))
+        nodes, bary = np.zeros((n.value, 4), np.uint32), np.zeros((n.value, 4), np.float32)
+        if n.value:
+            self._ck(lib.xrt_quality_imminent_generate(self._h, _pu(nodes), _pf(bary), n.value, C.byref(n)))
+        return nodes, bary
+
+    def ImminentSolve(self):
+        self._ck(lib.xrt_quality_imminent_solve(self._h))
+
+    def RepUpdatePairs(self):
+        n = C.c_size_t(0)
+        self._ck(lib.xrt_quality_rep_update_pairs(self._h, None, 0, C.byref(n)))
+        pairs = np.zeros((n.value, 2), np.uint32)
+        if n.value:
+            # the second call refreshes the same pairs (the cloth tree only grows by positions it already holds)
+            self._ck(lib.xrt_quality_rep_update_pairs(self._h, _pu(pairs), n.value, C.byref(n)))
+        return pairs
+
+    def RepSolve(self):
+        self._ck(lib.xrt_quality_rep_solve(self._h))
+
+    def ObstacleBvhUpdate(self):
+        self._ck(lib.xrt_quality_obstacle_bvh_update(self._h))
+
+    def QualityIteration(self, iteration):
+        self._ck(lib.xrt_quality_iteration(self._h, int(iteration)))
+
+    def FindImpacts(self, thickness):
+        """(nodes[n,4], twn[n,9] = t, w[4], n[3], is_vf, n_pairs, n_candidates)"""
+        n, npairs, ncand = C.c_size_t(0), C.c_size_t(0), C.c_size_t(0)
+        self._ck(lib.xrt_quality_find_impacts(self._h, thickness, None, None, 0, C.byref(n), C.byref(npairs), C.byref(ncand)))
+        nodes, twn = np.zeros((n.value, 4), np.uint32), np.zeros((n.value, 9), np.float32)
+        if n.value:
+            self._ck(lib.xrt_quality_find_impacts(self._h, thickness, _pu(nodes), _pf(twn), n.value, C.byref(n),
+                                                  C.byref(npairs), C.byref(ncand)))
+        return nodes, twn, int(npairs.value), int(ncand.value)
+
+    def IndependentImpacts(self, nodes, twn, deform=0):
+        nodes, twn = _u32(nodes).reshape(-1, 4), _f32(twn).reshape(-1, 9)
+        on, ot = np.zeros_like(nodes), np.zeros_like(twn)
+        m = C.c_size_t(0)
+        self._ck(lib.xrt_quality_independent_impacts(self._h, _pu(nodes), _pf(twn), len(nodes), int(deform), _pu(on), _pf(ot),
+                                                     C.byref(m)))
+        return on[:m.value].copy(), ot[:m.value].copy()
+
+    def IsolateZones(self, nodes):
+        nodes = _u32(nodes).reshape(-1, 4)
+        col = np.zeros(len(nodes), np.int32)
+        nz = C.c_int32(0)
+        self._ck(lib.xrt_quality_isolate_zones(self._h, _pu(nodes), len(nodes), col.ctypes.data_as(_i32p), C.byref(nz)))
+        return col, int(nz.value)
+
+    def OptimizeZones(self, nodes, twn, colors, deform, thickness, obstacle_mass):
+        nodes, twn = _u32(nodes).reshape(-1, 4), _f32(twn).reshape(-1, 9)
+        colors = np.ascontiguousarray(colors, np.int32)
+        st = np.zeros(3, np.int32)
+        nz = int(colors.max()) + 1 if len(colors) else 0
+        self._ck(lib.xrt_quality_optimize_zones(self._h, _pu(nodes), _pf(twn), colors.ctypes.data_as(_i32p), len(nodes), nz,
+                                                int(deform), float(thickness), float(obstacle_mass), st.ctypes.data_as(_i32p)))
+        return dict(outer=int(st[0]), line_search=int(st[1]), converged=int(st[2]))
+
+    def CollisionStep(self):
+        st = XrtCollisionStats()
+        self._ck(lib.xrt_quality_collision_step(self._h, C.byref(st)))
+        return {name: int(getattr(st, name)) for name, _ in XrtCollisionStats._fields_}
+
+    def ClothRTri(self, n_faces):
+        out = np.zeros(n_faces, np.uint32)
+        self._ck(lib.xrt_quality_cloth_rtri(self._h, _pu(out), n_faces))
+        return out
+
+    def ObstaclePredicted(self):
+        out = np.zeros((self.n_obstacle_verts, 3), np.float32)
+        self._ck(lib.xrt_quality_get_obstacle_predicted(self._h, _pf(out)))
+        return out
 
     # -- building blocks (parity tests) ------------------------------------
     def BvhBuildObstacle(self):
