@@ -290,6 +290,28 @@ typedef struct xrt_stats {
 int xrt_greedy_color(const uint32_t* idx, size_t n, int arity, uint32_t n_verts,
                      uint32_t* colors, uint32_t* n_colors);
 
+/* Setup-time derivations of the reference on an index buffer: the unique undirected edges
+ * (sorted by (lower vertex, higher vertex)), the face -> edge table (edge j of a face joins its vertices j and j+1;
+ * what the reference's mesh loader hands to Face::SetEdges), the edge -> face adjacency (BuildEFAdjacency,
+ * physics/ClothSolverHelper.cpp:111-125), one stretch constraint per edge (PrepareBasicStretchData, :90-109) and
+ * one bend element per pair of faces on an edge (GenerateBendingElements, :4-88: [0], [1] the edge in the winding
+ * of the lower-index face, [2] its opposite vertex, [3] the other face's; theta = acos(clamp(n1 . n2))).
+ * O(F log F) on the host without vcglib's half-edge mesh; the arrays are allocated by the library and released
+ * with xrt_free_constraints.  Feed them to xrt_add_cloth (edges), xrt_set_stretch and xrt_set_bend. */
+typedef struct xrt_constraints {
+  uint32_t n_edges, n_bend;
+  uint32_t* edges;       /* 2 n_edges                       */
+  uint32_t* face_edges;  /* 3 n_faces                       */
+  float* stretch_rest;   /* n_edges                         */
+  uint32_t* bend_idx;    /* 4 n_bend                        */
+  float* bend_theta;     /* n_bend                          */
+  uint32_t* ef_offsets;  /* n_edges + 1 (CSR)               */
+  uint32_t* ef_faces;    /* ef_offsets[n_edges], ascending  */
+} xrt_constraints;
+int xrt_build_constraints(const float* positions, uint32_t n_verts, const uint32_t* indices, uint32_t n_faces,
+                          xrt_constraints* out);
+void xrt_free_constraints(xrt_constraints* c);
+
 /* Standalone LBVH build over triangles (BVH::UpdateData(ccd=false)+Construct)
  * for parity tests and the 200k-face scaling config.  Outputs as above. */
 int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts,

@@ -111,3 +111,47 @@ def test_shard_partition():
     with pytest.raises(ValueError):
         batch.shard(4, 2, 2)
     assert batch.frames_per_second(100, [10.0, 20.0]) == 5000.0
+
+
+def test_build_constraints_equals_the_numpy_generators():
+    """xrt_build_constraints (edges, face -> edge, edge -> face, stretch, bend in O(F log F) on the
+    host) against the numpy generators the scenes use, and on a non-manifold fin (three faces on one edge: three bend
+    elements, like GenerateBendingElements' i < j loop over the edge's face star)."""
+    for sc in (scene.drop_scene(24, sphere=(6, 12)), scene.body_scene(0.05)[0], scene.dress_scene(0.05)[0]):
+        c = X.build_constraints(sc.cloth_pos, sc.cloth_tri)
+        assert np.array_equal(c["edges"], sc.cloth_edges)
+        np.testing.assert_allclose(c["stretch_rest"], sc.stretch_rest, rtol=0, atol=1e-7)
+        assert np.array_equal(c["bend_idx"], sc.bend_idx)
+        np.testing.assert_allclose(c["bend_theta"], sc.bend_theta, rtol=0, atol=1e-6)
+        # face -> edge: edge j of a face joins its vertices j and j + 1
+        tri, fe = sc.cloth_tri.astype(np.int64), c["face_edges"]
+        for j in range(3):
+            e = c["edges"][fe[:, j]].astype(np.int64)
+            a, b = tri[:, j], tri[:, (j + 1) % 3]
+            assert np.array_equal(e[:, 0], np.minimum(a, b)) and np.array_equal(e[:, 1], np.maximum(a, b))
+        # edge -> faces: ascending, and exactly the faces that list the edge
+        off, ef = c["ef_offsets"], c["ef_faces"]
+        assert off[-1] == 3 * len(tri) and (np.diff(off) >= 1).all() and (np.diff(off) <= 2).all()
+        for e in (0, len(off) // 2, len(off) - 2):
+            faces = ef[off[e]:off[e + 1]]
+            assert list(faces) == sorted(faces) and all(e in fe[f] for f in faces)
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1]], np.float32)
+    tri = np.array([[0, 1, 2], [1, 0, 3], [0, 1, 4]], np.uint32)
+    c = X.build_constraints(pos, tri)
+    assert len(c["edges"]) == 7 and len(c["bend_idx"]) == 3
+    assert sorted(map(tuple, c["bend_idx"][:, 2:].tolist())) == [(2, 3), (2, 4), (3, 4)]
+    assert list(c["ef_faces"][c["ef_offsets"][0]:c["ef_offsets"][1]]) == [0, 1, 2]     # edge (0, 1)
+    with pytest.raises(X.XrtError):
+        X.build_constraints(pos, np.array([[0, 1, 9]], np.uint32))
+
+
+def test_workload_params_mirror_the_library_defaults():
+    """workloads.scene.swift_params (what the reference arm of bench.py uses without loading the product) must stay
+    equal to xrt_default_params."""
+    p, w = X.default_params(), scene.swift_params()
+    for name, _ in _abi.XrtParams._fields_:
+        a, b = getattr(p, name), getattr(w, name)
+        if name == "gravity":
+            assert list(a) == pytest.approx(list(b))
+        else:
+            assert a == pytest.approx(b), name

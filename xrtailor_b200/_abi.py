@@ -55,6 +55,15 @@ class XrtQualityParams(C.Structure):
     ]
 
 
+class XrtConstraints(C.Structure):
+    _fields_ = [
+        ("n_edges", C.c_uint32), ("n_bend", C.c_uint32), ("edges", C.POINTER(C.c_uint32)),
+        ("face_edges", C.POINTER(C.c_uint32)), ("stretch_rest", C.POINTER(C.c_float)),
+        ("bend_idx", C.POINTER(C.c_uint32)), ("bend_theta", C.POINTER(C.c_float)),
+        ("ef_offsets", C.POINTER(C.c_uint32)), ("ef_faces", C.POINTER(C.c_uint32)),
+    ]
+
+
 class XrtCollisionStats(C.Structure):
     _fields_ = [
         ("rounds", C.c_int32), ("success", C.c_int32), ("total_impacts", C.c_int32), ("deform", C.c_int32),
@@ -74,6 +83,7 @@ SYMBOLS = [
     "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
     "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
+    "xrt_build_constraints", "xrt_free_constraints",
     "xrt_default_quality_params", "xrt_set_quality", "xrt_quality_begin_frame", "xrt_quality_imminent_generate",
     "xrt_quality_imminent_solve", "xrt_quality_rep_update_pairs", "xrt_quality_rep_solve",
     "xrt_quality_obstacle_bvh_update", "xrt_quality_iteration", "xrt_quality_find_impacts",
@@ -137,6 +147,7 @@ def _load():
         "xrt_batch_set_obstacle_targets": [vp, f32p, C.c_size_t],
         "xrt_batch_launches_per_frame": [vp, C.c_int, u32p],
         "xrt_batch_set_readback": [vp, C.c_int],
+        "xrt_build_constraints": [f32p, C.c_uint32, u32p, C.c_uint32, C.POINTER(XrtConstraints)],
         "xrt_default_quality_params": [C.POINTER(XrtQualityParams)],
         "xrt_set_quality": [vp, C.POINTER(XrtQualityParams), u32p],
         "xrt_quality_begin_frame": [vp],
@@ -163,6 +174,8 @@ def _load():
     L.xrt_destroy.restype = None
     L.xrt_batch_destroy.argtypes = [vp]
     L.xrt_batch_destroy.restype = None
+    L.xrt_free_constraints.argtypes = [C.POINTER(XrtConstraints)]
+    L.xrt_free_constraints.restype = None
     L.xrt_last_error.argtypes = [vp]
     L.xrt_last_error.restype = C.c_char_p
     return L

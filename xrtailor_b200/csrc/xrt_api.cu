@@ -170,109 +170,6 @@ extern "C" int xrt_set_colors(xrt_solver* s, int kind, const uint32_t* colors, s
   return XRT_OK;
 }
 
-// ---------------------------------------------------------------------------
-// setup-time host work
-// ---------------------------------------------------------------------------
-
-// Deterministic greedy colouring in O(n): a 128-bit mask per vertex holds the
-// colours already used by constraints on that vertex.  Replaces the random
-// palette colouring + O(n^2) adjacency build of graph_coloring/Base.cu:163-317
-// and impl/StretchColoring.cu:6-24; any proper colouring is a valid
-// Gauss-Seidel order, and the reference's own order is random per run (F9).
-extern "C" int xrt_greedy_color(const uint32_t* idx, size_t n, int arity, uint32_t n_verts, uint32_t* colors,
-                                uint32_t* n_colors) {
-  if ((n && (!idx || !colors)) || (arity < 2 || arity > 4)) return XRT_ERR_INVALID;
-  std::vector<uint64_t> lo(n_verts, 0), hi(n_verts, 0);
-  uint32_t used = 0;
-  for (size_t c = 0; c < n; c++) {
-    uint64_t ml = 0, mh = 0;
-    for (int a = 0; a < arity; a++) {
-      const uint32_t v = idx[c * arity + a];
-      if (v >= n_verts) return XRT_ERR_INVALID;
-      ml |= lo[v];
-      mh |= hi[v];
-    }
-    uint32_t col;
-    if (~ml) col = (uint32_t)__builtin_ctzll(~ml);
-    else if (~mh) col = 64u + (uint32_t)__builtin_ctzll(~mh);
-    else return XRT_ERR_INVALID;  // > 128 colours: vertex degree beyond anything a triangle mesh produces
-    for (int a = 0; a < arity; a++) {
-      const uint32_t v = idx[c * arity + a];
-      if (col < 64) lo[v] |= 1ull << col;
-      else hi[v] |= 1ull << (col - 64);
-    }
-    colors[c] = col;
-    used = std::max(used, col + 1);
-  }
-  if (n_colors) *n_colors = used;
-  return XRT_OK;
-}
-
-// stable counting sort of constraints by colour; returns offsets[n_colors+1]
-// and whether any colour touches a vertex twice (then the kernels use atomics
-// like the reference does unconditionally)
-static void color_ranges(const std::vector<uint32_t>& idx, int arity, const std::vector<uint32_t>& color,
-                         uint32_t n_verts, std::vector<uint32_t>& perm, std::vector<uint32_t>& off, bool& improper) {
-  const size_t n = color.size();
-  uint32_t nc = 0;
-  for (uint32_t c : color) nc = std::max(nc, c + 1);
-  off.assign(nc + 1, 0);
-  for (uint32_t c : color) off[c + 1]++;
-  for (uint32_t c = 0; c < nc; c++) off[c + 1] += off[c];
-  perm.resize(n);
-  std::vector<uint32_t> cur(off.begin(), off.end() - 1);
-  for (size_t i = 0; i < n; i++) perm[cur[color[i]]++] = (uint32_t)i;
-  improper = false;
-  std::vector<uint32_t> stamp(n_verts, 0xFFFFFFFFu);
-  for (uint32_t c = 0; c < nc && !improper; c++)
-    for (uint32_t s = off[c]; s < off[c + 1] && !improper; s++)
-      for (int a = 0; a < arity; a++) {
-        const uint32_t v = idx[(size_t)perm[s] * arity + a];
-        if (stamp[v] == c) improper = true;
-        stamp[v] = c;
-      }
-}
-
-// vertex -> (face << 2 | corner) CSR, faces ascending per vertex
-// (BuildVFAdjacency, physics/ClothSolverHelper.cu:377-401 uses std::set<uint>)
-void xrt_build_vf(const std::vector<uint32_t>& tri, uint32_t V, std::vector<uint32_t>& off,
-                     std::vector<uint32_t>& idx) {
-  const size_t F = tri.size() / 3;
-  off.assign(V + 1, 0);
-  for (size_t i = 0; i < 3 * F; i++) off[tri[i] + 1]++;
-  for (uint32_t v = 0; v < V; v++) off[v + 1] += off[v];
-  idx.resize(3 * F);
-  std::vector<uint32_t> cur(off.begin(), off.end() - 1);
-  for (size_t f = 0; f < F; f++)
-    for (uint32_t j = 0; j < 3; j++) idx[cur[tri[3 * f + j]]++] = (uint32_t)(f << 2) | j;
-}
-
-// RTriBuild_Kernel (physics/representative_triangle/RTriangle.cu:19-74) on the
-// host: bit i   = this face is the lowest-index face on its vertex i,
-//       bit 3+i = this face owns edge (i, i+1): no other face shares it, or
-//                 the lowest-index other face sharing it has a larger index.
-void xrt_build_rtri(const std::vector<uint32_t>& tri, const std::vector<uint32_t>& vf_off,
-                       const std::vector<uint32_t>& vf_idx, std::vector<uint32_t>& rtri) {
-  const size_t F = tri.size() / 3;
-  rtri.assign(F, 0);
-  for (size_t f = 0; f < F; f++) {
-    uint32_t info = 0;
-    for (uint32_t i = 0; i < 3; i++) {
-      const uint32_t vi = tri[3 * f + i], vj = tri[3 * f + (i + 1) % 3];
-      if (vf_off[vi] < vf_off[vi + 1] && (vf_idx[vf_off[vi]] >> 2) == f) info |= 1u << i;
-      uint32_t of = 0xFFFFFFFFu;
-      for (uint32_t a = vf_off[vi]; a < vf_off[vi + 1] && of == 0xFFFFFFFFu; a++) {
-        const uint32_t g = vf_idx[a] >> 2;
-        if (g == f) continue;
-        for (uint32_t b = vf_off[vj]; b < vf_off[vj + 1]; b++)
-          if ((vf_idx[b] >> 2) == g) { of = g; break; }
-      }
-      if (f < of) info |= 1u << (i + 3u);
-    }
-    rtri[f] = info;
-  }
-}
-
 static std::vector<float4> to_float4(const std::vector<float>& pos, const std::vector<float>& w) {
   std::vector<float4> out(w.size());
   for (size_t i = 0; i < w.size(); i++) out[i] = make_float4(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2], w[i]);
@@ -336,8 +233,8 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
     }
   }
   std::vector<uint32_t> s_perm, b_perm;
-  color_ranges(s->s_idx, 2, s->s_color, c.V, s_perm, s->s_off, s->atomic_s);
-  color_ranges(s->b_idx, 4, s->b_color, c.V, b_perm, s->b_off, s->atomic_b);
+  xrt_color_ranges(s->s_idx, 2, s->s_color, c.V, s_perm, s->s_off, s->atomic_s);
+  xrt_color_ranges(s->b_idx, 4, s->b_color, c.V, b_perm, s->b_off, s->atomic_b);
   c.n_stretch = ns; c.n_sc = (uint32_t)s->s_off.size() - 1;
   c.n_bend = nb;    c.n_bc = (uint32_t)s->b_off.size() - 1;
   std::vector<uint2> hs(ns);

@@ -3,7 +3,7 @@
 // quadratures and the PBD repulsion constraints.  IEEE arithmetic in the reference's evaluation
 // order (this library is built with -fmad=false and without --use_fast_math), because every
 // function here ends in a discrete decision (a root inside [0,1], a barycentric sign, a proximity
-// threshold) that must come out the same as the CPU oracle's.
+// threshold) that must come out the same as in the CPU oracle.
 // Follows xrtailor/src/math/BasicPrimitiveTests.cu:286-301,369-438, math/MathFunctions.cu:85-146,
 // physics/impact_zone/ImpactHelper.cu:34-114, physics/repulsion/ImminentRepulsionHelper.cu:10-150,
 // physics/repulsion/PBDRepulsion.cu:329-468, physics/repulsion/Proximity.cu:10-36.

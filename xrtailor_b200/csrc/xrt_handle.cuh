@@ -106,7 +106,9 @@ static inline cudaError_t join_batch(xrt_solver* s) {
   XRT_CUDA_OK(join_batch(s))
 
 
-// host helpers of xrt_api.cu that the Quality-mode setup shares
+// setup-time host helpers (xrt_setup.cu)
+void xrt_color_ranges(const std::vector<uint32_t>& idx, int arity, const std::vector<uint32_t>& color, uint32_t n_verts,
+                      std::vector<uint32_t>& perm, std::vector<uint32_t>& off, bool& improper);
 void xrt_build_vf(const std::vector<uint32_t>& tri, uint32_t V, std::vector<uint32_t>& off, std::vector<uint32_t>& idx);
 void xrt_build_rtri(const std::vector<uint32_t>& tri, const std::vector<uint32_t>& vf_off,
                     const std::vector<uint32_t>& vf_idx, std::vector<uint32_t>& rtri);

@@ -647,7 +647,7 @@ __global__ void __launch_bounds__(QB) zone_optimize_kernel(OptArgs a) {
   }
   // Finalize_Kernel.  A node two zones list (an impact takes the zone of its FIRST zoned node, its other nodes may
   // sit in another zone) is a variable of both; the reference lets the zones race for it, here the zone with the
-  // higher index writes it, which is also what the serial oracle does.
+  // higher index writes it (what a serial pass over the variables would leave behind).
   for (uint32_t k = no + t; k < no + nn; k += QB) {
     if (a.skip[k]) continue;
     const uint32_t g = a.node[k];

@@ -11,7 +11,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._abi import (XrtCollisionStats, XrtError, XrtMeshDesc, XrtParams, XrtQualityParams, XrtStats, default_params,
+from ._abi import (XrtCollisionStats, XrtConstraints, XrtError, XrtMeshDesc, XrtParams, XrtQualityParams, XrtStats, default_params,
                    default_quality_params, lib)
 
 DBG = dict(MORTON=0, SORTED_OBJECT=1, NODES=2, AABBS=3, ESCAPE_INT=4, ESCAPE_EXT=5, VF_CONTACTS=6, RT_CONTACTS=7,
@@ -432,6 +432,24 @@ def persist_info(cluster=-1):
     if rc:
         raise XrtError(rc, "xrt_persist_info failed (no CUDA device)")
     return mx.value, res.value
+
+
+def build_constraints(positions, indices):
+    """xrt_build_constraints: dict(edges[E,2], face_edges[F,3], stretch_rest[E], bend_idx[B,4], bend_theta[B],
+    ef_offsets[E+1], ef_faces) from a vertex array and an index buffer (host work, no GPU needed)."""
+    pos, tri = _f32(positions).reshape(-1, 3), _u32(indices).reshape(-1, 3)
+    c = XrtConstraints()
+    rc = lib.xrt_build_constraints(_pf(pos), len(pos), _pu(tri), len(tri), C.byref(c))
+    if rc:
+        raise XrtError(rc, "xrt_build_constraints")
+    E, B, F = c.n_edges, c.n_bend, len(tri)
+    arr = lambda p, n, shape: np.ctypeslib.as_array(p, shape=(max(n, 1),))[:n].copy().reshape(shape)  # noqa: E731
+    out = dict(edges=arr(c.edges, 2 * E, (-1, 2)), face_edges=arr(c.face_edges, 3 * F, (-1, 3)),
+               stretch_rest=arr(c.stretch_rest, E, (-1,)), bend_idx=arr(c.bend_idx, 4 * B, (-1, 4)),
+               bend_theta=arr(c.bend_theta, B, (-1,)), ef_offsets=arr(c.ef_offsets, E + 1, (-1,)))
+    out["ef_faces"] = arr(c.ef_faces, int(out["ef_offsets"][-1]), (-1,))
+    lib.xrt_free_constraints(C.byref(c))
+    return out
 
 
 def greedy_color(idx, n_verts):
