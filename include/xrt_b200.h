@@ -381,9 +381,10 @@ typedef struct xrt_quality_params {
   float impact_zone_thickness;
   /* arena sizes (every list of the collision path lives in preallocated device memory; an overflow
    * makes the call fail with XRT_ERR_FACE_POOL and names the arena).  0 = default.               */
-  uint32_t max_pairs;       /* face-face pairs of one broad phase; default max(1 << 20, 128 F)    */
+  uint32_t max_pairs;       /* face-face pairs of one broad phase; default max(1 << 20, 256 F); quadratures share
+                             * this bound, repulsion items get four times it                                  */
   uint32_t max_candidates;  /* narrow-phase candidates (<= 15 per pair); default 4 * max_pairs    */
-  uint32_t max_impacts;     /* impacts / quadratures / repulsion items; default max_pairs         */
+  uint32_t max_impacts;     /* impacts of one FindImpacts; default max(1 << 20, max_pairs / 2)    */
 } xrt_quality_params;
 int xrt_default_quality_params(xrt_quality_params* q);
 
@@ -434,6 +435,11 @@ int xrt_quality_optimize_zones(xrt_solver* s, const uint32_t* nodes, const float
                                size_t n, int n_zones, int deform, float thickness, float obstacle_mass,
                                int32_t* stats3);
 int xrt_quality_collision_step(xrt_solver* s, xrt_collision_stats* stats);  /* CollisionStep, Entry.cu:140-256 */
+/* CUDA-event time of one stage on the handle's current state, mean of `reps` runs.  what: 0 cloth BVH build
+ * (UpdateData + Construct), 1 BVH::Update(ccd), 2 ccd tree build, 3 face-pair broad phase (cloth x obstacle + cloth x
+ * cloth on the ccd trees), 4 CCD narrow phase on those pairs (filter, expand, cubic tests, compaction), 5 FindImpacts
+ * as a whole.  *count: faces (0-2), pairs (3), candidates that reached the cubic solver (4), impacts (5). */
+int xrt_quality_profile(xrt_solver* s, int what, int reps, float* avg_ms, double* count);
 /* uint32[F] representative-triangle masks of the cloth (ClothSolverBase::SetupRTriangle) */
 int xrt_quality_cloth_rtri(xrt_solver* s, uint32_t* out, size_t n_faces);
 /* obstacle predicted positions (Node::x), float[3 Vo]: the deform pass of CollisionStep moves them */

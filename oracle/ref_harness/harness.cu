@@ -735,6 +735,50 @@ long long ref_find_impacts(void* h, float thickness, float dt, uint* nodes, floa
   cudaDeviceSynchronize();
   return ImpactsOut(s, s->last_impacts, nodes, twn, cap);
 }
+// CUDA-event times (ms, mean of reps) of the reference's own stages on the current state, for the C4 scaling table:
+// out[0] cloth BVH UpdateData(ccd) + Construct, [1] BVH::Update(ccd), [2] the two Traverse calls of FindImpacts,
+// [3] FindImpacts as a whole (its Traverses + CheckImpacts_Kernel + remove_if); counts: pairs, impacts
+void ref_quality_timing(void* h, float thickness, float dt, int reps, float* out, long long* counts) {
+  auto* s = use(h);
+  const int V = s->cloth->NumNodes(), Vo = s->obstacle->NumNodes();
+  SnapshotX1_Kernel<<<(V + 255) / 256, 256>>>(pointer(s->cloth->nodes), V, dt, 0);
+  if (Vo) SnapshotX1_Kernel<<<(Vo + 255) / 256, 256>>>(pointer(s->obstacle->nodes), Vo, dt, 1);
+  auto cb = std::make_shared<XRTailor::BVH>();
+  auto ob = std::make_shared<XRTailor::BVH>();
+  ob->UpdateData(pointer(s->obstacle->faces), 0.0f, true, s->obstacle->NumFaces());
+  ob->Construct(0.0f);
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  auto timed = [&](auto&& fn) {
+    fn();  // warm-up (first-touch allocations of thrust)
+    cudaDeviceSynchronize();
+    cudaEventRecord(e0);
+    for (int r = 0; r < reps; r++) fn();
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    return ms / (float)reps;
+  };
+  out[0] = timed([&] {
+    cb->UpdateData(pointer(s->cloth->faces), 0.0f, true, s->cloth->NumFaces());
+    cb->Construct(0.0f);
+  });
+  out[1] = timed([&] { cb->Update(pointer(s->cloth->faces), true); });
+  long long np = 0;
+  Scalar th = thickness;
+  out[2] = timed([&] {
+    np = (long long)Traverse(cb, ob, pointer(s->cloth->faces), pointer(s->obstacle->faces), th).size() +
+         (long long)Traverse(cb, cb, pointer(s->cloth->faces), pointer(s->cloth->faces), th).size();
+  });
+  long long ni = 0;
+  out[3] = timed([&] { ni = (long long)FindImpacts(cb, ob, pointer(s->cloth->faces), pointer(s->obstacle->faces), thickness, 0, 0).size(); });
+  counts[0] = np;
+  counts[1] = ni;
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+}
 // independentImpacts (Entry.cu:25-70) on the list ref_find_impacts kept
 long long ref_independent_impacts(void* h, int deform, uint* nodes, float* twn, long long cap) {
   auto* s = use(h);

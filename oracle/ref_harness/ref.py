@@ -58,6 +58,7 @@ def lib():
         L.ref_find_impacts.argtypes = [vp, C.c_float, C.c_float, u32p, f32p, ll, llp]; L.ref_find_impacts.restype = ll
         L.ref_independent_impacts.argtypes = [vp, C.c_int, u32p, f32p, ll]; L.ref_independent_impacts.restype = ll
         L.ref_collision_step.argtypes = [vp, C.c_float]; L.ref_collision_step.restype = None
+        L.ref_quality_timing.argtypes = [vp, C.c_float, C.c_float, C.c_int, f32p, C.POINTER(C.c_longlong)]; L.ref_quality_timing.restype = None
         L.ref_rep_evaluate_only.argtypes = [vp, f32p, i32p]; L.ref_rep_evaluate_only.restype = None
         L.ref_rep_contributions.argtypes = [vp, C.c_int, i32p, f32p, C.c_int]; L.ref_rep_contributions.restype = C.c_int
         L.ref_imminent_generate.argtypes = [vp, u32p, f32p, ll]; L.ref_imminent_generate.restype = ll
@@ -261,6 +262,13 @@ class RefSolver:
     def rep_solve(self, dt, iteration=0):
         lib().ref_rep_solve(self.h, dt, iteration)
 
+    def quality_timing(self, thickness, dt, reps=3):
+        """ms of the reference's ccd tree build, BVH::Update, the two Traverses and FindImpacts; pair and impact counts"""
+        out, cnt = np.zeros(4, np.float32), np.zeros(2, np.int64)
+        lib().ref_quality_timing(self.h, float(thickness), float(dt), int(reps), _pf(out), cnt.ctypes.data_as(C.POINTER(C.c_longlong)))
+        return dict(tree_build_ms=float(out[0]), tree_update_ms=float(out[1]), traverse_ms=float(out[2]), find_impacts_ms=float(out[3]),
+                    pairs=int(cnt[0]), impacts=int(cnt[1]))
+
     def rep_evaluate_only(self):
         V = self.V if hasattr(self, "V") else len(self.state(0)["x"])
         d, c = np.zeros((V, 3), np.float32), np.zeros(V, np.int32)
@@ -287,12 +295,12 @@ class RefSolver:
             self.h = None
 
 
-def time_frames(sc, steps, warmup, device=0, params=None, motion=None, bindings=None):
-    """Reference arm of bench.py: the reference's own Solver_Total (CUDA events
-    around SimulateSwift) over `steps` frames after `warmup`, same workload."""
-    import xrtailor_b200 as X
-    from xrtailor_b200 import scene
-    p = params or X.default_params()
+def time_frames(sc, steps, warmup, device=0, params=None, motion=None, bindings=None, ready=None):
+    """Reference arm of bench.py: the reference's own Solver_Total (CUDA events around SimulateSwift) over `steps`
+    frames after `warmup`, same workload.  Nothing of the product is loaded: scenes and defaults come from the
+    `workloads` package.  ready: optional callable run after setup + warm-up (the start line of a concurrent run)."""
+    from workloads import scene
+    p = params or scene.swift_params()
     if p.particle_diameter <= 0:
         p.particle_diameter = sc.particle_diameter()
     r = RefSolver(sc, p, device=device)
@@ -304,6 +312,8 @@ def time_frames(sc, steps, warmup, device=0, params=None, motion=None, bindings=
     wall0 = None
     for f in range(warmup + steps):
         if f == warmup:
+            if ready is not None:
+                ready()
             wall0 = time.perf_counter()
         r.set_obstacle_target(motion(f))
         ms.append(r.step_frame())
@@ -311,8 +321,10 @@ def time_frames(sc, steps, warmup, device=0, params=None, motion=None, bindings=
     ms = np.array(ms[warmup:])
     cs, cb, nsc, nbc = r.colors()
     r.close()
+    timers = "stubbed" if os.environ.get("XRT_REF_NO_TIMERS") == "1" else "as shipped"
     return {"frames_per_s": steps / (ms.sum() * 1e-3), "ms_per_frame": float(ms.mean()),
-            "ms_median": float(np.median(ms)), "wall_frames_per_s": steps / wall, "cores": 1,
+            "ms_median": float(np.median(ms)), "ms_p10": float(np.percentile(ms, 10)), "ms_p90": float(np.percentile(ms, 90)),
+            "wall_s": wall, "wall_frames_per_s": steps / wall, "cores": 1,
             "colors": [int(nsc), int(nbc)],
-            "sample": f"{steps} frames, reference CUDA physics (sm_100a, --use_fast_math) through the GL-free "
-                      f"harness, Solver_Total event time; {nsc}/{nbc} stretch/bend colours"}
+            "sample": f"{steps} frames, reference CUDA physics (sm_100a, --use_fast_math, per-kernel GPU timers {timers}) "
+                      f"through the GL-free harness, Solver_Total event time; {nsc}/{nbc} stretch/bend colours"}

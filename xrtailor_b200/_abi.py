@@ -88,7 +88,7 @@ SYMBOLS = [
     "xrt_quality_imminent_solve", "xrt_quality_rep_update_pairs", "xrt_quality_rep_solve",
     "xrt_quality_obstacle_bvh_update", "xrt_quality_iteration", "xrt_quality_find_impacts",
     "xrt_quality_independent_impacts", "xrt_quality_isolate_zones", "xrt_quality_optimize_zones",
-    "xrt_quality_collision_step", "xrt_quality_cloth_rtri", "xrt_quality_get_obstacle_predicted",
+    "xrt_quality_collision_step", "xrt_quality_profile", "xrt_quality_cloth_rtri", "xrt_quality_get_obstacle_predicted",
 ]
 
 
@@ -163,6 +163,7 @@ def _load():
         "xrt_quality_isolate_zones": [vp, u32p, C.c_size_t, i32p, i32p],
         "xrt_quality_optimize_zones": [vp, u32p, f32p, i32p, C.c_size_t, C.c_int, C.c_int, C.c_float, C.c_float, i32p],
         "xrt_quality_collision_step": [vp, C.POINTER(XrtCollisionStats)],
+        "xrt_quality_profile": [vp, C.c_int, C.c_int, f32p, C.POINTER(C.c_double)],
         "xrt_quality_cloth_rtri": [vp, u32p, C.c_size_t],
         "xrt_quality_get_obstacle_predicted": [vp, f32p],
     }

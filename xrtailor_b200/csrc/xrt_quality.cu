@@ -74,7 +74,7 @@ struct QualityState {
   BvhWork cbw, ccd_cw, ccd_ow;
   PairWork pw;
   // arenas
-  uint32_t pair_cap = 0, cand_cap = 0, imp_cap = 0;
+  uint32_t pair_cap = 0, cand_cap = 0, imp_cap = 0, quad_cap = 0, rep_cap = 0;
   uint2* pairs = nullptr;
   uint16_t* masks = nullptr;   // per pair: which of its tests pass the static filters
   uint32_t* cand = nullptr;    // pair << 4 | slot
@@ -1292,8 +1292,8 @@ void enqueue_imminent_generate(xrt_solver* s) {
   enqueue_pairs(s, q->cbvh, s->o.F ? &s->bvh : nullptr, 1e-6f);
   quad_count_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cnt + N_PAIRS, q->masks, q->bsum, q->bsum + QG_MAX);
   scan_sums_kernel<<<1, QG_MAX, 0, st>>>(q->bsum, q->boff, q->bsum + QG_MAX, q->boff + QG_MAX, G, q->cnt + N_QUAD_EE, q->cnt + N_QUAD,
-                                        q->imp_cap, q->cnt + OVERFLOW, OV_QUAD);
-  quad_fill_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cnt + N_PAIRS, q->masks, q->boff, q->boff + QG_MAX, q->quad_n, q->quad_b, q->imp_cap);
+                                        q->quad_cap, q->cnt + OVERFLOW, OV_QUAD);
+  quad_fill_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cnt + N_PAIRS, q->masks, q->boff, q->boff + QG_MAX, q->quad_n, q->quad_b, q->quad_cap);
 }
 int enqueue_imminent_solve(xrt_solver* s) {
   QualityState* q = s->q;
@@ -1311,8 +1311,8 @@ int enqueue_rep_update_pairs(xrt_solver* s) {
   bvh_update(q->cbvh, q->cbw, s->c.x0, s->c.x, s->c.tri, 1, st);
   enqueue_pairs(s, q->cbvh, s->o.F ? &s->bvh : nullptr, 1e-6f);
   rep_count_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cnt + N_PAIRS, q->masks, q->bsum);
-  scan_sums_kernel<<<1, QG_MAX, 0, st>>>(q->bsum, q->boff, nullptr, nullptr, G, nullptr, q->cnt + N_REP, q->imp_cap, q->cnt + OVERFLOW, OV_REP);
-  rep_fill_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cnt + N_PAIRS, q->masks, q->boff, q->rep_items, q->imp_cap);
+  scan_sums_kernel<<<1, QG_MAX, 0, st>>>(q->bsum, q->boff, nullptr, nullptr, G, nullptr, q->cnt + N_REP, q->rep_cap, q->cnt + OVERFLOW, OV_REP);
+  rep_fill_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cnt + N_PAIRS, q->masks, q->boff, q->rep_items, q->rep_cap);
   return 2 + 8 + 3;
 }
 int enqueue_rep_solve(xrt_solver* s) {
@@ -1444,10 +1444,12 @@ int xrt_quality_finalize(xrt_solver* s) {
     return XRT_ERR_CUDA;
   }
   // --- arenas ---
-  q->pair_cap = q->qp.max_pairs ? q->qp.max_pairs : std::max<uint32_t>(1u << 20, 128u * c.F);
+  q->pair_cap = q->qp.max_pairs ? q->qp.max_pairs : std::max<uint32_t>(1u << 20, 256u * c.F);
   XRT_REQUIRE(q->pair_cap < (1u << 28), "max_pairs must stay below 2^28");
   q->cand_cap = q->qp.max_candidates ? q->qp.max_candidates : 4u * q->pair_cap;
-  q->imp_cap = q->qp.max_impacts ? q->qp.max_impacts : q->pair_cap;
+  q->imp_cap = q->qp.max_impacts ? q->qp.max_impacts : std::max<uint32_t>(1u << 20, q->pair_cap / 2u);
+  q->quad_cap = q->pair_cap;       // <= 12 quadratures per pair, in practice a few per hundred pairs
+  q->rep_cap = 4u * q->pair_cap;   // <= 12 repulsion items per pair; ownership leaves about 3
   XRT_CUDA_OK(dev_alloc(&q->pairs, q->pair_cap));
   XRT_CUDA_OK(dev_alloc(&q->masks, q->pair_cap));
   XRT_CUDA_OK(dev_alloc(&q->cand, q->cand_cap));
@@ -1464,9 +1466,9 @@ int xrt_quality_finalize(xrt_solver* s) {
     XRT_CUDA_OK(cub::DeviceRadixSort::SortPairs(nullptr, q->sort_bytes, k, v, (int)q->imp_cap, 0, 32, s->st));
     XRT_CUDA_OK(cudaMalloc(&q->sort_tmp, q->sort_bytes ? q->sort_bytes : 16));
   }
-  XRT_CUDA_OK(dev_alloc(&q->quad_n, q->imp_cap));
-  XRT_CUDA_OK(dev_alloc(&q->quad_b, q->imp_cap));
-  XRT_CUDA_OK(dev_alloc(&q->rep_items, q->imp_cap));
+  XRT_CUDA_OK(dev_alloc(&q->quad_n, q->quad_cap));
+  XRT_CUDA_OK(dev_alloc(&q->quad_b, q->quad_cap));
+  XRT_CUDA_OK(dev_alloc(&q->rep_items, q->rep_cap));
   XRT_CUDA_OK(dev_alloc(&q->bsum, 2 * QG_MAX));
   XRT_CUDA_OK(dev_alloc(&q->boff, 2 * QG_MAX));
   XRT_CUDA_OK(dev_alloc(&q->cnt, N_COUNTERS));
@@ -1709,6 +1711,46 @@ extern "C" int xrt_quality_collision_step(xrt_solver* s, xrt_collision_stats* st
   if (rc == XRT_OK) XRT_CUDA_OK(cudaStreamSynchronize(s->st));
   if (stats) *stats = q->stats;
   return rc;
+}
+
+// CUDA-event time of one stage of the Quality path, averaged over `reps` launches on the handle's stream
+extern "C" int xrt_quality_profile(xrt_solver* s, int what, int reps, float* avg_ms, double* count) {
+  Q_READY();
+  XRT_REQUIRE(avg_ms && reps > 0 && what >= 0 && what <= 5, "quality_profile: bad argument");
+  cudaStream_t st = s->st;
+  const float th = q->qp.impact_zone_thickness;
+  if (what >= 2) {  // the stages below work on the ccd trees
+    enqueue_collision_setup(s);
+    if (what >= 4) enqueue_pairs(s, q->ccd_c, s->o.F ? &q->ccd_o : nullptr, th);
+  }
+  const QMesh m = make_mesh(s);
+  const int G = q->grid;
+  XRT_CUDA_OK(cudaStreamSynchronize(st));
+  XRT_CUDA_OK(cudaEventRecord(s->ev0, st));
+  for (int r = 0; r < reps; r++) {
+    switch (what) {
+      case 0: bvh_build(q->cbvh, q->cbw, s->c.x0, s->c.tri, s->c.F, s->p.morton_fast_div, st); break;
+      case 1: bvh_update(q->cbvh, q->cbw, s->c.x0, s->c.x, s->c.tri, 1, st); break;
+      case 2: bvh_build_ccd(q->ccd_c, q->ccd_cw, s->c.x0, s->c.x, s->c.tri, s->c.F, s->p.morton_fast_div, st); break;
+      case 3: enqueue_pairs(s, q->ccd_c, s->o.F ? &q->ccd_o : nullptr, th); break;
+      case 4:  // the narrow phase on the pairs in the arena: filter, expand, cubic test, compaction
+        ccd_filter_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cnt + N_PAIRS, th, q->masks, q->bsum);
+        scan_sums_kernel<<<1, QG_MAX, 0, st>>>(q->bsum, q->boff, nullptr, nullptr, G, nullptr, q->cnt + N_CAND, q->cand_cap, q->cnt + OVERFLOW, OV_CAND);
+        ccd_expand_kernel<<<G, QB, 0, st>>>(q->cnt + N_PAIRS, q->masks, q->boff, q->cand, q->cand_cap);
+        ccd_test_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cand, q->cnt + N_CAND, q->cand_t, q->bsum);
+        scan_sums_kernel<<<1, QG_MAX, 0, st>>>(q->bsum, q->boff, nullptr, nullptr, G, nullptr, q->cnt + N_IMP, q->imp_cap, q->cnt + OVERFLOW, OV_IMP);
+        ccd_compact_kernel<<<G, QB, 0, st>>>(m, q->pairs, q->cand, q->cnt + N_CAND, q->cand_t, q->boff, q->impacts, q->imp_cap);
+        break;
+      default: enqueue_find_impacts(s, th); break;
+    }
+  }
+  XRT_CUDA_OK(cudaEventRecord(s->ev1, st));
+  if (int rc = read_counters(s)) return rc;
+  float ms = 0.f;
+  XRT_CUDA_OK(cudaEventElapsedTime(&ms, s->ev0, s->ev1));
+  *avg_ms = ms / (float)reps;
+  if (count) *count = what == 3 ? (double)q->h_cnt[N_PAIRS] : (what == 4 ? (double)q->h_cnt[N_CAND] : (what == 5 ? (double)q->h_cnt[N_IMP] : (double)s->c.F));
+  return XRT_OK;
 }
 
 extern "C" int xrt_quality_cloth_rtri(xrt_solver* s, uint32_t* out, size_t n_faces) {

@@ -266,6 +266,11 @@ class ClothSolver:
         self._ck(lib.xrt_quality_collision_step(self._h, C.byref(st)))
         return {name: int(getattr(st, name)) for name, _ in XrtCollisionStats._fields_}
 
+    def QualityProfile(self, what, reps=5):
+        ms, n = C.c_float(), C.c_double()
+        self._ck(lib.xrt_quality_profile(self._h, int(what), int(reps), C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
     def ClothRTri(self, n_faces):
         out = np.zeros(n_faces, np.uint32)
         self._ck(lib.xrt_quality_cloth_rtri(self._h, _pu(out), n_faces))
