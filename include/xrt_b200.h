@@ -63,8 +63,13 @@ typedef struct xrt_params {
    * hardware cluster barriers between the phases; 148 / C garments run
    * concurrently on a B200.  -1: the largest cluster the device schedules.
    * -2: every SM of the device on ONE garment (cooperative launch, grid-wide
-   * software barrier): lowest latency for a single garment, no concurrency.
-   * Both shapes call the same device bodies and give identical results. */
+   * software barrier), no concurrency.
+   * -3: lowest latency for a single garment: a 16-CTA cluster keeps the predicted positions of
+   * the whole garment in its distributed shared memory and runs the Gauss-Seidel phases between two collision
+   * passes as ONE kernel (gathers are 215-cycle ld.shared::cluster, the phase boundary is the hardware cluster
+   * barrier); the collision passes themselves (BVH refit + queries) run device-wide in between.  Garments up to
+   * 131 072 vertices, proper colourings only.
+   * All shapes call the same device bodies and give identical results. */
   int32_t persist_cluster;
   int32_t device;                /* CUDA device ordinal                */
 } xrt_params;

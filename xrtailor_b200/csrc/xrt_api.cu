@@ -235,6 +235,35 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
   std::vector<uint32_t> s_perm, b_perm;
   xrt_color_ranges(s->s_idx, 2, s->s_color, c.V, s_perm, s->s_off, s->atomic_s);
   xrt_color_ranges(s->b_idx, 4, s->b_color, c.V, b_perm, s->b_off, s->atomic_b);
+  std::vector<uint32_t> s_cta, b_cta;
+  if (s->p.persist_cluster == -3) {
+    // distributed-shared-memory shape: inside each colour the constraints are ordered by the CTA that owns their
+    // lowest vertex (slice = vertices [r << shift, (r + 1) << shift)), and every CTA gets its own range of the colour
+    s->dsmem_shift = persist_dsmem_shift(c.V);
+    XRT_REQUIRE(s->dsmem_shift >= 0, "persist_cluster -3: needs 16-CTA clusters and a garment of at most 131072 vertices");
+    XRT_REQUIRE(!s->atomic_s && !s->atomic_b, "persist_cluster -3: needs proper stretch and bend colourings");
+    auto by_owner = [&](const std::vector<uint32_t>& idx, int arity, std::vector<uint32_t>& perm, const std::vector<uint32_t>& off,
+                        std::vector<uint32_t>& cta) {
+      auto owner = [&](uint32_t k) {
+        uint32_t m = idx[(size_t)k * arity];
+        for (int a = 1; a < arity; a++) m = std::min(m, idx[(size_t)k * arity + a]);
+        return m >> s->dsmem_shift;
+      };
+      cta.assign((off.size() - 1) * (XRT_DSMEM_CLUSTER + 1), 0);
+      for (size_t col = 0; col + 1 < off.size(); col++) {
+        std::stable_sort(perm.begin() + off[col], perm.begin() + off[col + 1], [&](uint32_t x, uint32_t y) { return owner(x) < owner(y); });
+        uint32_t* o = &cta[col * (XRT_DSMEM_CLUSTER + 1)];
+        uint32_t at = off[col];
+        for (int r = 0; r <= XRT_DSMEM_CLUSTER; r++) {
+          while (at < off[col + 1] && (int)owner(perm[at]) < r) at++;
+          o[r] = at;
+        }
+        o[XRT_DSMEM_CLUSTER] = off[col + 1];
+      }
+    };
+    by_owner(s->s_idx, 2, s_perm, s->s_off, s_cta);
+    by_owner(s->b_idx, 4, b_perm, s->b_off, b_cta);
+  }
   c.n_stretch = ns; c.n_sc = (uint32_t)s->s_off.size() - 1;
   c.n_bend = nb;    c.n_bc = (uint32_t)s->b_off.size() - 1;
   std::vector<uint2> hs(ns);
@@ -276,6 +305,10 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
   XRT_CUDA_OK(dev_upload(&c.b_theta, ht));
   XRT_CUDA_OK(dev_upload(&s->d_s_off, s->s_off));
   XRT_CUDA_OK(dev_upload(&s->d_b_off, s->b_off));
+  if (s->dsmem_shift >= 0) {
+    XRT_CUDA_OK(dev_upload(&s->d_s_cta_off, s_cta));
+    XRT_CUDA_OK(dev_upload(&s->d_b_cta_off, b_cta));
+  }
   c.n_lra = (uint32_t)s->l_rest.size();
   XRT_CUDA_OK(dev_upload(&c.l_src, s->l_src));
   XRT_CUDA_OK(dev_upload(&c.l_tgt, s->l_tgt));
@@ -361,11 +394,13 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
       cl = XRT_PERSIST_GRID;
       XRT_CUDA_OK(dev_alloc(&s->d_grid_bar, 1));
       XRT_CUDA_OK(cudaMemset(s->d_grid_bar, 0, sizeof(unsigned long long)));
+    } else if (cl == -3) {
+      cl = XRT_PERSIST_DSMEM;  // checked where the constraints were ordered, above
     } else if (cl < 0 || cl > mx) {
       cl = mx;
     }
-    XRT_REQUIRE(cl == 0 || cl == XRT_PERSIST_GRID || (cl & (cl - 1)) == 0,
-                "persist_cluster must be 0, -1, -2 or a power of two up to 16");
+    XRT_REQUIRE(cl == 0 || cl == XRT_PERSIST_GRID || cl == XRT_PERSIST_DSMEM || (cl & (cl - 1)) == 0,
+                "persist_cluster must be 0, -1, -2, -3 or a power of two up to 16");
     s->cluster = cl;
     const char* pe = getenv("XRT_PERSIST_PROF");
     if (cl > 0 && pe && pe[0] == '1') {
@@ -482,6 +517,38 @@ static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
   int cnt = 0;
   for (int substep = 0; substep < p.num_substeps; substep++) {
     const bool hash = p.enable_self_collision && substep % std::max(1, p.inter_leaved_hash) == 0;
+    if (s->cluster == XRT_PERSIST_DSMEM) {
+      // distributed-shared-memory shape: the substep is cut at its collision passes; those run as device-wide
+      // per-stage kernels, everything between them as one segment on the 16-CTA cluster (xrt_persist.cu)
+      if (hash) {
+        launch_predict(c, s->k, st);
+        launch_hash(c, s->k, st);
+        launches += 6;
+      }
+      PersistArgs a = make_persist_args(s, substep, moved, !hash);
+      a.x_shift = (uint32_t)s->dsmem_shift;
+      a.s_cta_off = s->d_s_cta_off;
+      a.b_cta_off = s->d_b_cta_off;
+      auto due = [&](int it) { return s->o.F && (uint32_t)(substep * p.num_iterations + it) % frequency == 0; };
+      int it = 0;
+      bool resume = false;
+      while (true) {
+        int g = resume ? it + 1 : it;
+        while (g < p.num_iterations && !due(g)) g++;
+        a.it_begin = it;
+        a.stop_at = g;  // == num_iterations: run to the end of the substep (and finalize)
+        a.resume = resume ? 1 : 0;
+        launch_swift_segment(a, st);
+        launches++;
+        a.do_predict = 0;
+        if (g >= p.num_iterations) break;
+        enqueue_collision_pass(s, moved, cnt, &launches);
+        cnt++;
+        it = g;
+        resume = true;
+      }
+      continue;
+    }
     if (s->cluster > 0) {
       // persistent shape: [predict + hash when due] + ONE kernel for the rest of the substep
       if (hash) {
@@ -722,7 +789,7 @@ extern "C" int xrt_profile_kernel(xrt_solver* s, int which, int reps, float* avg
         case 5: {
           // the persistent substep kernel (substep 1: predict inside, no hash before it);
           // algorithmic bytes = the frame's minus the BVH build, per substep
-          XRT_REQUIRE(s->cluster > 0, "profile_kernel: persistent shape is off (persist_cluster = 0)");
+          XRT_REQUIRE(s->cluster > 0 && s->cluster != XRT_PERSIST_DSMEM, "profile_kernel: no persistent substep kernel in this launch shape");
           const PersistArgs a = make_persist_args(s, 1 % s->p.num_substeps, s->o.F != 0, true);
           XRT_CUDA_OK(launch_swift_substep(a, s->cluster, s->st));
           launches++;
@@ -747,7 +814,8 @@ extern "C" int xrt_batch_profile_substep(xrt_solver** handles, int n, int reps, 
   xrt_solver* s = handles[0];
   XRT_READY();
   for (int i = 0; i < n; i++) {
-    if (!handles[i] || !handles[i]->finalized || handles[i]->p.device != s->p.device || handles[i]->cluster <= 0) {
+    if (!handles[i] || !handles[i]->finalized || handles[i]->p.device != s->p.device || handles[i]->cluster <= 0 ||
+        handles[i]->cluster == XRT_PERSIST_DSMEM) {
       xrt_set_error(s, "batch_profile_substep: handle %d is null, not finalized, on another device or per-stage", i);
       return XRT_ERR_INVALID;
     }
@@ -862,7 +930,7 @@ extern "C" int xrt_batch_create(xrt_solver** handles, int n, int groups, int wor
       xrt_set_error(s, "batch_create: handle %d is null, not finalized, on another device or a Quality-mode handle", i);
       return XRT_ERR_INVALID;
     }
-    if (h->cluster < 1 || h->cluster == XRT_PERSIST_GRID || h->cluster != s->cluster ||
+    if (h->cluster < 1 || h->cluster == XRT_PERSIST_GRID || h->cluster == XRT_PERSIST_DSMEM || h->cluster != s->cluster ||
         h->p.num_substeps != s->p.num_substeps) {
       xrt_set_error(s, "batch_create: handle %d: a shared launch needs persist_cluster >= 1 and the same cluster size "
                        "and substep count on every handle", i);
@@ -1602,7 +1670,7 @@ extern "C" void xrt_destroy(xrt_solver* s) {
                   c.s_perm, c.b_idx, c.b_theta, c.l_src, c.l_tgt, c.l_rest, c.delta, c.vf, c.rt, c.ee, c.p_hash,
                   c.p_index, c.p_hash_b, c.p_index_b, c.cell_start, c.cell_end, c.neighbors, c.hash_tmp, c.cnt_vf, c.v_active, c.e_active, s->d_prof, s->d_grid_bar, c.bd_idx, c.bd_par, c.bd_k,
                   c.cnt_rt, c.cnt_ee, s->o.x0, s->o.x, s->o.x1, s->o.n, s->o.n1, s->o.tri, s->o.vf_off,
-                  s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_stage, s->d_seq, s->d_up, s->d_dn};
+                  s->o.vf_idx, s->o.rtri, s->d_s_off, s->d_b_off, s->d_s_cta_off, s->d_b_cta_off, s->d_stage, s->d_seq, s->d_up, s->d_dn};
   for (void* p : ptrs) cudaFree(p);
   if (s->bvh.n_obj) bvh_free(&s->bvh, &s->bw);
   if (s->stage) cudaFreeHost(s->stage);

@@ -331,7 +331,8 @@ __device__ __forceinline__ bool gen_edge_item(const TNode* t, const float4* pred
 
 // SolveVFCCD_Kernel then SolveVFDCD_Kernel (PBDCollision.cu:279-297,57-75) on
 // the same vertex, in the reference's order, one load/store of x.
-__device__ __forceinline__ void solve_vertex_item(const float4* pred, float4* x, const VFContact* vf,
+template <class X>
+__device__ __forceinline__ void solve_vertex_item(const float4* pred, X x, const VFContact* vf,
                                                   const VFContact* rt, uint32_t i) {
   const VFContact c = rt[i], d = vf[i];
   if (c.index == -1 && d.index == -1) return;
@@ -359,7 +360,8 @@ __device__ __forceinline__ void solve_vertex_item(const float4* pred, float4* x,
 // SolveEEDCD_Kernel, PBDCollision.cu:163-207.  `active` is the bit the
 // generation pass recorded for this edge (dist < 1e6); inactive records are
 // not stored, so they must not be read.
-__device__ __forceinline__ void solve_edge_item(const float4* x, const uint2* edge, const EEContact* ee,
+template <class X>
+__device__ __forceinline__ void solve_edge_item(X x, const uint2* edge, const EEContact* ee,
                                                 float4* delta, uint32_t i) {
   const EEContact c = ee[i];
   const uint2 e = edge[i];

@@ -10,7 +10,8 @@
 namespace xrtdev {
 
 // PredictPositions_Kernel, ClothSolverHelper.cu:125-131
-__device__ __forceinline__ void predict_item(const float4* x0, float4* x, float4* v, const StepConst& k, uint32_t i) {
+template <class X>
+__device__ __forceinline__ void predict_item(const float4* x0, X x, float4* v, const StepConst& k, uint32_t i) {
   float4 p = x0[i], vel = v[i];
   if (p.w > XRT_EPS) {
     vel.x += k.gx * k.dt;
@@ -22,18 +23,24 @@ __device__ __forceinline__ void predict_item(const float4* x0, float4* x, float4
 }
 
 // Finalize_Kernel, ClothSolverHelper.cu:222-229
-__device__ __forceinline__ void finalize_item(float4* x0, const float4* x, float4* v, const StepConst& k, uint32_t i) {
+template <class X>
+__device__ __forceinline__ void finalize_item(float4* x0, X x, float4* v, const StepConst& k, uint32_t i) {
   float4 p = x[i], q = x0[i];
   const float s = xf_rcp(k.dt) * (1.0f - k.damping * k.dt);
   v[i] = make_float4((p.x - q.x) * s, (p.y - q.y) * s, (p.z - q.z) * s, 0.f);
   x0[i] = p;
 }
 
-__device__ __forceinline__ void add_pos(float4* x, uint32_t i, f3 c, bool atomic) {
+// float atomics on a position (improper colouring only); the distributed-shared-memory accessor has no such path
+__device__ __forceinline__ void pos_atomic_add(float4* x, uint32_t i, f3 c) {
+  atomicAdd(&x[i].x, c.x);
+  atomicAdd(&x[i].y, c.y);
+  atomicAdd(&x[i].z, c.z);
+}
+template <class X>
+__device__ __forceinline__ void add_pos(X x, uint32_t i, f3 c, bool atomic) {
   if (atomic) {
-    atomicAdd(&x[i].x, c.x);
-    atomicAdd(&x[i].y, c.y);
-    atomicAdd(&x[i].z, c.z);
+    pos_atomic_add(x, i, c);
   } else {
     float4 p = x[i];
     p.x += c.x; p.y += c.y; p.z += c.z;
@@ -44,7 +51,8 @@ __device__ __forceinline__ void add_pos(float4* x, uint32_t i, f3 c, bool atomic
 // SolveStretch_Kernel, BasicSolverHelper.cu:80-127.  The record (ij, rest) is
 // passed in so a caller can fetch it ahead of a barrier.
 // `lambda` is the multiplier carried from the previous iteration (0 at iteration 0).
-__device__ __forceinline__ void stretch_rec(float4* x, float* s_lambda, uint32_t id, uint2 ij, float rest,
+template <class X>
+__device__ __forceinline__ void stretch_rec(X x, float* s_lambda, uint32_t id, uint2 ij, float rest,
                                             float lambda, float alpha_tilde, bool atomic) {
   const float4 a = x[ij.x], b = x[ij.y];
   const f3 diff = mk3(a) - mk3(b);
@@ -66,7 +74,8 @@ __device__ __forceinline__ void stretch_rec(float4* x, float* s_lambda, uint32_t
   }
   s_lambda[id] = lambda;
 }
-__device__ __forceinline__ void stretch_one(float4* x, const uint2* s_idx, const float* s_rest, float* s_lambda,
+template <class X>
+__device__ __forceinline__ void stretch_one(X x, const uint2* s_idx, const float* s_rest, float* s_lambda,
                                             uint32_t id, float alpha_tilde, int iter, bool atomic) {
   stretch_rec(x, s_lambda, id, s_idx[id], s_rest[id], iter == 0 ? 0.f : s_lambda[id], alpha_tilde, atomic);
 }
@@ -74,7 +83,8 @@ __device__ __forceinline__ void stretch_one(float4* x, const uint2* s_idx, const
 // SolveBend_Kernel, BasicSolverHelper.cu:8-66.  Without atomics the four
 // positions gathered at the top are the ones updated at the bottom (a proper
 // colouring gives this thread exclusive ownership), so x is read once.
-__device__ __forceinline__ void bend_rec(float4* x, uint4 q, float theta0, float xpbd_bend, bool atomic) {
+template <class X>
+__device__ __forceinline__ void bend_rec(X x, uint4 q, float theta0, float xpbd_bend, bool atomic) {
   const float4 a1 = x[q.x], a2 = x[q.y], a3 = x[q.z], a4 = x[q.w];
   const float w1 = a1.w, w2 = a2.w, w3 = a3.w, w4 = a4.w;
   const f3 p1 = mk3(a1);
@@ -109,14 +119,16 @@ __device__ __forceinline__ void bend_rec(float4* x, uint4 q, float theta0, float
     x[q.w] = make_float4(r4.x, r4.y, r4.z, w4);
   }
 }
-__device__ __forceinline__ void bend_one(float4* x, const uint4* b_idx, const float* b_theta, uint32_t id,
+template <class X>
+__device__ __forceinline__ void bend_one(X x, const uint4* b_idx, const float* b_theta, uint32_t id,
                                          float xpbd_bend, bool atomic) {
   bend_rec(x, b_idx[id], b_theta[id], xpbd_bend, atomic);
 }
 
 // SolveGeodesicLRA_Kernel, LongRangeAttachments.cu:5-26 (the reference's
 // non-atomic += on the target is kept: one slot per vertex is race free)
-__device__ __forceinline__ void lra_item(float4* x, const uint32_t* src, const uint32_t* tgt, const float* rest,
+template <class X>
+__device__ __forceinline__ void lra_item(X x, const uint32_t* src, const uint32_t* tgt, const float* rest,
                                          float stretchiness, uint32_t i) {
   const uint32_t s = src[i], t = tgt[i];
   const float target = rest[i] * stretchiness;
@@ -134,7 +146,8 @@ __device__ __forceinline__ void lra_item(float4* x, const uint32_t* src, const u
 // SolveBinding_Kernel, BindingConstraint.cu:56-92: one-sided tether of a cloth
 // vertex to a barycentric point of an obstacle triangle at its frame-end
 // position (Node::x); the kernel's `s = C / inv_mass ... * inv_mass` is kept as written.
-__device__ __forceinline__ void binding_item(float4* x, const float4* ox, const uint4* bd_idx, const float4* bd_par,
+template <class X>
+__device__ __forceinline__ void binding_item(X x, const float4* ox, const uint4* bd_idx, const float4* bd_par,
                                              const float* bd_k, uint32_t i) {
   const uint4 id = bd_idx[i];
   const float4 par = bd_par[i];
@@ -155,7 +168,8 @@ __device__ __forceinline__ void binding_item(float4* x, const float4* ox, const 
 }
 
 // ApplyDeltas_Kernel, ClothSolverHelper.cu:139-148
-__device__ __forceinline__ void apply_delta_item(float4* x, float4* delta, float relaxation, uint32_t i) {
+template <class X>
+__device__ __forceinline__ void apply_delta_item(X x, float4* delta, float relaxation, uint32_t i) {
   const float4 d = delta[i];
   if (d.w > 0.f) {
     float4 p = x[i];

@@ -6,7 +6,8 @@
 namespace xrtdev {
 
 // ComputeFriction + CollideParticles_Kernel, ClothSolverHelper.cu:150-211
-__device__ __forceinline__ void collide_item(float4* delta, const float4* x, const float4* x0,
+template <class X>
+__device__ __forceinline__ void collide_item(float4* delta, X x, const float4* x0,
                                              const uint32_t* neighbors, const StepConst& k, uint32_t V, uint32_t id) {
   const float4 pi4 = x[id];
   const f3 pi = mk3(pi4);

@@ -29,6 +29,8 @@ struct xrt_solver {
   // colour ranges over the permuted constraint arrays
   std::vector<uint32_t> s_off, b_off;
   uint32_t *d_s_off = nullptr, *d_b_off = nullptr;
+  uint32_t *d_s_cta_off = nullptr, *d_b_cta_off = nullptr;  // persist_cluster -3: [colours][17] per-CTA ranges
+  int dsmem_shift = -1;
   bool atomic_s = false, atomic_b = false;
   // device state
   ClothDev c;

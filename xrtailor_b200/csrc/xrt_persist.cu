@@ -121,6 +121,34 @@ __device__ __forceinline__ ColorRec fetch_color_rec(const PersistArgs& a, uint32
   return r;
 }
 
+// the same for the distributed-shared-memory shape: first item of this thread in CTA `rank`'s share of the phase
+__device__ __forceinline__ ColorRec fetch_color_rec_cta(const PersistArgs& a, uint32_t ph, uint32_t n_sc, uint32_t n_ph,
+                                                        uint32_t rank, int it) {
+  ColorRec r;
+  r.q = make_uint4(0, 0, 0, 0);
+  r.f = 0.f;
+  r.lambda = 0.f;
+  if (ph < n_sc) {
+    const uint32_t* o = a.s_cta_off + ph * (XRT_DSMEM_CLUSTER + 1) + rank;
+    const uint32_t i = o[0] + threadIdx.x;
+    if (i < o[1]) {
+      const uint2 ij = a.c.s_idx[i];
+      r.q.x = ij.x;
+      r.q.y = ij.y;
+      r.f = a.c.s_rest[i];
+      if (it != 0) r.lambda = a.c.s_lambda[i];
+    }
+  } else if (ph < n_ph) {
+    const uint32_t* o = a.b_cta_off + (ph - n_sc) * (XRT_DSMEM_CLUSTER + 1) + rank;
+    const uint32_t i = o[0] + threadIdx.x;
+    if (i < o[1]) {
+      r.q = a.c.b_idx[i];
+      r.f = a.c.b_theta[i];
+    }
+  }
+  return r;
+}
+
 template <int MODE>
 __device__ __forceinline__ void swift_substep_body(const PersistArgs& a) {
   const uint32_t nth = (MODE == SYNC_CLUSTER ? cluster_nctarank() : (MODE == SYNC_GRID ? gridDim.x : 1u)) * PT;
@@ -265,6 +293,160 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_batch_kernel(const Persis
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Distributed-shared-memory shape (single-garment latency).
+//
+// What bounds ONE garment is not bandwidth but ~1 100 dependent Gauss-Seidel phases per frame, each a short
+// gather -> project -> scatter over the predicted positions.  In the cluster shape above those positions travel
+// through L2: every phase pays a drain of the scatter to L2 (MEMBAR.GPU), an L1 invalidate and ~700-cycle gathers.
+// Here a 16-CTA cluster keeps Node::x of the whole garment in its shared memory (50 176 vertices x 16 B = 0.8 MB
+// over 16 x 64 KB; 100 489 over 16 x 128 KB): a gather is a 215-cycle ld.shared::cluster, a scatter a
+// st.shared::cluster, the phase boundary the hardware cluster barrier.  Per-vertex phases run on the CTA that owns
+// the vertex, so their own position is a local shared-memory access.
+// The BVH queries (contact generation) are the opposite kind of work -- wide and independent -- so they stay
+// device-wide kernels: the host cuts each substep into SEGMENTS at the iterations where a collision pass is due
+// (every `frequency` steps, ClothSolverBase.cpp:204), runs interpolate / refit / generate as per-stage kernels on all
+// 148 SMs, and the cluster resumes.  A frame is ~10 generation passes + ~14 segments in one CUDA graph.
+// Same device bodies as every other shape, so positions are bit-identical to the per-stage path.
+// ------------------------------------------------------------------------------------------------
+}  // namespace
+namespace xrtdev {
+struct XDsm {
+  uint32_t base;   // shared-window address of the slice (the same offset in every CTA of the cluster)
+  uint32_t shift;  // vertex i lives in CTA i >> shift, slot i & mask
+  uint32_t mask;
+  struct Ref {
+    uint32_t addr;
+    __device__ __forceinline__ operator float4() const {
+      float4 v;
+      asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+      return v;
+    }
+    __device__ __forceinline__ void operator=(float4 v) const {
+      asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    }
+  };
+  __device__ __forceinline__ uint32_t addr(uint32_t i) const {
+    uint32_t a;
+    asm("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(base + ((i & mask) << 4)), "r"(i >> shift));
+    return a;
+  }
+  __device__ __forceinline__ Ref operator[](uint32_t i) const { return Ref{addr(i)}; }
+};
+// improper colourings are rejected for this shape at setup; kept so add_pos<XDsm> instantiates
+__device__ __forceinline__ void pos_atomic_add(XDsm x, uint32_t i, f3 c) {
+  const uint32_t a = x.addr(i);
+  asm volatile("red.shared::cluster.add.f32 [%0], %1;" ::"r"(a), "f"(c.x) : "memory");
+  asm volatile("red.shared::cluster.add.f32 [%0], %1;" ::"r"(a + 4), "f"(c.y) : "memory");
+  asm volatile("red.shared::cluster.add.f32 [%0], %1;" ::"r"(a + 8), "f"(c.z) : "memory");
+}
+}  // namespace xrtdev
+namespace {
+
+// One segment of a substep: [predict] then, from iteration it_begin on,
+//   head of an iteration = particle self-contact (collide + apply), tail = colours, LRA, contact solves, binding.
+// resume: iteration it_begin starts at its tail (its head and its collision pass ran before this launch).
+// The segment ends after the head of iteration stop_at (a collision pass is due there: the host runs it next), or
+// after the last iteration, with finalize.
+__global__ void __launch_bounds__(PT, 1) swift_segment_kernel(const __grid_constant__ PersistArgs a) {
+  extern __shared__ float4 xs[];
+  const uint32_t rank = cluster_ctarank();
+  const uint32_t nth = cluster_nctarank() * PT, tid = rank * PT + threadIdx.x;
+  const ClothDev& c = a.c;
+  const ObstacleDev& o = a.o;
+  const StepConst& k = a.k;
+  const uint32_t V = c.V, E = c.E;
+  const float alpha_s = k.stretch_compliance / (k.dt * k.dt);
+  const float xpbd_b = k.bend_compliance / k.dt / k.dt;
+  const XDsm x{(uint32_t)__cvta_generic_to_shared(xs), a.x_shift, (1u << a.x_shift) - 1u};
+  const uint32_t lo = rank << a.x_shift;                                // this CTA owns vertices [lo, hi)
+  const uint32_t hi = min(V, lo + (1u << a.x_shift));
+  const bool fresh = a.do_predict && a.it_begin == 0 && !a.resume;
+  PhaseClock pc;
+  pc.start(a.prof, tid);
+  if (fresh) {
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += PT) predict_item(c.x0, x, c.v, k, i);
+  } else {
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += PT) xs[i - lo] = c.x[i];
+  }
+  phase_sync<SYNC_CLUSTER>();
+  pc.lap(0);
+  int it = a.it_begin;
+  bool skip_head = a.resume != 0;
+  while (it < a.n_iter) {
+    if (!skip_head) {
+      if (a.self_collision) {
+        for (uint32_t i = lo + threadIdx.x; i < hi; i += PT) collide_item(c.delta, x, c.x0, c.neighbors, k, V, i);
+        phase_sync<SYNC_CLUSTER>();
+        pc.lap(1);
+        for (uint32_t i = lo + threadIdx.x; i < hi; i += PT) apply_delta_item(x, c.delta, k.relaxation, i);
+        phase_sync<SYNC_CLUSTER>();
+        pc.lap(2);
+      }
+      if (it == a.stop_at) break;
+    }
+    skip_head = false;
+    {
+      // a colour phase: every CTA projects the constraints it owns (those whose lowest vertex lives in its slice), so
+      // on a mesh numbered row by row all but the constraints across a slice boundary touch local shared memory only
+      // (the cluster's remote path moves 17 B per cycle and SM; a colour with every endpoint remote is bound by it)
+      const uint32_t n_sc = c.n_sc, n_ph = c.n_sc + (a.solve_bending ? c.n_bc : 0u);
+      ColorRec cur = fetch_color_rec_cta(a, 0, n_sc, n_ph, rank, it);
+      for (uint32_t ph = 0; ph < n_ph; ph++) {
+        if (ph < n_sc) {
+          const uint32_t end = a.s_cta_off[ph * (XRT_DSMEM_CLUSTER + 1) + rank + 1];
+          uint32_t i = a.s_cta_off[ph * (XRT_DSMEM_CLUSTER + 1) + rank] + threadIdx.x;
+          if (i < end) {
+            stretch_rec(x, c.s_lambda, i, make_uint2(cur.q.x, cur.q.y), cur.f, cur.lambda, alpha_s, false);
+            for (i += PT; i < end; i += PT) stretch_one(x, c.s_idx, c.s_rest, c.s_lambda, i, alpha_s, it, false);
+          }
+        } else {
+          const uint32_t col = ph - n_sc, end = a.b_cta_off[col * (XRT_DSMEM_CLUSTER + 1) + rank + 1];
+          uint32_t i = a.b_cta_off[col * (XRT_DSMEM_CLUSTER + 1) + rank] + threadIdx.x;
+          if (i < end) {
+            bend_rec(x, cur.q, cur.f, xpbd_b, false);
+            for (i += PT; i < end; i += PT) bend_one(x, c.b_idx, c.b_theta, i, xpbd_b, false);
+          }
+        }
+        cur = fetch_color_rec_cta(a, ph + 1, n_sc, n_ph, rank, it);
+        phase_sync<SYNC_CLUSTER>();
+        pc.lap(ph < n_sc ? 6 : 7);
+      }
+    }
+    if (a.lra && c.n_lra) {
+      for (uint32_t i = tid; i < c.n_lra; i += nth) lra_item(x, c.l_src, c.l_tgt, c.l_rest, k.lra_stretchiness, i);
+      phase_sync<SYNC_CLUSTER>();
+    }
+    if (o.F) {
+      for (uint32_t i = lo + threadIdx.x; i < hi; i += PT)
+        if (load_active_bit(c.v_active, i)) solve_vertex_item(a.bvh.pred, x, c.vf, c.rt, i);
+      phase_sync<SYNC_CLUSTER>();
+      pc.lap(9);
+      if (E) {
+        for (uint32_t i = tid; i < E; i += nth)
+          if (load_active_bit(c.e_active, i)) solve_edge_item(x, c.edge, c.ee, c.delta, i);
+        phase_sync<SYNC_CLUSTER>();
+        pc.lap(10);
+      }
+      for (uint32_t i = lo + threadIdx.x; i < hi; i += PT) apply_delta_item(x, c.delta, k.relaxation, i);
+      phase_sync<SYNC_CLUSTER>();
+      pc.lap(11);
+      if (c.n_bind) {
+        for (uint32_t i = tid; i < c.n_bind; i += nth) binding_item(x, o.x, c.bd_idx, c.bd_par, c.bd_k, i);
+        phase_sync<SYNC_CLUSTER>();
+      }
+    }
+    it++;
+  }
+  if (it >= a.n_iter && a.do_finalize)
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += PT) finalize_item(c.x0, x, c.v, k, i);
+  // Node::x back to global memory for the kernels that run between segments (BVH queries, spatial hash, getters);
+  // every CTA's slice is final here: the last phase above ended with a cluster barrier
+  for (uint32_t i = lo + threadIdx.x; i < hi; i += PT) c.x[i] = xs[i - lo];
+  phase_sync<SYNC_CLUSTER>();  // no CTA leaves while another one may still read its shared memory
+  pc.lap(12);
+}
+
 }  // namespace
 
 int persist_max_cluster() {
@@ -361,6 +543,35 @@ cudaError_t launch_swift_substep(const PersistArgs& a, int cluster, cudaStream_t
   cfg.attrs = at;
   cfg.numAttrs = 1;
   return cudaLaunchKernelEx(&cfg, swift_substep_kernel<SYNC_CLUSTER>, a);
+}
+
+int persist_dsmem_shift(uint32_t V) {
+  if (persist_max_cluster() < XRT_DSMEM_CLUSTER) return -1;
+  for (int sh = 6; sh <= XRT_DSMEM_MAX_SHIFT; sh++)
+    if (((uint64_t)XRT_DSMEM_CLUSTER << sh) >= V) return sh;
+  return -1;
+}
+
+cudaError_t launch_swift_segment(const PersistArgs& a, cudaStream_t st) {
+  static bool once = false;
+  if (!once) {
+    cudaFuncSetAttribute(swift_segment_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+    cudaFuncSetAttribute(swift_segment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (16 << XRT_DSMEM_MAX_SHIFT));
+    once = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(XRT_DSMEM_CLUSTER);
+  cfg.blockDim = dim3(PT);
+  cfg.dynamicSmemBytes = (size_t)16 << a.x_shift;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = XRT_DSMEM_CLUSTER;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, swift_segment_kernel, a);
 }
 
 cudaError_t launch_swift_substep_batch(const PersistArgs* table, const int* moved, uint32_t n, int sub_begin,

@@ -2,7 +2,7 @@
 bench.py uses them without loading libxrt_b200.so).  This module re-exports them for the tests and adds make_solver,
 the one helper that does touch the product."""
 from workloads.scene import *  # noqa: F401,F403
-from workloads.scene import SEED, Scene  # noqa: F401
+from workloads.scene import SEED, Scene, _BODY_PARTS  # noqa: F401
 
 
 def make_solver(scene, colors=None, bindings=None, lra=None, quality=None, strain_colors=None, **params):
