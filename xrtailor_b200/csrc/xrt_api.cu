@@ -61,6 +61,11 @@ extern "C" int xrt_create(const xrt_params* p, xrt_solver** out) {
   xrt_solver* s = new xrt_solver();
   s->p = *p;
   if (cudaStreamCreateWithFlags(&s->st, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&s->st2, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&s->ev_prep, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&s->ev_side, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&s->ev_gv, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreate(&s->ev0) != cudaSuccess || cudaEventCreate(&s->ev1) != cudaSuccess) {
     delete s;
     return XRT_ERR_CUDA;
@@ -356,6 +361,7 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
       xrt_set_error(s, "BVH allocation failed");
       return XRT_ERR_CUDA;
     }
+    XRT_CUDA_OK(dev_alloc(&s->pred_alt, 3 * (size_t)o.F));
   }
   // --- bindings: GenerateBinding_Kernel (BindingConstraint.cu:22-46) on the host ---
   c.n_bind = (uint32_t)s->bd_vert.size();
@@ -439,6 +445,7 @@ extern "C" int xrt_finalize_setup(xrt_solver* s) {
 // (ClothSolverBase.cpp:215-237; binding->Solve is a no-op without bindings)
 static void enqueue_iteration(xrt_solver* s, int iteration, uint32_t* launches) {
   const ClothDev& c = s->c;
+  if (!s->frame_bvh.tnodes) s->frame_bvh = s->bvh;  // eager use outside a frame
   cudaStream_t st = s->st;
   for (uint32_t col = 0; col < c.n_sc; col++) {
     launch_stretch_color(c, s->k, s->s_off[col], s->s_off[col + 1], iteration, s->atomic_s, st);
@@ -454,7 +461,7 @@ static void enqueue_iteration(xrt_solver* s, int iteration, uint32_t* launches) 
     (*launches)++;
   }
   if (s->o.F) {
-    launch_solve_contacts(c, s->bvh, s->k, st);  // RT solve, VF solve, EE solve
+    launch_solve_contacts(c, s->frame_bvh, s->k, st);  // RT solve, VF solve, EE solve
     (*launches) += c.E ? 2 : 1;
     launch_apply_deltas(c, s->k, st);
     (*launches)++;
@@ -465,17 +472,66 @@ static void enqueue_iteration(xrt_solver* s, int iteration, uint32_t* launches) 
   }
 }
 
-static void enqueue_collision_pass(xrt_solver* s, bool moved, int cnt, uint32_t* launches) {
-  if (!s->o.F) return;
-  cudaStream_t st = s->st;
-  if (moved) {
-    launch_interpolate(s->o, cnt, s->p.num_collision_passes, st);
-    launch_normals(s->o.x1, s->o.n1, s->o.tri, s->o.vf_off, s->o.vf_idx, s->o.V, st);
-    bvh_refit_midstep(s->bvh, s->bw, s->o.x1, s->o.n1, s->o.tri, s->p.bvh_tolerance, st);
-    (*launches) += 2 + bvh_refit_launches();
+// The tree as collision pass `cnt` of this frame sees it.  The primitives (pred = x1 + tol n1) exist twice: the contact
+// solves after pass k still read pass k's copy while the side branch already refits the tree for pass k + 1 into the
+// other one.  The last pass of a frame always lands in s->bvh.pred (what the getters and the eager entry points read).
+static DevBVH pass_bvh(const xrt_solver* s, int cnt) {
+  DevBVH b = s->bvh;
+  if (((s->frame_passes - 1 - cnt) & 1) && s->pred_alt) b.pred = s->pred_alt;
+  return b;
+}
+
+// Obstacle side of collision pass `cnt`: Interpolate + UpdateMidstepNormals + RefitMidstep (ClothSolverBase.cpp:
+// 205-209).  It needs nothing from the cloth, so in the frame graph it runs on the side branch while the main branch
+// is still busy with the Gauss-Seidel phases before the pass.  It waits for the vertex queries of the previous pass
+// (they read the tree this refit grows); the edge queries of that pass precede it on the side branch itself.
+static void enqueue_obstacle_prep(xrt_solver* s, int cnt, uint32_t* launches) {
+  cudaStream_t st2 = s->st2;
+  if (!s->side_open) {
+    cudaEventRecord(s->ev_fork, s->st);
+    cudaStreamWaitEvent(st2, s->ev_fork, 0);
+    s->side_open = true;
   }
-  launch_generate_contacts(s->c, s->bvh, s->o.rtri, false, st);
+  if (cnt > 0) cudaStreamWaitEvent(st2, s->ev_gv, 0);
+  launch_interpolate(s->o, cnt, s->p.num_collision_passes, st2);
+  launch_normals(s->o.x1, s->o.n1, s->o.tri, s->o.vf_off, s->o.vf_idx, s->o.V, st2);
+  bvh_refit_midstep(pass_bvh(s, cnt), s->bw, s->o.x1, s->o.n1, s->o.tri, s->p.bvh_tolerance, st2);
+  cudaEventRecord(s->ev_prep, st2);
+  (*launches) += 2 + bvh_refit_launches();
+}
+
+// One collision pass of the per-stage frame graph.  Main branch: vertex queries; side branch: edge queries
+// (independent of the vertex queries: both only read the tree and the positions), then the obstacle side of the
+// next pass.  last: no pass follows in this frame.
+static void enqueue_collision_pass(xrt_solver* s, bool moved, int cnt, bool last, uint32_t* launches) {
+  if (!s->o.F) return;
+  cudaStream_t st = s->st, st2 = s->st2;
+  if (moved) {
+    cudaStreamWaitEvent(st, s->ev_prep, 0);  // the tree of this pass (enqueue_obstacle_prep)
+    s->frame_bvh = pass_bvh(s, cnt);
+  }
+  if (s->c.E) {
+    cudaEventRecord(s->ev_fork, st);
+    cudaStreamWaitEvent(st2, s->ev_fork, 0);
+    s->side_open = true;
+  }
+  launch_generate_vertex_contacts(s->c, s->frame_bvh, st);
+  if (moved && !last) cudaEventRecord(s->ev_gv, st);
+  if (s->c.E) {
+    launch_generate_edge_contacts(s->c, s->frame_bvh, s->o.rtri, st2);
+    cudaEventRecord(s->ev_side, st2);
+    cudaStreamWaitEvent(st, s->ev_side, 0);
+  }
   (*launches) += s->c.E ? 2 : 1;
+  if (moved && !last) enqueue_obstacle_prep(s, cnt + 1, launches);
+}
+
+// the side branch must have rejoined the main one before the capture (or the frame) ends
+static void close_side_branch(xrt_solver* s) {
+  if (!s->side_open) return;
+  cudaEventRecord(s->ev_side, s->st2);
+  cudaStreamWaitEvent(s->st, s->ev_side, 0);
+  s->side_open = false;
 }
 
 // arguments of the persistent kernel for one substep of the frame
@@ -506,15 +562,30 @@ static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
   const ClothDev& c = s->c;
   cudaStream_t st = s->st;
   uint32_t launches = 0;
-  if (moved && s->o.F) {
-    // UpdateObstacleAnimationFrame: BVH UpdateData(0, ccd=false) + Construct on the
-    // frame-start positions (impl/smpl/ClothSolver.cpp:257-261)
-    bvh_build(s->bvh, s->bw, s->o.x0, s->o.tri, s->o.F, p.morton_fast_div, st);
-    launches += bvh_build_launches();
-  }
   uint32_t frequency = (uint32_t)(p.num_substeps * p.num_iterations) / (uint32_t)p.num_collision_passes;
   if (frequency == 0) frequency = 1;  // the reference divides by zero here
+  int n_pass = 0;  // collision passes of this frame
+  for (int step = 0; step < p.num_substeps * p.num_iterations; step++) n_pass += (uint32_t)step % frequency == 0;
+  s->frame_passes = n_pass;
+  s->frame_bvh = s->bvh;
+  const bool staged = s->cluster == 0 || s->cluster == XRT_PERSIST_DSMEM;  // collision passes are separate kernels
+  if (moved && s->o.F) {
+    // UpdateObstacleAnimationFrame: BVH UpdateData(0, ccd=false) + Construct on the frame-start positions
+    // (impl/smpl/ClothSolver.cpp:257-261).  In the staged shapes the build and the obstacle side of the first pass
+    // run on the side branch, beside predict, the spatial hash and the first self-contact solve.
+    cudaStream_t bst = st;
+    if (staged) {
+      cudaEventRecord(s->ev_fork, st);
+      cudaStreamWaitEvent(s->st2, s->ev_fork, 0);
+      s->side_open = true;
+      bst = s->st2;
+    }
+    bvh_build(s->bvh, s->bw, s->o.x0, s->o.tri, s->o.F, p.morton_fast_div, bst);
+    launches += bvh_build_launches();
+    if (staged) enqueue_obstacle_prep(s, 0, &launches);
+  }
   int cnt = 0;
+
   for (int substep = 0; substep < p.num_substeps; substep++) {
     const bool hash = p.enable_self_collision && substep % std::max(1, p.inter_leaved_hash) == 0;
     if (s->cluster == XRT_PERSIST_DSMEM) {
@@ -535,6 +606,7 @@ static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
       while (true) {
         int g = resume ? it + 1 : it;
         while (g < p.num_iterations && !due(g)) g++;
+        a.bvh = s->frame_bvh;
         a.it_begin = it;
         a.stop_at = g;  // == num_iterations: run to the end of the substep (and finalize)
         a.resume = resume ? 1 : 0;
@@ -542,7 +614,7 @@ static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
         launches++;
         a.do_predict = 0;
         if (g >= p.num_iterations) break;
-        enqueue_collision_pass(s, moved, cnt, &launches);
+        enqueue_collision_pass(s, moved, cnt, cnt + 1 >= n_pass, &launches);
         cnt++;
         it = g;
         resume = true;
@@ -574,7 +646,7 @@ static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
       }
       const uint32_t step = (uint32_t)(substep * p.num_iterations + it);
       if (step % frequency == 0) {
-        enqueue_collision_pass(s, moved, cnt, &launches);
+        enqueue_collision_pass(s, moved, cnt, cnt + 1 >= n_pass, &launches);
         cnt++;
       }
       enqueue_iteration(s, it, &launches);
@@ -590,6 +662,7 @@ static uint32_t enqueue_frame(xrt_solver* s, bool moved) {
   }
   launch_normals(c.x0, c.n, c.tri, c.vf_off, c.vf_idx, c.V, st);
   launches++;
+  close_side_branch(s);
   return launches;
 }
 
@@ -1405,6 +1478,7 @@ extern "C" int xrt_predict(xrt_solver* s) {
 extern "C" int xrt_solve_iteration(xrt_solver* s, int iteration) {
   XRT_READY();
   uint32_t l = 0;
+  s->frame_bvh = s->bvh;
   if (s->p.enable_self_collision) launch_collide_particles(s->c, s->k, s->st);
   enqueue_iteration(s, iteration, &l);
   XRT_CUDA_OK(cudaStreamSynchronize(s->st));
@@ -1680,6 +1754,12 @@ extern "C" void xrt_destroy(xrt_solver* s) {
   if (s->ev0) cudaEventDestroy(s->ev0);
   if (s->ev1) cudaEventDestroy(s->ev1);
   if (s->ev_join) cudaEventDestroy(s->ev_join);
+  if (s->st2) cudaStreamDestroy(s->st2);
+  if (s->ev_fork) cudaEventDestroy(s->ev_fork);
+  if (s->ev_prep) cudaEventDestroy(s->ev_prep);
+  if (s->ev_side) cudaEventDestroy(s->ev_side);
+  if (s->ev_gv) cudaEventDestroy(s->ev_gv);
+  cudaFree(s->pred_alt);
   if (s->st) cudaStreamDestroy(s->st);
   delete s;
 }

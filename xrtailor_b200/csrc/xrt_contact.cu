@@ -78,6 +78,17 @@ void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32
         bvh.tnodes, bvh.pred, rtri, c.x, c.edge, c.ee, counts ? c.cnt_ee : nullptr, c.e_active, c.E);
 }
 
+void launch_generate_vertex_contacts(const ClothDev& c, const DevBVH& bvh, cudaStream_t st) {
+  if (!bvh.n_obj) return;
+  generate_vertex_contacts_kernel<<<xrt_grid(c.V), XRT_BLOCK, 0, st>>>(bvh.tnodes, bvh.pred, c.x0, c.x, c.vf, c.rt, nullptr, nullptr,
+                                                                        c.v_active, c.V);
+}
+void launch_generate_edge_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, cudaStream_t st) {
+  if (!bvh.n_obj || !c.E) return;
+  generate_edge_contacts_kernel<<<xrt_grid(c.E), XRT_BLOCK, 0, st>>>(bvh.tnodes, bvh.pred, rtri, c.x, c.edge, c.ee, nullptr, c.e_active,
+                                                                      c.E);
+}
+
 void launch_solve_contacts(const ClothDev& c, const DevBVH& bvh, const StepConst& k, cudaStream_t st) {
   if (!bvh.n_obj) return;
   solve_vertex_contacts_kernel<<<xrt_grid(c.V), XRT_BLOCK, 0, st>>>(bvh.pred, c.x, c.vf, c.rt, c.v_active, c.V);

@@ -16,6 +16,12 @@ struct xrt_solver {
   xrt_params p{};
   char err[512] = {0};
   cudaStream_t st = nullptr;
+  cudaStream_t st2 = nullptr;  // side branch of the per-stage frame graph (edge queries, next pass's obstacle interpolation)
+  cudaEvent_t ev_fork = nullptr, ev_prep = nullptr, ev_side = nullptr, ev_gv = nullptr;
+  float4* pred_alt = nullptr;  // second copy of the obstacle primitives: pass k + 1 is refitted while pass k's contacts are solved
+  DevBVH frame_bvh{};          // the tree as the pass being enqueued sees it (pred = this pass's copy)
+  int frame_passes = 0;
+  bool side_open = false;      // the side stream has joined the capture of this frame
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool finalized = false;
   // host staging (caller data is copied, never retained)

@@ -91,6 +91,9 @@ void launch_interpolate(const ObstacleDev& o, int step, int num_steps, cudaStrea
 // ---- contacts (xrt_contact.cu) ----
 // counts: also record the per-query leaf-hit counts (debug getters); the frame path passes false
 void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, bool counts, cudaStream_t st);
+// the two halves of launch_generate_contacts, for the frame graph that runs them on two branches
+void launch_generate_vertex_contacts(const ClothDev& c, const DevBVH& bvh, cudaStream_t st);
+void launch_generate_edge_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, cudaStream_t st);
 void launch_solve_contacts(const ClothDev& c, const DevBVH& bvh, const StepConst& k, cudaStream_t st);
 void launch_candidates(const ClothDev& c, const DevBVH& bvh, int kind, const uint32_t* offsets,
                        uint32_t* items, uint32_t* counts, cudaStream_t st);
