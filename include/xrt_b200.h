@@ -90,23 +90,30 @@ typedef struct xrt_mesh_desc {
   uint32_t n_verts, n_faces, n_edges;
 } xrt_mesh_desc;
 
+/* Optional, once per process, before the host's first CUDA call: asks the driver for 32 hardware queues
+ * (CUDA_DEVICE_MAX_CONNECTIONS, unless the host set it), which batches of more than 8 streams need to run side by
+ * side.  The library changes nothing in the process environment unless this is called. */
+int xrt_global_init(void);
+
 /* ClothSolverBase lifetime: constructor / OnDestroy. */
 int xrt_create(const xrt_params* p, xrt_solver** out);
 void xrt_destroy(xrt_solver* s);
 const char* xrt_last_error(const xrt_solver* s);
 
 /* ClothSolverUniversal::AddCloth / AddObstacle
- * (impl/universal/ClothSolver.cpp:189,247).  One cloth mesh and one obstacle
- * mesh per handle (merge meshes on the caller side; the reference merges
- * them into one PhysicsMesh too).  *index_offset receives the first vertex
- * index of the mesh, like the reference's return value. */
+ * (impl/universal/ClothSolver.cpp:189,247).  Call once per garment / collider:
+ * like the reference, the library merges them into one cloth and one obstacle
+ * mesh with running index offsets.  *index_offset receives the first vertex
+ * index of this mesh in the merged numbering (the reference's return value);
+ * constraints, tethers and bindings added afterwards use merged indices. */
 int xrt_add_cloth(xrt_solver* s, const xrt_mesh_desc* m, int32_t* index_offset);
 int xrt_add_obstacle(xrt_solver* s, const xrt_mesh_desc* m, int32_t* index_offset);
 
 /* StretchSolver::AddCloth / BendSolver::AddCloth
  * (physics/dynamics/BasicSolver.cu:36-62,101-117).  Constraints as produced by
  * PrepareBasicStretchData / GenerateBendingElements
- * (physics/ClothSolverHelper.cpp:4-109). */
+ * (physics/ClothSolverHelper.cpp:4-109), or by xrt_build_constraints.  Each call
+ * APPENDS one garment's constraints (indices in the merged numbering). */
 int xrt_set_stretch(xrt_solver* s, const uint32_t* idx01, const float* rest, size_t n);
 int xrt_set_bend(xrt_solver* s, const uint32_t* idx0123, const float* theta, size_t n);
 

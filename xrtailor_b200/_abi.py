@@ -83,7 +83,7 @@ SYMBOLS = [
     "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
     "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
-    "xrt_build_constraints", "xrt_free_constraints",
+    "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init",
     "xrt_default_quality_params", "xrt_set_quality", "xrt_quality_begin_frame", "xrt_quality_imminent_generate",
     "xrt_quality_imminent_solve", "xrt_quality_rep_update_pairs", "xrt_quality_rep_solve",
     "xrt_quality_obstacle_bvh_update", "xrt_quality_iteration", "xrt_quality_find_impacts",
@@ -179,6 +179,9 @@ def _load():
     L.xrt_free_constraints.restype = None
     L.xrt_last_error.argtypes = [vp]
     L.xrt_last_error.restype = C.c_char_p
+    L.xrt_global_init.argtypes = []
+    L.xrt_global_init.restype = C.c_int
+    L.xrt_global_init()  # the tests and the bench step batches of up to 32 streams: ask for the queues before any CUDA call
     return L
 
 

@@ -13,13 +13,15 @@
 #include <cstring>
 #include <vector>
 
-// Batch mode steps many handles side by side, one stream each, every stream a chain of dependent
-// launches.  Streams map onto CUDA_DEVICE_MAX_CONNECTIONS hardware queues (default 8); two chains
-// in one queue serialise behind each other's dependencies, which capped the batch at 8 garments
-// in flight however many clusters were free (scratch/batch_curve.py: rounds of 10-16 launches took
-// two waves).  Ask for the maximum before the CUDA context exists; a value the caller set wins,
-// and if the host application created the context earlier this is a no-op.
-__attribute__((constructor)) static void xrt_request_hw_queues() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0); }
+// Batch mode steps many handles side by side, every stream a chain of dependent launches.  Streams map onto
+// CUDA_DEVICE_MAX_CONNECTIONS hardware queues (default 8); two chains in one queue serialise behind each other's
+// dependencies, which capped a batch at 8 garments in flight however many clusters were free
+// (profiles/r01h_hardware_queue_finding.txt).  The variable is read when the CUDA context is created, so a host that
+// wants 32 queues calls this once before its first CUDA call; a value the host already set wins.  Nothing happens at
+// load time any more (round 1 did this in a library constructor).
+extern "C" int xrt_global_init(void) {
+  return setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0) == 0 ? XRT_OK : XRT_ERR_INVALID;
+}
 
 extern "C" int xrt_default_params(xrt_params* p) {
   if (!p) return XRT_ERR_INVALID;
@@ -76,51 +78,50 @@ extern "C" int xrt_create(const xrt_params* p, xrt_solver** out) {
 
 extern "C" const char* xrt_last_error(const xrt_solver* s) { return s ? s->err : "null solver"; }
 
+// Appends mesh m to the merged mesh (pos / invm / tri / edge), its indices shifted by the vertices already there:
+// the reference merges every garment into one PhysicsMesh the same way (RegisterNewMesh with a running offset,
+// impl/universal/ClothSolver.cpp:247-350) and returns that offset to the caller.
 static int copy_mesh(xrt_solver* s, const xrt_mesh_desc* m, std::vector<float>& pos, std::vector<float>& invm,
-                     std::vector<uint32_t>& tri, std::vector<uint32_t>& edge, float default_inv_mass) {
+                     std::vector<uint32_t>& tri, std::vector<uint32_t>& edge, float default_inv_mass, int32_t* index_offset) {
   XRT_REQUIRE(m && m->positions && m->n_verts > 0, "mesh: positions missing");
   XRT_REQUIRE(m->n_faces == 0 || m->indices, "mesh: indices missing");
   XRT_REQUIRE(m->n_edges == 0 || m->edges, "mesh: edges missing");
-  if (m->n_verts > 1000000u) {  // MemoryPool.cuh:12-14 pool sizes
-    xrt_set_error(s, "node pool exhausted (%u > 1000000)", m->n_verts);
+  const size_t v0 = invm.size();
+  if (v0 + m->n_verts > 1000000u) {  // MemoryPool.cuh:12-14 pool sizes
+    xrt_set_error(s, "node pool exhausted (%zu > 1000000)", v0 + m->n_verts);
     return XRT_ERR_NODE_POOL;
   }
-  if (m->n_edges > 3000000u) { xrt_set_error(s, "edge pool exhausted"); return XRT_ERR_EDGE_POOL; }
-  if (m->n_faces > 2000000u) { xrt_set_error(s, "face pool exhausted"); return XRT_ERR_FACE_POOL; }
+  if (edge.size() / 2 + m->n_edges > 3000000u) { xrt_set_error(s, "edge pool exhausted"); return XRT_ERR_EDGE_POOL; }
+  if (tri.size() / 3 + m->n_faces > 2000000u) { xrt_set_error(s, "face pool exhausted"); return XRT_ERR_FACE_POOL; }
   for (size_t i = 0; i < 3 * (size_t)m->n_faces; i++) XRT_REQUIRE(m->indices[i] < m->n_verts, "mesh: face index out of range");
   for (size_t i = 0; i < 2 * (size_t)m->n_edges; i++) XRT_REQUIRE(m->edges[i] < m->n_verts, "mesh: edge index out of range");
-  pos.assign(m->positions, m->positions + 3 * (size_t)m->n_verts);
-  if (m->inv_mass) invm.assign(m->inv_mass, m->inv_mass + m->n_verts);
-  else invm.assign(m->n_verts, default_inv_mass);
-  tri.assign(m->indices, m->indices + 3 * (size_t)m->n_faces);
-  edge.assign(m->edges, m->edges + 2 * (size_t)m->n_edges);
+  pos.insert(pos.end(), m->positions, m->positions + 3 * (size_t)m->n_verts);
+  if (m->inv_mass) invm.insert(invm.end(), m->inv_mass, m->inv_mass + m->n_verts);
+  else invm.insert(invm.end(), m->n_verts, default_inv_mass);
+  for (size_t i = 0; i < 3 * (size_t)m->n_faces; i++) tri.push_back(m->indices[i] + (uint32_t)v0);
+  for (size_t i = 0; i < 2 * (size_t)m->n_edges; i++) edge.push_back(m->edges[i] + (uint32_t)v0);
+  if (index_offset) *index_offset = (int32_t)v0;
   return XRT_OK;
 }
 
 extern "C" int xrt_add_cloth(xrt_solver* s, const xrt_mesh_desc* m, int32_t* index_offset) {
   if (!s) return XRT_ERR_INVALID;
   XRT_REQUIRE(!s->finalized, "add_cloth after finalize_setup");
-  XRT_REQUIRE(s->c_pos.empty(), "one cloth mesh per handle (merge meshes on the caller side)");
-  int rc = copy_mesh(s, m, s->c_pos, s->c_invm, s->c_tri, s->c_edge, 1.0f);
-  if (rc == XRT_OK && index_offset) *index_offset = 0;
-  return rc;
+  return copy_mesh(s, m, s->c_pos, s->c_invm, s->c_tri, s->c_edge, 1.0f, index_offset);
 }
 
 extern "C" int xrt_add_obstacle(xrt_solver* s, const xrt_mesh_desc* m, int32_t* index_offset) {
   if (!s) return XRT_ERR_INVALID;
   XRT_REQUIRE(!s->finalized, "add_obstacle after finalize_setup");
-  XRT_REQUIRE(s->o_pos.empty(), "one obstacle mesh per handle (merge meshes on the caller side)");
-  int rc = copy_mesh(s, m, s->o_pos, s->o_invm, s->o_tri, s->o_edge, 1.0f / 1e3f);  // PhysicsMeshHelper.cu:139
-  if (rc == XRT_OK && index_offset) *index_offset = 0;
-  return rc;
+  return copy_mesh(s, m, s->o_pos, s->o_invm, s->o_tri, s->o_edge, 1.0f / 1e3f, index_offset);  // PhysicsMeshHelper.cu:139
 }
 
 extern "C" int xrt_set_stretch(xrt_solver* s, const uint32_t* idx01, const float* rest, size_t n) {
   if (!s) return XRT_ERR_INVALID;
   XRT_REQUIRE(!s->finalized, "set_stretch after finalize_setup");
   XRT_REQUIRE(n == 0 || (idx01 && rest), "set_stretch: null array");
-  s->s_idx.assign(idx01, idx01 + 2 * n);
-  s->s_rest.assign(rest, rest + n);
+  s->s_idx.insert(s->s_idx.end(), idx01, idx01 + 2 * n);  // one call per garment, indices already in the merged numbering
+  s->s_rest.insert(s->s_rest.end(), rest, rest + n);
   s->s_color_set = false;
   return XRT_OK;
 }
@@ -129,8 +130,8 @@ extern "C" int xrt_set_bend(xrt_solver* s, const uint32_t* idx0123, const float*
   if (!s) return XRT_ERR_INVALID;
   XRT_REQUIRE(!s->finalized, "set_bend after finalize_setup");
   XRT_REQUIRE(n == 0 || (idx0123 && theta), "set_bend: null array");
-  s->b_idx.assign(idx0123, idx0123 + 4 * n);
-  s->b_theta.assign(theta, theta + n);
+  s->b_idx.insert(s->b_idx.end(), idx0123, idx0123 + 4 * n);
+  s->b_theta.insert(s->b_theta.end(), theta, theta + n);
   s->b_color_set = false;
   return XRT_OK;
 }
