@@ -5,12 +5,14 @@
  * bench.py's cpu_baseline / --impl reference legs as the checker; the product
  * (xrtailor_b200/) never links or calls it.
  *
- * Parity status: the reference (openxrlab/xrtailor @ 4eaf5c3) has no tests,
- * golden vectors or CPU path, so this restatement is
- * pinned against (a) the reference's own __host__ __device__ helpers compiled
- * for the host from /root/reference (oracle/_ref, see oracle/Makefile) and
- * (b) hand-derived known answers in tests/golden/.  Float position parity
- * against the reference's CUDA itself can only run on a GPU box.
+ * Parity status: pinned.  The reference (openxrlab/xrtailor @ 4eaf5c3) has no tests, golden vectors or CPU path
+ * (SURVEY.md section 4); this restatement is pinned against the reference's own CUDA physics, compiled from
+ * /root/reference by oracle/ref_harness/Makefile into oracle/_ref/libxrt_ref.so and run on the GPU box:
+ * (a) live, in tests/test_ref_parity_gpu.py and tests/test_quality_gpu.py (BVH bit for bit, pair lists row for
+ * row, contacts index for index, impacts, positions to the north star's tolerances), and (b) offline, through the
+ * fixtures under tests/golden/ that scratch/r02_quality_ref.py wrote from the reference's outputs on that box
+ * (tests/test_oracle_cpu.py::test_quality_oracle_against_golden_reference_outputs runs here, without a GPU).
+ * Brute-force numpy restatements and hand-derived known answers (tests/test_oracle_cpu.py) cover the rest.
  *
  * Every function cites the reference file:line it follows (paths relative to
  * /root/reference/xrtailor/).  Plain C, scalar, one thread, IEEE arithmetic

@@ -385,3 +385,84 @@ def test_fem_bending_flattens_a_fold():
     far = np.abs(pos[:, 0] - pos[:, 0].mean()) > 0.15
     move = np.linalg.norm(one - x, axis=1)
     assert move[far].max() < 0.1 * move[~far].max(), (move[far].max(), move[~far].max())
+
+
+# ---- Quality mode (oracle/xrt_oracle_quality.c) ----
+
+def _quality_oracle(sc, N=20):
+    import types
+    q = types.SimpleNamespace(xx_stiffness=1.0, yy_stiffness=1.0, xy_stiffness=1.0, xy_poisson_ratio=0.3,
+                              yx_poisson_ratio=0.3, bending_stiffness=1e-2, enable_imminent_repulsion=1,
+                              imminent_thickness=1e-3, enable_pbd_repulsion=1, pbd_thickness=1e-4, relaxation_rate=0.75,
+                              obstacle_mass=1e3, impact_zone_thickness=1e-4)
+    p = X.default_params()
+    p.num_substeps, p.num_iterations, p.enable_self_collision = 1, N, 0
+    p.particle_diameter = sc.particle_diameter()
+    cs, _ = X.greedy_color(sc.stretch_idx, len(sc.cloth_pos))
+    cb, _ = X.greedy_color(sc.bend_idx, len(sc.cloth_pos))
+    cf, _ = X.greedy_color(sc.cloth_tri, len(sc.cloth_pos))
+    o = O.Scene(sc, p, (cs, cb))
+    o.set_quality(sc, q, cf)
+    return o, q
+
+
+def test_solve_cubic_and_check_impact_known_answers():
+    """MathFunctions::SolveCubic (MathFunctions.cu:122-146) on cubics with known roots, and the continuous vertex-face
+    test (ImpactHelper.cu:34-87) on a vertex falling through the middle of a static triangle."""
+    r = sorted(O.solve_cubic(1.0, -6.0, 11.0, -6.0))            # (t - 1)(t - 2)(t - 3)
+    np.testing.assert_allclose(r, [1, 2, 3], atol=1e-4)
+    r = O.solve_cubic(1.0, 0.0, 1.0, -2.0)                      # t^3 + t - 2: one real root, t = 1
+    assert len(r) == 1 and abs(r[0] - 1.0) < 1e-5
+    r = sorted(O.solve_cubic(0.0, 1.0, -3.0, 2.0))              # degenerates to (t - 1)(t - 2)
+    np.testing.assert_allclose(r, [1, 2], atol=1e-5)
+    # a scene of one triangle pair is enough to drive FindImpacts: vertex 3 of the cloth falls through face (0, 1, 2)
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0.25, 0.25, 0.5], [2, 2, 0.5], [2, 3, 0.5]], np.float32)
+    tri = np.array([[0, 1, 2], [3, 4, 5]], np.uint32)
+    sc = scene.Scene(pos, tri, None, None)
+    o, q = _quality_oracle(sc)
+    x1 = pos.copy()
+    x1[3:, 2] -= 1.0                                             # the second triangle moves 1 m down in the step
+    o.set_state(pos, np.zeros_like(pos))
+    o.set_predicted(x1)
+    nodes, twn, npairs = o.find_impacts(1e-4)
+    vf = [(n, t) for n, t in zip(nodes, twn) if t[8] > 0.5 and n[0] == 3]
+    assert vf, (nodes, twn)
+    n, t = vf[0]
+    assert sorted(n[1:]) == [0, 1, 2]
+    assert abs(t[0] - 0.5) < 1e-5                                # reaches z = 0 at half the step
+    np.testing.assert_allclose(sorted(-t[2:5]), sorted([0.5, 0.25, 0.25]), atol=1e-5)   # barycentric weights
+    assert abs(abs(t[7]) - 1.0) < 1e-5                           # normal along z
+
+
+def test_quality_oracle_against_golden_reference_outputs():
+    """tests/golden/quality_*_s16.npz hold what the REFERENCE's own CUDA returned on a B200 for a two-sheet scene
+    (scratch/r02_quality_ref.py wrote them from oracle/_ref through the harness): FindImpacts rows, the
+    independentImpacts selection, and the positions after CollisionStep.  The CPU oracle must reproduce them here."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "quality_impacts_s16.npz"))
+    sc = scene.layered_scene(16, 2, gap=4e-3, sphere=(8, 16))
+    np.testing.assert_array_equal(sc.cloth_pos, g["cloth_pos"])  # the generator still makes the scene of the fixture
+    np.testing.assert_array_equal(sc.cloth_tri, g["cloth_tri"])
+    o, q = _quality_oracle(sc)
+    o.set_state(g["x0"], g["v"])
+    o.set_predicted(g["x1"])
+    nodes, twn, npairs = o.find_impacts(float(g["thickness"]))
+    assert npairs == int(g["ref_pairs"]) == 29608
+    rn, rt = g["ref_nodes"], g["ref_twn"]
+    assert len(nodes) == len(rn) == 19260
+    np.testing.assert_array_equal(nodes, rn)                      # the reference's rows, in the reference's order
+    np.testing.assert_array_equal(twn[:, 8], rt[:, 8])
+    assert np.abs(twn[:, 0] - rt[:, 0]).max() <= 5e-5 and np.median(np.abs(twn[:, 0] - rt[:, 0])) <= 1e-6
+    inn, itw = o.independent_impacts(rn, rt, 0)
+    np.testing.assert_array_equal(inn, g["ref_ind_nodes"])       # 102 impacts, none sharing a movable node
+    np.testing.assert_array_equal(itw[:, 0], g["ref_ind_twn"][:, 0])
+    assert len(inn) == 102
+    # CollisionStep from that state: every impact resolved, within 1e-3 m RMS of the reference's result
+    o.collision_step()
+    st = o.collision_stats()
+    assert st["success"] == 1
+    gs = np.load(os.path.join(os.path.dirname(__file__), "golden", "quality_step_s16.npz"))
+    d = np.sqrt(((o.predicted() - gs["ref_x"]) ** 2).sum(1))
+    assert np.sqrt((d ** 2).mean()) <= 1e-3
+    left, _, _ = o.find_impacts(float(g["thickness"]))
+    assert len(left) == 0
