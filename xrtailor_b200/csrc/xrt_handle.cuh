@@ -120,6 +120,11 @@ void xrt_color_ranges(const std::vector<uint32_t>& idx, int arity, const std::ve
 void xrt_build_vf(const std::vector<uint32_t>& tri, uint32_t V, std::vector<uint32_t>& off, std::vector<uint32_t>& idx);
 void xrt_build_rtri(const std::vector<uint32_t>& tri, const std::vector<uint32_t>& vf_off,
                     const std::vector<uint32_t>& vf_idx, std::vector<uint32_t>& rtri);
+// frame path pieces of xrt_api.cu that the batch code (xrt_batch.cu) shares
+PersistArgs xrt_make_persist_args(const xrt_solver* s, int substep, bool moved, bool do_predict);
+int xrt_take_sequence_frame(xrt_solver* s, cudaStream_t st);
+double xrt_frame_bytes(const xrt_solver* s, bool moved);  // algorithmic bytes of one frame, SURVEY 8(d)
+double xrt_bvh_build_bytes(const xrt_solver* s);
 // Quality mode (xrt_quality.cu)
 int xrt_quality_finalize(xrt_solver* s);           // called by xrt_finalize_setup when xrt_set_quality was called
 int xrt_quality_step_frame(xrt_solver* s, float* solver_ms);  // ClothSolverBase::SimulateQuality

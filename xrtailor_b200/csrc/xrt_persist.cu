@@ -449,9 +449,19 @@ __global__ void __launch_bounds__(PT, 1) swift_segment_kernel(const __grid_const
 
 }  // namespace
 
+// per-device caches: the non-portable cluster opt-in and the occupancy answers belong to the current device
+static int current_device_slot() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return dev >= 0 && dev < 64 ? dev : 0;
+}
+
 int persist_max_cluster() {
-  static int cached = -1;
-  if (cached >= 0) return cached;
+  static int cache[64];
+  static bool have[64] = {false};
+  const int slot = current_device_slot();
+  if (have[slot]) return cache[slot];
+  int& cached = cache[slot];
   // clusters above 8 CTAs need the non-portable opt-in
   cudaFuncSetAttribute(swift_substep_kernel<SYNC_CLUSTER>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
   cudaFuncSetAttribute(swift_substep_batch_kernel<SYNC_CLUSTER>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
@@ -472,6 +482,7 @@ int persist_max_cluster() {
   }
   (void)cudaGetLastError();
   cached = best;
+  have[slot] = true;
   return cached;
 }
 
@@ -502,13 +513,17 @@ int persist_active_clusters(int cluster) {
 }
 
 int persist_grid_ctas() {
-  static int cached = -1;
-  if (cached >= 0) return cached;
+  static int cache[64];
+  static bool have[64] = {false};
+  const int slot = current_device_slot();
+  if (have[slot]) return cache[slot];
+  int& cached = cache[slot];
   int dev = 0, sms = 0, per_sm = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, swift_substep_kernel<SYNC_GRID>, PT, 0);
   cached = per_sm > 0 ? sms : 0;  // one CTA per SM, all co-resident
+  have[slot] = true;
   return cached;
 }
 
@@ -553,11 +568,12 @@ int persist_dsmem_shift(uint32_t V) {
 }
 
 cudaError_t launch_swift_segment(const PersistArgs& a, cudaStream_t st) {
-  static bool once = false;
-  if (!once) {
+  static bool once[64] = {false};
+  const int slot = current_device_slot();
+  if (!once[slot]) {
     cudaFuncSetAttribute(swift_segment_kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
     cudaFuncSetAttribute(swift_segment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (16 << XRT_DSMEM_MAX_SHIFT));
-    once = true;
+    once[slot] = true;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(XRT_DSMEM_CLUSTER);
