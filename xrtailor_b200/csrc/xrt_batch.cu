@@ -25,6 +25,14 @@ struct BatchGroup {
   cudaEvent_t ev_snap = nullptr;
   PersistArgs* d_table = nullptr;  // [S][2][n]
   int *d_moved = nullptr, *h_moved = nullptr;
+  // the per-garment stages between two shared launches as ONE launch per stage over the whole group (blockIdx.y =
+  // garment): obstacle BVH builds, predict + spatial hash, end-of-frame copy + normals.  Used when every garment of
+  // the group hashes on the same substeps (`uniform`); otherwise the per-garment graphs on the worker streams.
+  bool uniform = false;
+  BvhBatch bb;
+  HashBatch hb;
+  NormalsBatchItem* d_post = nullptr;
+  uint32_t n_post = 0, post_max_v = 0;
 };
 // Garments are split into `groups` that step independently (own stream, own shared launches):
 // while one group's substep kernel holds its SMs, another group's builds and hashes run.
@@ -73,6 +81,9 @@ extern "C" void xrt_batch_destroy(xrt_batch* b) {
       if (e) cudaEventDestroy(e);
     cudaFree(g.d_table);
     cudaFree(g.d_moved);
+    bvh_batch_free(&g.bb);
+    hash_batch_free(&g.hb);
+    cudaFree(g.d_post);
     cudaFreeHost(g.h_moved);
     if (g.st) cudaStreamDestroy(g.st);
   }
@@ -138,6 +149,45 @@ extern "C" int xrt_batch_create(xrt_solver** handles, int n, int groups, int wor
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.ev_fork, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.ev_flags, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&g.ev_done, cudaEventDisableTiming);
+    // group-wide stages
+    if (e == cudaSuccess) {
+      const xrt_solver* h0 = handles[g.first];
+      g.uniform = true;
+      std::vector<BvhBatchItem> bi;
+      std::vector<HashBatchItem> hi;
+      std::vector<NormalsBatchItem> ni;
+      for (int i = 0; i < g.n; i++) {
+        xrt_solver* h = handles[g.first + i];
+        if (h->p.enable_self_collision != h0->p.enable_self_collision || h->p.inter_leaved_hash != h0->p.inter_leaved_hash ||
+            h->p.morton_fast_div != h0->p.morton_fast_div)
+          g.uniform = false;
+        BvhBatchItem b1{};
+        b1.b = h->bvh; b1.w = h->bw; b1.x = h->o.x0; b1.tri = h->o.tri; b1.F = h->o.F;
+        bi.push_back(b1);
+        HashBatchItem h1{};
+        h1.c = h->c; h1.k = h->k;
+        hi.push_back(h1);
+        if (h->o.V) ni.push_back(NormalsBatchItem{h->o.x0, h->o.x, h->o.n, h->o.tri, h->o.vf_off, h->o.vf_idx, h->o.V, (uint32_t)i});
+        ni.push_back(NormalsBatchItem{h->c.x0, nullptr, h->c.n, h->c.tri, h->c.vf_off, h->c.vf_idx, h->c.V, (uint32_t)i});
+        g.post_max_v = std::max(g.post_max_v, std::max(h->o.V, h->c.V));
+      }
+      if (g.uniform) {
+        if (bvh_batch_alloc(&g.bb, bi) || hash_batch_alloc(&g.hb, hi)) e = cudaErrorMemoryAllocation;
+        g.n_post = (uint32_t)ni.size();
+        if (e == cudaSuccess) e = cudaMalloc((void**)&g.d_post, ni.size() * sizeof(NormalsBatchItem));
+        if (e == cudaSuccess) e = cudaMemcpy(g.d_post, ni.data(), ni.size() * sizeof(NormalsBatchItem), cudaMemcpyHostToDevice);
+        // the sorted keys of a tree now live in the group's buffers (what the BVH getters read)
+        uint32_t seg = 0;
+        for (int i = 0; i < g.n && e == cudaSuccess; i++) {
+          xrt_solver* h = handles[g.first + i];
+          if (h->o.F) {
+            h->bvh.morton = g.bb.key_out + seg;
+            h->bvh.sorted_obj = g.bb.val_out + seg;
+          }
+          seg += h->o.F;
+        }
+      }
+    }
   }
   if (e != cudaSuccess) {
     xrt_set_error(s, "batch_create: %s", cudaGetErrorString(e));
@@ -302,6 +352,31 @@ static int batch_enqueue_frame(xrt_batch* b) {
     for (BatchGroup& g : b->g) {
       gr.assign(g.n, nullptr);
       bool any = sub == 0 || sub == b->S;
+      if (g.uniform) {
+        const xrt_solver* h0 = b->h[g.first];
+        const bool hash = sub < b->S && h0->p.enable_self_collision && sub % std::max(1, h0->p.inter_leaved_hash) == 0;
+        bool build = false;
+        if (sub == 0)
+          for (int i = 0; i < g.n; i++) build = build || (g.h_moved[i] && b->h[g.first + i]->o.F);
+        if (!(hash || build || sub == b->S)) continue;  // this substep joins the running segment
+        if (sub > g.seg_begin)
+          XRT_CUDA_OK(launch_swift_substep_batch(g.d_table, g.d_moved, (uint32_t)g.n, g.seg_begin, sub, b->cluster, g.st));
+        g.seg_begin = sub;
+        if (build) bvh_build_batched(g.bb, g.d_moved, h0->p.morton_fast_div, g.st);
+        if (hash) launch_predict_hash_batched(g.hb, g.st);
+        if (sub == b->S) {
+          launch_post_batched(g.d_post, g.n_post, g.post_max_v, g.d_moved, g.st);
+          if (b->readback)
+            if (int rc = batch_snapshot(b, g)) return rc;
+          XRT_CUDA_OK(cudaEventRecord(g.ev_done, g.st));
+          for (int i = 0; i < g.n; i++) {
+            b->h[g.first + i]->target_pending = false;
+            b->h[g.first + i]->batch_ev = g.ev_done;
+          }
+        }
+        XRT_CUDA_OK(cudaGetLastError());
+        continue;
+      }
       for (int i = 0; i < g.n; i++) {
         xrt_solver* h = b->h[g.first + i];
         const int rc = sub < b->S ? batch_pre_graph(h, sub, g.h_moved[i], &gr[i]) : batch_post_graph(h, g.h_moved[i], &gr[i]);
@@ -468,11 +543,24 @@ extern "C" int xrt_batch_launches_per_frame(xrt_batch* b, int moved, uint32_t* o
       }
       n += any ? 1u : 0u;
     }
-  for (const xrt_solver* h : b->h) {
-    if (moved && h->o.F) n += (uint32_t)bvh_build_launches();
-    for (int sub = 0; sub < b->S; sub++)
-      if (h->p.enable_self_collision && sub % std::max(1, h->p.inter_leaved_hash) == 0) n += 6;  // predict + hash
-    n += h->o.V ? 2 : 1;  // end-of-frame normals
+  for (const BatchGroup& g : b->g) {
+    if (g.uniform) {  // group-wide stages: one launch per stage whatever the number of garments
+      const xrt_solver* h0 = b->h[g.first];
+      bool obstacle = false;
+      for (int i = 0; i < g.n; i++) obstacle = obstacle || b->h[g.first + i]->o.F;
+      if (moved && obstacle) n += (uint32_t)bvh_build_launches();
+      for (int sub = 0; sub < b->S; sub++)
+        if (h0->p.enable_self_collision && sub % std::max(1, h0->p.inter_leaved_hash) == 0) n += 5;  // predict+hash, sort (1), clear, ranges, neighbours
+      n += 2;  // end of frame: copy, normals
+      continue;
+    }
+    for (int i = 0; i < g.n; i++) {
+      const xrt_solver* h = b->h[g.first + i];
+      if (moved && h->o.F) n += (uint32_t)bvh_build_launches();
+      for (int sub = 0; sub < b->S; sub++)
+        if (h->p.enable_self_collision && sub % std::max(1, h->p.inter_leaved_hash) == 0) n += 6;  // predict + hash
+      n += h->o.V ? 2 : 1;  // end-of-frame normals
+    }
   }
   *out = n;
   return XRT_OK;

@@ -8,6 +8,9 @@
 #include "xrt_bvh.cuh"
 #include "xrt_dev_bvh.cuh"
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_segmented_radix_sort.cuh>
+#include <algorithm>
+#include <vector>
 
 namespace {
 using namespace xrtdev;
@@ -19,17 +22,17 @@ __device__ __forceinline__ int f2ord(float f) {
 }
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7FFFFFFF); }
 
-__global__ void scene_init_kernel(int* scene) {
+__device__ __forceinline__ void scene_init_body(int* scene) {
   if (threadIdx.x < 3) scene[threadIdx.x] = f2ord(INFINITY);
   else if (threadIdx.x < 6) scene[threadIdx.x] = f2ord(-INFINITY);
 }
+__global__ void scene_init_kernel(int* scene) { scene_init_body(scene); }
 
 // UpdateObjects_Kernel + InitAABBs_Kernel + thrust::reduce (BVH.cu:382-462,642)
 // in one pass over the faces.
-__global__ void leaf_box_kernel(const float4* __restrict__ x, const float4* __restrict__ xp,
-                                const uint32_t* __restrict__ tri, float4* __restrict__ pred,
-                                float* __restrict__ leaf_box, int* __restrict__ scene, uint32_t F) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void leaf_box_body(const float4* __restrict__ x, const float4* __restrict__ xp,
+                                              const uint32_t* __restrict__ tri, float4* __restrict__ pred,
+                                              float* __restrict__ leaf_box, int* __restrict__ scene, uint32_t F, uint32_t i) {
   float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
   if (i < F) {
     const uint32_t i0 = tri[3 * i], i1 = tri[3 * i + 1], i2 = tri[3 * i + 2];
@@ -71,6 +74,11 @@ __global__ void leaf_box_kernel(const float4* __restrict__ x, const float4* __re
     }
   }
 }
+__global__ void leaf_box_kernel(const float4* __restrict__ x, const float4* __restrict__ xp,
+                                const uint32_t* __restrict__ tri, float4* __restrict__ pred,
+                                float* __restrict__ leaf_box, int* __restrict__ scene, uint32_t F) {
+  leaf_box_body(x, xp, tri, pred, leaf_box, scene, F, blockIdx.x * blockDim.x + threadIdx.x);
+}
 
 __device__ __forceinline__ uint32_t expand_bits10(uint32_t v) {  // BVH.cu:18-24
   v = (v * 0x00010001u) & 0xFF0000FFu;
@@ -88,9 +96,8 @@ __device__ __forceinline__ uint32_t quant10(float t) {
 
 // ComputeMortons_Kernel + InitObjectIndices_Kernel (BVH.cu:464-487)
 template <bool FAST_DIV>
-__global__ void morton_kernel(const float* __restrict__ leaf_box, const int* __restrict__ scene,
-                              uint32_t* __restrict__ key, uint32_t* __restrict__ val, uint32_t F) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void morton_body(const float* __restrict__ leaf_box, const int* __restrict__ scene,
+                                            uint32_t* __restrict__ key, uint32_t* __restrict__ val, uint32_t F, uint32_t i) {
   if (i >= F) return;
   const float* b = leaf_box + 6 * (size_t)i;
   float wl[3] = {ord2f(scene[0]), ord2f(scene[1]), ord2f(scene[2])};
@@ -107,6 +114,11 @@ __global__ void morton_kernel(const float* __restrict__ leaf_box, const int* __r
   key[i] = expand_bits10(q[0]) * 4 + expand_bits10(q[1]) * 2 + expand_bits10(q[2]);
   val[i] = i;
 }
+template <bool FAST_DIV>
+__global__ void morton_kernel(const float* __restrict__ leaf_box, const int* __restrict__ scene,
+                              uint32_t* __restrict__ key, uint32_t* __restrict__ val, uint32_t F) {
+  morton_body<FAST_DIV>(leaf_box, scene, key, val, F, blockIdx.x * blockDim.x + threadIdx.x);
+}
 
 // common_upper_bits on the reference's 64-bit key (morton << 32 | object),
 // evaluated from the two halves.  For distinct Morton codes it equals the
@@ -117,9 +129,8 @@ __device__ __forceinline__ int delta_pair(uint32_t m0, uint32_t o0, uint32_t m1,
 }
 
 // ConstructLeafNodes_Kernel + ConstructInternalNodes64Bits_Kernel (BVH.cu:297-318,489-500)
-__global__ void karras_kernel(const uint32_t* __restrict__ morton, const uint32_t* __restrict__ obj,
-                              BVNode* __restrict__ nodes, int2* __restrict__ ranges, uint32_t F) {
-  uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void karras_body(const uint32_t* __restrict__ morton, const uint32_t* __restrict__ obj,
+                                            BVNode* __restrict__ nodes, int2* __restrict__ ranges, uint32_t F, uint32_t tid) {
   if (tid >= F) return;
   const int n = (int)F;
   // leaf tid
@@ -170,16 +181,24 @@ __global__ void karras_kernel(const uint32_t* __restrict__ morton, const uint32_
   nodes[R].parent = idx;
   ranges[idx] = make_int2(first, last);
 }
+__global__ void karras_kernel(const uint32_t* __restrict__ morton, const uint32_t* __restrict__ obj,
+                              BVNode* __restrict__ nodes, int2* __restrict__ ranges, uint32_t F) {
+  karras_body(morton, obj, nodes, ranges, F, blockIdx.x * blockDim.x + threadIdx.x);
+}
 
-__global__ void build_boxes_kernel(TNode* tn, const BVNode* __restrict__ nodes,
-                                   const float* __restrict__ leaf_box,
-                                   const uint32_t* __restrict__ obj, int* flags, uint32_t F) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void build_boxes_body(TNode* tn, const BVNode* __restrict__ nodes,
+                                                 const float* __restrict__ leaf_box,
+                                                 const uint32_t* __restrict__ obj, int* flags, uint32_t F, uint32_t i) {
   if (i >= F) return;
   const float* b = leaf_box + 6 * (size_t)obj[i];
   float lo[3] = {b[0], b[1], b[2]}, hi[3] = {b[3], b[4], b[5]};
   tnode_store_box(tn + tnode_slot(nodes, F - 1 + i), lo, hi);
   walk_up<false>(tn, nodes, flags, F - 1 + i);
+}
+__global__ void build_boxes_kernel(TNode* tn, const BVNode* __restrict__ nodes,
+                                   const float* __restrict__ leaf_box,
+                                   const uint32_t* __restrict__ obj, int* flags, uint32_t F) {
+  build_boxes_body(tn, nodes, leaf_box, obj, flags, F, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // Escape links in O(1) from the Karras ranges: the subtree that follows a
@@ -193,9 +212,8 @@ __device__ __forceinline__ int escape_after(int last, const int2* ranges, int n)
   return n - 1 + k;
 }
 
-__global__ void link_kernel(TNode* tn, const BVNode* __restrict__ nodes, const int2* __restrict__ ranges,
-                            int32_t* __restrict__ esc_int, int32_t* __restrict__ esc_ext, uint32_t F) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+__device__ __forceinline__ void link_body(TNode* tn, const BVNode* __restrict__ nodes, const int2* __restrict__ ranges,
+                                          int32_t* __restrict__ esc_int, int32_t* __restrict__ esc_ext, uint32_t F, uint32_t i) {
   const int n = (int)F;
   if (i >= 2 * F - 1) return;
   TNode* me = tn + tnode_slot(nodes, i);
@@ -211,6 +229,51 @@ __global__ void link_kernel(TNode* tn, const BVNode* __restrict__ nodes, const i
     me->link_hit = ~(int)nodes[i].object;
     me->link_miss = e < 0 ? -1 : (int)tnode_slot(nodes, (uint32_t)e);
   }
+}
+__global__ void link_kernel(TNode* tn, const BVNode* __restrict__ nodes, const int2* __restrict__ ranges,
+                            int32_t* __restrict__ esc_int, int32_t* __restrict__ esc_ext, uint32_t F) {
+  link_body(tn, nodes, ranges, esc_int, esc_ext, F, blockIdx.x * blockDim.x + threadIdx.x);
+}
+
+// ---- the same seven stages for a whole batch of trees: blockIdx.y = tree, one launch per stage ----
+// (a shared-launch batch rebuilds 148 obstacle trees per frame; as 148 x 7 launches of less than one wave each they
+// took 10 % of the frame).  Trees whose `moved` flag is 0 keep last frame's tree.
+__global__ void batch_stage0_kernel(const BvhBatchItem* __restrict__ items, const int* __restrict__ moved) {
+  const BvhBatchItem& it = items[blockIdx.y];
+  if ((moved && !moved[blockIdx.y]) || !it.F) return;
+  if (blockIdx.x == 0) scene_init_body(it.w.scene);
+  // arrival counters of the bottom-up box pass
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < it.F; i += gridDim.x * blockDim.x) it.w.flags[i] = 0;
+}
+__global__ void batch_leaf_box_kernel(const BvhBatchItem* __restrict__ items, const int* __restrict__ moved) {
+  const BvhBatchItem& it = items[blockIdx.y];
+  if (moved && !moved[blockIdx.y]) return;
+  if (blockIdx.x * blockDim.x >= it.F) return;
+  leaf_box_body(it.x, nullptr, it.tri, it.b.pred, it.w.leaf_box, it.w.scene, it.F, blockIdx.x * blockDim.x + threadIdx.x);
+}
+template <bool FAST_DIV>
+__global__ void batch_morton_kernel(const BvhBatchItem* __restrict__ items, const int* __restrict__ moved,
+                                    uint32_t* __restrict__ key, uint32_t* __restrict__ val) {
+  const BvhBatchItem& it = items[blockIdx.y];
+  if (moved && !moved[blockIdx.y]) return;
+  morton_body<FAST_DIV>(it.w.leaf_box, it.w.scene, key + it.seg, val + it.seg, it.F, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__global__ void batch_karras_kernel(const BvhBatchItem* __restrict__ items, const int* __restrict__ moved,
+                                    const uint32_t* __restrict__ key, const uint32_t* __restrict__ val) {
+  const BvhBatchItem& it = items[blockIdx.y];
+  if (moved && !moved[blockIdx.y]) return;
+  karras_body(key + it.seg, val + it.seg, it.b.nodes, it.w.ranges, it.F, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__global__ void batch_boxes_kernel(const BvhBatchItem* __restrict__ items, const int* __restrict__ moved,
+                                   const uint32_t* __restrict__ val) {
+  const BvhBatchItem& it = items[blockIdx.y];
+  if (moved && !moved[blockIdx.y]) return;
+  build_boxes_body(it.b.tnodes, it.b.nodes, it.w.leaf_box, val + it.seg, it.w.flags, it.F, blockIdx.x * blockDim.x + threadIdx.x);
+}
+__global__ void batch_link_kernel(const BvhBatchItem* __restrict__ items, const int* __restrict__ moved) {
+  const BvhBatchItem& it = items[blockIdx.y];
+  if (moved && !moved[blockIdx.y]) return;
+  link_body(it.b.tnodes, it.b.nodes, it.w.ranges, it.b.esc_int, it.b.esc_ext, it.F, blockIdx.x * blockDim.x + threadIdx.x);
 }
 
 // RefitMidstep, one kernel (body in xrt_dev_bvh.cuh)
@@ -294,6 +357,58 @@ void bvh_free(DevBVH* b, BvhWork* w) {
 
 int bvh_build_launches() { return 7; }   // scene_init, leaf_box, morton, sort(~2: histogram+onesweep counted as 2), karras, boxes, link  (memset excluded)
 int bvh_refit_launches() { return 1; }
+
+int bvh_batch_alloc(BvhBatch* bb, const std::vector<BvhBatchItem>& items) {
+  bb->n = (uint32_t)items.size();
+  bb->total = 0;
+  bb->max_f = 0;
+  std::vector<BvhBatchItem> h = items;
+  std::vector<uint32_t> off(items.size() + 1, 0);
+  for (size_t i = 0; i < h.size(); i++) {
+    h[i].seg = bb->total;
+    off[i] = bb->total;
+    bb->total += h[i].F;
+    bb->max_f = std::max(bb->max_f, h[i].F);
+  }
+  off[h.size()] = bb->total;
+  cudaError_t e = cudaSuccess;
+  auto A = [&](void** p, size_t bytes) {
+    if (e == cudaSuccess) e = cudaMalloc(p, bytes ? bytes : 16);
+  };
+  A((void**)&bb->items, h.size() * sizeof(BvhBatchItem));
+  A((void**)&bb->seg_off, off.size() * 4);
+  A((void**)&bb->key_in, (size_t)bb->total * 4); A((void**)&bb->val_in, (size_t)bb->total * 4);
+  A((void**)&bb->key_out, (size_t)bb->total * 4); A((void**)&bb->val_out, (size_t)bb->total * 4);
+  if (e != cudaSuccess) return (int)e;
+  cudaMemcpy(bb->items, h.data(), h.size() * sizeof(BvhBatchItem), cudaMemcpyHostToDevice);
+  cudaMemcpy(bb->seg_off, off.data(), off.size() * 4, cudaMemcpyHostToDevice);
+  bb->cub_bytes = 0;
+  e = cub::DeviceSegmentedRadixSort::SortPairs(nullptr, bb->cub_bytes, bb->key_in, bb->key_out, bb->val_in, bb->val_out, (int)bb->total,
+                                               (int)bb->n, bb->seg_off, bb->seg_off + 1, 0, 30);
+  A(&bb->cub_tmp, bb->cub_bytes);
+  return (int)e;
+}
+void bvh_batch_free(BvhBatch* bb) {
+  cudaFree(bb->items); cudaFree(bb->seg_off); cudaFree(bb->key_in); cudaFree(bb->val_in); cudaFree(bb->key_out);
+  cudaFree(bb->val_out); cudaFree(bb->cub_tmp);
+  *bb = BvhBatch{};
+}
+// bvh_build of every tree of the batch in seven launches (the segmented sort is cub's, like the per-tree sort)
+void bvh_build_batched(const BvhBatch& bb, const int* d_moved, int fast_div, cudaStream_t st) {
+  if (!bb.n || !bb.total) return;
+  const dim3 g(xrt_grid(bb.max_f), bb.n), g2(xrt_grid(2 * (size_t)bb.max_f), bb.n);
+  batch_stage0_kernel<<<dim3(std::min<unsigned>(g.x, 8u), bb.n), XRT_BLOCK, 0, st>>>(bb.items, d_moved);
+  batch_leaf_box_kernel<<<g, XRT_BLOCK, 0, st>>>(bb.items, d_moved);
+  if (fast_div) batch_morton_kernel<true><<<g, XRT_BLOCK, 0, st>>>(bb.items, d_moved, bb.key_in, bb.val_in);
+  else batch_morton_kernel<false><<<g, XRT_BLOCK, 0, st>>>(bb.items, d_moved, bb.key_in, bb.val_in);
+  size_t bytes = bb.cub_bytes;
+  // a tree that did not move re-sorts last frame's keys (key_in is kept): same order, its other stages are skipped
+  cub::DeviceSegmentedRadixSort::SortPairs(bb.cub_tmp, bytes, bb.key_in, bb.key_out, bb.val_in, bb.val_out, (int)bb.total, (int)bb.n,
+                                           bb.seg_off, bb.seg_off + 1, 0, 30, st);
+  batch_karras_kernel<<<g, XRT_BLOCK, 0, st>>>(bb.items, d_moved, bb.key_out, bb.val_out);
+  batch_boxes_kernel<<<g, XRT_BLOCK, 0, st>>>(bb.items, d_moved, bb.val_out);
+  batch_link_kernel<<<g2, XRT_BLOCK, 0, st>>>(bb.items, d_moved);
+}
 
 void bvh_build(const DevBVH& b_, const BvhWork& w, const float4* x, const uint32_t* tri, uint32_t F,
                int fast_div, cudaStream_t st) {

@@ -40,6 +40,31 @@ void bvh_refit_midstep(const DevBVH& b, const BvhWork& w, const float4* x1, cons
 int bvh_build_launches();
 int bvh_refit_launches();
 
+// ---- batched build (shared-launch batches): every tree of a group in seven launches ----
+struct BvhBatchItem {
+  DevBVH b;
+  BvhWork w;
+  const float4* x;      // vertex positions the tree is built on (obstacle x0)
+  const uint32_t* tri;
+  uint32_t F;
+  uint32_t seg;         // where this tree's keys start in the batch's key / value buffers
+};
+struct BvhBatch {
+  uint32_t n = 0, total = 0, max_f = 0;
+  BvhBatchItem* items = nullptr;   // device
+  uint32_t* seg_off = nullptr;     // device [n + 1]
+  uint32_t *key_in = nullptr, *val_in = nullptr, *key_out = nullptr, *val_out = nullptr;  // [total]
+  void* cub_tmp = nullptr;
+  size_t cub_bytes = 0;
+};
+#ifdef __cplusplus
+#include <vector>
+int bvh_batch_alloc(BvhBatch* bb, const std::vector<BvhBatchItem>& items);
+#endif
+void bvh_batch_free(BvhBatch* bb);
+// d_moved: device int[n] or nullptr (all); trees with moved == 0 are left as they are
+void bvh_build_batched(const BvhBatch& bb, const int* d_moved, int fast_div, cudaStream_t st);
+
 // ---- face-face pair lists (xrt_pairs.cu): BVH::Traverse / TraverseSelf (BVH.cu:1149-1400) on preallocated scratch ----
 struct PairWork {
   uint32_t cap = 0;  // left faces this scratch was sized for

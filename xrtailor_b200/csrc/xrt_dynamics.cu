@@ -54,6 +54,18 @@ __global__ void normals_kernel(const float4* __restrict__ x, float4* __restrict_
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < V) normals_item(x, n, tri, vf_off, vf_idx, i);
 }
+// end-of-frame work of a whole batch (blockIdx.y = mesh): PredictedToPositions, then vertex normals
+__global__ void batch_copy_kernel(const NormalsBatchItem* __restrict__ items, const int* __restrict__ moved) {
+  const NormalsBatchItem& it = items[blockIdx.y];
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (!it.copy_src || i >= it.V || (moved && !moved[it.garment])) return;
+  it.x[i] = it.copy_src[i];
+}
+__global__ void batch_normals_kernel(const NormalsBatchItem* __restrict__ items) {
+  const NormalsBatchItem& it = items[blockIdx.y];
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < it.V) normals_item(it.x, it.n, it.tri, it.vf_off, it.vf_idx, i);
+}
 __global__ void interpolate_kernel(const float4* __restrict__ x0, const float4* __restrict__ x,
                                    float4* __restrict__ x1, float alpha, uint32_t V) {
   uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -134,4 +146,11 @@ void launch_unpack_xyz(const float* src, float4* dst, uint32_t n, cudaStream_t s
 }
 void launch_pack_xyz(const float4* a, const float4* b, float* out, uint32_t n, cudaStream_t st) {
   if (n) pack_xyz_kernel<<<xrt_grid(n), XRT_BLOCK, 0, st>>>(a, b, out, n);
+}
+
+void launch_post_batched(const NormalsBatchItem* d_items, uint32_t n_items, uint32_t max_v, const int* d_moved, cudaStream_t st) {
+  if (!n_items || !max_v) return;
+  const dim3 g(xrt_grid(max_v), n_items);
+  batch_copy_kernel<<<g, XRT_BLOCK, 0, st>>>(d_items, d_moved);
+  batch_normals_kernel<<<g, XRT_BLOCK, 0, st>>>(d_items);
 }

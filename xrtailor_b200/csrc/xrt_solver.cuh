@@ -88,6 +88,17 @@ void launch_normals(const float4* x, float4* n, const uint32_t* tri, const uint3
 void launch_unpack_xyz(const float* src, float4* dst, uint32_t n, cudaStream_t st);
 void launch_pack_xyz(const float4* a, const float4* b, float* out, uint32_t n, cudaStream_t st);
 void launch_interpolate(const ObstacleDev& o, int step, int num_steps, cudaStream_t st);
+// end of frame for a whole batch: obstacle_->PredictedToPositions() (x = copy_src where the garment's target moved), then
+// UpdateNormals of every mesh; two launches (blockIdx.y = mesh)
+struct NormalsBatchItem {
+  float4* x;               // positions the normals are taken on (x0)
+  const float4* copy_src;  // obstacle: Node::x, copied into x first; cloth: nullptr
+  float4* n;
+  const uint32_t *tri, *vf_off, *vf_idx;
+  uint32_t V;
+  uint32_t garment;        // index into the moved flags
+};
+void launch_post_batched(const NormalsBatchItem* d_items, uint32_t n_items, uint32_t max_v, const int* d_moved, cudaStream_t st);
 // ---- contacts (xrt_contact.cu) ----
 // counts: also record the per-query leaf-hit counts (debug getters); the frame path passes false
 void launch_generate_contacts(const ClothDev& c, const DevBVH& bvh, const uint32_t* rtri, bool counts, cudaStream_t st);
@@ -99,6 +110,25 @@ void launch_candidates(const ClothDev& c, const DevBVH& bvh, int kind, const uin
                        uint32_t* items, uint32_t* counts, cudaStream_t st);
 
 // ---- self contact (xrt_hash.cu) ----
+// predict + spatial hash of every garment of a shared-launch batch in five launches (blockIdx.y = garment)
+struct HashBatchItem {
+  ClothDev c;
+  StepConst k;
+  uint32_t seg;  // where this garment's keys start in the batch's key / value buffers
+};
+struct HashBatch {
+  uint32_t n = 0, total = 0, max_v = 0, max_table = 0;
+  int bits = 0;
+  HashBatchItem* items = nullptr;  // device
+  uint32_t* seg_off = nullptr;
+  uint32_t *key_in = nullptr, *val_in = nullptr, *key_out = nullptr, *val_out = nullptr;
+  void* cub_tmp = nullptr;
+  size_t cub_bytes = 0;
+};
+#include <vector>
+int hash_batch_alloc(HashBatch* hb, const std::vector<HashBatchItem>& items);
+void hash_batch_free(HashBatch* hb);
+void launch_predict_hash_batched(const HashBatch& hb, cudaStream_t st);
 int hash_alloc(ClothDev* c, const StepConst& k);
 void launch_hash(const ClothDev& c, const StepConst& k, cudaStream_t st);
 void launch_collide_particles(const ClothDev& c, const StepConst& k, cudaStream_t st);
