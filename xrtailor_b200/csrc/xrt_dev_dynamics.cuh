@@ -51,10 +51,12 @@ __device__ __forceinline__ void add_pos(X x, uint32_t i, f3 c, bool atomic) {
 // SolveStretch_Kernel, BasicSolverHelper.cu:80-127.  The record (ij, rest) is
 // passed in so a caller can fetch it ahead of a barrier.
 // `lambda` is the multiplier carried from the previous iteration (0 at iteration 0).
+// Projection of one stretch constraint on positions a, b that the caller has already gathered (proper colouring:
+// this thread owns both vertices until the phase barrier), so a caller can issue the gathers of its next item
+// before the arithmetic of this one.
 template <class X>
-__device__ __forceinline__ void stretch_rec(X x, float* s_lambda, uint32_t id, uint2 ij, float rest,
-                                            float lambda, float alpha_tilde, bool atomic) {
-  const float4 a = x[ij.x], b = x[ij.y];
+__device__ __forceinline__ void stretch_apply(X x, float* s_lambda, uint32_t id, uint2 ij, float rest, float lambda,
+                                              float alpha_tilde, float4 a, float4 b) {
   const f3 diff = mk3(a) - mk3(b);
   const float dist = xf_len(diff);
   const float w1 = a.w, w2 = b.w;
@@ -64,13 +66,30 @@ __device__ __forceinline__ void stretch_rec(X x, float* s_lambda, uint32_t id, u
     const float dl = xf_div(-C - alpha_tilde * lambda, w1 + w2 + alpha_tilde);
     const f3 corr = dl * grad;
     lambda += dl;
-    if (atomic) {
-      add_pos(x, ij.x, corr * w1, true);
-      add_pos(x, ij.y, (-corr) * w2, true);
-    } else {
-      x[ij.x] = make_float4(fmaf(corr.x, w1, a.x), fmaf(corr.y, w1, a.y), fmaf(corr.z, w1, a.z), a.w);
-      x[ij.y] = make_float4(fmaf(-corr.x, w2, b.x), fmaf(-corr.y, w2, b.y), fmaf(-corr.z, w2, b.z), b.w);
-    }
+    x[ij.x] = make_float4(fmaf(corr.x, w1, a.x), fmaf(corr.y, w1, a.y), fmaf(corr.z, w1, a.z), a.w);
+    x[ij.y] = make_float4(fmaf(-corr.x, w2, b.x), fmaf(-corr.y, w2, b.y), fmaf(-corr.z, w2, b.z), b.w);
+  }
+  s_lambda[id] = lambda;
+}
+template <class X>
+__device__ __forceinline__ void stretch_rec(X x, float* s_lambda, uint32_t id, uint2 ij, float rest,
+                                            float lambda, float alpha_tilde, bool atomic) {
+  const float4 a = x[ij.x], b = x[ij.y];
+  if (!atomic) {
+    stretch_apply(x, s_lambda, id, ij, rest, lambda, alpha_tilde, a, b);
+    return;
+  }
+  const f3 diff = mk3(a) - mk3(b);
+  const float dist = xf_len(diff);
+  const float w1 = a.w, w2 = b.w;
+  if (dist != rest && w1 + w2 > 0.f) {
+    const f3 grad = diff * xf_rcp(dist + XRT_EPS);
+    const float C = dist - rest;
+    const float dl = xf_div(-C - alpha_tilde * lambda, w1 + w2 + alpha_tilde);
+    const f3 corr = dl * grad;
+    lambda += dl;
+    add_pos(x, ij.x, corr * w1, true);
+    add_pos(x, ij.y, (-corr) * w2, true);
   }
   s_lambda[id] = lambda;
 }
@@ -83,9 +102,9 @@ __device__ __forceinline__ void stretch_one(X x, const uint2* s_idx, const float
 // SolveBend_Kernel, BasicSolverHelper.cu:8-66.  Without atomics the four
 // positions gathered at the top are the ones updated at the bottom (a proper
 // colouring gives this thread exclusive ownership), so x is read once.
-template <class X>
-__device__ __forceinline__ void bend_rec(X x, uint4 q, float theta0, float xpbd_bend, bool atomic) {
-  const float4 a1 = x[q.x], a2 = x[q.y], a3 = x[q.z], a4 = x[q.w];
+template <class X, bool ATOMIC>
+__device__ __forceinline__ void bend_project(X x, uint4 q, float theta0, float xpbd_bend, float4 a1, float4 a2, float4 a3,
+                                             float4 a4) {
   const float w1 = a1.w, w2 = a2.w, w3 = a3.w, w4 = a4.w;
   const f3 p1 = mk3(a1);
   const f3 p2 = mk3(a2) - p1, p3 = mk3(a3) - p1, p4 = mk3(a4) - p1;
@@ -105,7 +124,7 @@ __device__ __forceinline__ void bend_rec(X x, uint4 q, float theta0, float xpbd_
   const float denom = xpbd_bend + fmaf(w1, xf_dot(q1, q1), fmaf(w2, xf_dot(q2, q2), fmaf(w3, xf_dot(q3, q3), w4 * xf_dot(q4, q4))));
   if (denom < XRT_EPS) return;
   const float lambda = xf_div(xf_sqrt(fmaf(-d, d, 1.0f)) * (angle - theta0), denom);
-  if (atomic) {
+  if (ATOMIC) {
     add_pos(x, q.x, (w1 * lambda) * q1, true);
     add_pos(x, q.y, (w2 * lambda) * q2, true);
     add_pos(x, q.z, (w3 * lambda) * q3, true);
@@ -118,6 +137,14 @@ __device__ __forceinline__ void bend_rec(X x, uint4 q, float theta0, float xpbd_
     x[q.z] = make_float4(r3.x, r3.y, r3.z, w3);
     x[q.w] = make_float4(r4.x, r4.y, r4.z, w4);
   }
+}
+template <class X>
+__device__ __forceinline__ void bend_rec(X x, uint4 q, float theta0, float xpbd_bend, bool atomic) {
+  const float4 a1 = x[q.x], a2 = x[q.y], a3 = x[q.z], a4 = x[q.w];
+  if (atomic)
+    bend_project<X, true>(x, q, theta0, xpbd_bend, a1, a2, a3, a4);
+  else
+    bend_project<X, false>(x, q, theta0, xpbd_bend, a1, a2, a3, a4);
 }
 template <class X>
 __device__ __forceinline__ void bend_one(X x, const uint4* b_idx, const float* b_theta, uint32_t id,
