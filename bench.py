@@ -646,6 +646,10 @@ def run_reference(args):
                        key=lambda k: variants[k]["frames_per_s"])
         value = variants[best_key]["frames_per_s"]
         ms_step = 1e3 / value
+        if best_key != "as_shipped":
+            sample = (f"{args.steps} frames per process, reference CUDA physics (sm_100a, --use_fast_math) through the GL-free "
+                      f"harness, best of its variants on one GPU: {best_key} x{_best_procs(variants, best_key)} process(es), "
+                      "per-kernel GPU timers stubbed; wall time of the slowest process")
     else:
         frames = max(1, min(args.steps, args.cpu_frames))
         dt = oracle_frames(wl, frames)
@@ -746,7 +750,7 @@ def main():
                     "(comma list; measured slower than one process: 67 vs 90 frames/s at P = 4 and 8, profiles/r02d_bench_reference_arm.json)")
     ap.add_argument("--ref-mps", type=int, default=1, help="reference arm: time P concurrent reference processes under the CUDA MPS "
                     "daemon (the reference at its best per GPU); falls back to time-sliced processes when the daemon cannot start")
-    ap.add_argument("--ref-mps-procs", default="8,16", help="process counts of the MPS run")
+    ap.add_argument("--ref-mps-procs", default="8,16,32", help="process counts of the MPS run")
     ap.add_argument("--ref-child", default="", help=argparse.SUPPRESS)
     ap.add_argument("--ref-sync", default="", help=argparse.SUPPRESS)
     ap.add_argument("--ref-id", type=int, default=0, help=argparse.SUPPRESS)
