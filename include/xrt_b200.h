@@ -333,6 +333,31 @@ int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts,
                              uint32_t* nodes, float* aabbs,
                              int32_t* esc_int, int32_t* esc_ext, float* build_ms);
 
+/* Morton codes of a triangle mesh (leaf boxes -> scene box -> 30-bit codes, the first stage of the tree build)
+ * WITHOUT ANY ALLOCATION.  No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The stage's scratch (scene box, leaf boxes, object indices: 28 bytes per face) is a file-scope
+ * `static __device__` array of 256 + 28 * XRT_NOALLOC_MAX_FACES bytes (7.0 MiB) that every GPU loading the library
+ * holds until exit.  The call allocates and frees nothing, does not synchronise, and only enqueues 3-4 kernels on
+ * `stream` (a cudaStream_t, NULL = default stream) of the CURRENT device.
+ *   d_positions_xyzw : DEVICE, n_verts * 4 floats (x, y, z, w ignored -- the library's float4 layout)
+ *   d_indices        : DEVICE, 3 * n_faces vertex indices (each < n_verts; not checked)
+ *   d_morton         : DEVICE out, n_faces codes in object (face) order; equal to xrt_bvh_build_standalone's
+ *                      `morton` after that call's own sort: morton_sorted[i] == d_morton[sorted_object[i]]
+ *   d_scene_box      : DEVICE out or NULL, 6 floats (min xyz, max xyz over all leaf boxes)
+ *   err, err_cap     : optional buffer for a message when the call fails
+ * n_faces > XRT_NOALLOC_MAX_FACES fails with XRT_ERR_INVALID and a message; so do host pointers.
+ * Every call shares the one array per device, which keeps the last call's contents (the call itself resets what
+ * must start fresh): calls that overlap on the GPU -- two streams, two host threads -- race on it; serialise them.
+ * The first call on a device looks up the array's device address (cudaGetSymbolAddress, once per device); make that
+ * first call outside stream capture. */
+#define XRT_NOALLOC_MAX_FACES 262144u
+int xrt_morton_codes_noalloc(const float* d_positions_xyzw, uint32_t n_verts,
+                             const uint32_t* d_indices, uint32_t n_faces,
+                             int morton_fast_div, void* stream,
+                             uint32_t* d_morton, float* d_scene_box,
+                             char* err, size_t err_cap);
+
 /* Quality-mode cloth model on the GPU: orthotropic StVK strain
  * per triangle and isometric bending per hinge as coloured Gauss-Seidel passes,
  * `iterations` times [every strain colour, then every bending colour], the inner

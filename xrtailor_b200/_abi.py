@@ -83,7 +83,7 @@ SYMBOLS = [
     "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
     "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
-    "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init",
+    "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init", "xrt_morton_codes_noalloc",
     "xrt_default_quality_params", "xrt_set_quality", "xrt_quality_begin_frame", "xrt_quality_imminent_generate",
     "xrt_quality_imminent_solve", "xrt_quality_rep_update_pairs", "xrt_quality_rep_solve",
     "xrt_quality_obstacle_bvh_update", "xrt_quality_iteration", "xrt_quality_find_impacts",
@@ -134,6 +134,7 @@ def _load():
         "xrt_persist_info": [C.c_int, i32p, i32p],
         "xrt_bvh_build_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, C.c_int, C.c_int, u32p, u32p, u32p, f32p,
                                      i32p, i32p, f32p],
+        "xrt_morton_codes_noalloc": [vp, C.c_uint32, vp, C.c_uint32, C.c_int, vp, vp, vp, C.c_char_p, C.c_size_t],
         "xrt_traverse_pairs_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, f32p, C.c_uint32, u32p, C.c_uint32,
                                           C.c_float, C.c_int, C.c_int, u32p, C.c_size_t, C.POINTER(C.c_size_t), f32p],
         "xrt_fem_solve_standalone": [f32p, f32p, f32p, C.c_uint32, u32p, C.c_uint32, u32p, C.c_uint32, f32p, u32p, u32p,

@@ -454,3 +454,138 @@ void bvh_refit_midstep(const DevBVH& b, const BvhWork& w, const float4* x1, cons
   cudaMemsetAsync(w.flags, 0, F * sizeof(int), st);
   refit_kernel<<<xrt_grid(F), XRT_BLOCK, 0, st>>>(b.tnodes, b.nodes, b.pred, x1, n1, tri, tol, w.flags, F);
 }
+
+// ------------------------------------------------------------------------------------------------
+// xrt_morton_codes_noalloc: the first stage of the tree build (leaf boxes -> scene box -> Morton codes,
+// BVH.cu:423-487,642) for callers that must not allocate (CUDA graph capture, serving loops).  No counterpart in the
+// reference.  The stage's scratch -- the scene box the leaf boxes are
+// reduced into, the leaf boxes themselves and the object indices the Morton kernel writes beside its keys -- lives in
+// ONE file-scope device array that every GPU loading the library holds until exit.  Every call shares it and it keeps
+// the last call's contents: the scene box is re-initialised by the first kernel of each call, leaf boxes and indices
+// are fully overwritten for [0, n_faces) before they are read.  Calls that overlap on the GPU (different streams,
+// different host threads) race on it.
+// ------------------------------------------------------------------------------------------------
+#include "../../include/xrt_b200.h"
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+
+namespace {
+constexpr size_t NOALLOC_HEAD = 256;  // scene box (6 ints), padded so the leaf boxes start on a 256-byte boundary
+constexpr size_t NOALLOC_BYTES = NOALLOC_HEAD + (size_t)XRT_NOALLOC_MAX_FACES * (6 * sizeof(float) + sizeof(uint32_t));
+static __device__ __align__(256) unsigned char xrt_noalloc_scratch[NOALLOC_BYTES];
+
+// In host code `xrt_noalloc_scratch` is a host-side stand-in, not a device address: the address each device gave its
+// copy is asked for once per device, with that device current, and only that pointer is handed to kernels.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+std::mutex g_noalloc_mu;
+
+cudaError_t noalloc_scratch_for(int dev, unsigned char** out) {
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, xrt_noalloc_scratch);  // current device == dev (checked by the caller)
+    if (e != cudaSuccess) return e;
+    g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_noalloc_ptr[dev];
+  return cudaSuccess;
+}
+
+// leaf boxes of ccd = false without the primitive copy of leaf_box_kernel (same min / max, so the same boxes)
+__global__ void noalloc_leaf_box_kernel(const float4* __restrict__ x, const uint32_t* __restrict__ tri,
+                                        float* __restrict__ leaf_box, int* __restrict__ scene, uint32_t F) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+  if (i < F) {
+    const float4 a = x[tri[3 * i]], b = x[tri[3 * i + 1]], c = x[tri[3 * i + 2]];
+    lo[0] = fminf(a.x, fminf(b.x, c.x)); hi[0] = fmaxf(a.x, fmaxf(b.x, c.x));
+    lo[1] = fminf(a.y, fminf(b.y, c.y)); hi[1] = fmaxf(a.y, fmaxf(b.y, c.y));
+    lo[2] = fminf(a.z, fminf(b.z, c.z)); hi[2] = fmaxf(a.z, fmaxf(b.z, c.z));
+    float* o = leaf_box + 6 * (size_t)i;
+    o[0] = lo[0]; o[1] = lo[1]; o[2] = lo[2];
+    o[3] = hi[0]; o[4] = hi[1]; o[5] = hi[2];
+  }
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    float l = lo[k], h = hi[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      l = fminf(l, __shfl_xor_sync(0xFFFFFFFFu, l, o));
+      h = fmaxf(h, __shfl_xor_sync(0xFFFFFFFFu, h, o));
+    }
+    if ((threadIdx.x & 31) == 0) {
+      atomicMin(scene + k, f2ord(l));
+      atomicMax(scene + 3 + k, f2ord(h));
+    }
+  }
+}
+__global__ void noalloc_scene_out_kernel(const int* __restrict__ scene, float* __restrict__ out) {
+  if (threadIdx.x < 6) out[threadIdx.x] = ord2f(scene[threadIdx.x]);
+}
+
+int noalloc_fail(char* err, size_t cap, int code, const char* fmt, ...) {
+  if (err && cap) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(err, cap, fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+bool noalloc_on_device(const void* p, int dev) {
+  cudaPointerAttributes a{};
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return (a.type == cudaMemoryTypeDevice && a.device == dev) || a.type == cudaMemoryTypeManaged;
+}
+}  // namespace
+
+extern "C" int xrt_morton_codes_noalloc(const float* d_positions_xyzw, uint32_t n_verts, const uint32_t* d_indices,
+                                        uint32_t n_faces, int morton_fast_div, void* stream, uint32_t* d_morton,
+                                        float* d_scene_box, char* err, size_t err_cap) {
+  if (err && err_cap) err[0] = 0;
+  if (!d_positions_xyzw || !d_indices || !d_morton || !n_verts || !n_faces)
+    return noalloc_fail(err, err_cap, XRT_ERR_INVALID,
+                        "xrt_morton_codes_noalloc: positions, indices and the morton output are required and must not be empty");
+  if (n_faces > XRT_NOALLOC_MAX_FACES)
+    return noalloc_fail(err, err_cap, XRT_ERR_INVALID,
+                        "xrt_morton_codes_noalloc: %u faces exceed the static scratch of XRT_NOALLOC_MAX_FACES = %u faces "
+                        "(use xrt_bvh_build_standalone or a solver handle, which allocate)",
+                        n_faces, (unsigned)XRT_NOALLOC_MAX_FACES);
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess)
+    return noalloc_fail(err, err_cap, XRT_ERR_CUDA, "xrt_morton_codes_noalloc: no current CUDA device (%s)", cudaGetErrorString(e));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+    return noalloc_fail(err, err_cap, XRT_ERR_INVALID, "xrt_morton_codes_noalloc: device ordinal %d is not supported", dev);
+  if (!noalloc_on_device(d_positions_xyzw, dev) || !noalloc_on_device(d_indices, dev) || !noalloc_on_device(d_morton, dev) ||
+      (d_scene_box && !noalloc_on_device(d_scene_box, dev)))
+    return noalloc_fail(err, err_cap, XRT_ERR_INVALID,
+                        "xrt_morton_codes_noalloc: inputs and outputs must be device memory of the current device %d", dev);
+  unsigned char* base = nullptr;
+  e = noalloc_scratch_for(dev, &base);
+  if (e != cudaSuccess)
+    return noalloc_fail(err, err_cap, XRT_ERR_CUDA, "xrt_morton_codes_noalloc: cudaGetSymbolAddress failed on device %d (%s)", dev,
+                        cudaGetErrorString(e));
+  int* scene = reinterpret_cast<int*>(base);
+  float* leaf_box = reinterpret_cast<float*>(base + NOALLOC_HEAD);
+  uint32_t* val = reinterpret_cast<uint32_t*>(base + NOALLOC_HEAD + (size_t)XRT_NOALLOC_MAX_FACES * 6 * sizeof(float));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float4* x = reinterpret_cast<const float4*>(d_positions_xyzw);
+  const unsigned g = xrt_grid(n_faces);
+  scene_init_kernel<<<1, 32, 0, st>>>(scene);  // the array keeps the last call's scene box: start from +-inf again
+  noalloc_leaf_box_kernel<<<g, XRT_BLOCK, 0, st>>>(x, d_indices, leaf_box, scene, n_faces);
+  if (morton_fast_div)
+    morton_kernel<true><<<g, XRT_BLOCK, 0, st>>>(leaf_box, scene, d_morton, val, n_faces);
+  else
+    morton_kernel<false><<<g, XRT_BLOCK, 0, st>>>(leaf_box, scene, d_morton, val, n_faces);
+  if (d_scene_box) noalloc_scene_out_kernel<<<1, 32, 0, st>>>(scene, d_scene_box);
+  e = cudaGetLastError();
+  if (e != cudaSuccess)
+    return noalloc_fail(err, err_cap, XRT_ERR_CUDA, "xrt_morton_codes_noalloc: launch failed (%s)", cudaGetErrorString(e));
+  return XRT_OK;
+}

@@ -486,6 +486,16 @@ def bvh_build_standalone(positions, indices, fast_div=1, device=0):
     return out
 
 
+def morton_codes_noalloc(d_positions_xyzw, n_verts, d_indices, n_faces, d_morton, d_scene_box=0, fast_div=1, stream=0):
+    """xrt_morton_codes_noalloc: Morton codes in face order through the library's static device scratch, no allocation.
+    All d_* arguments are raw DEVICE addresses (ints) of the current CUDA device; the call only enqueues on `stream`."""
+    err = C.create_string_buffer(512)
+    rc = lib.xrt_morton_codes_noalloc(C.c_void_p(d_positions_xyzw), n_verts, C.c_void_p(d_indices), n_faces, fast_div,
+                                      C.c_void_p(stream), C.c_void_p(d_morton), C.c_void_p(d_scene_box or None), err, len(err))
+    if rc:
+        raise XrtError(rc, err.value.decode() or "xrt_morton_codes_noalloc failed")
+
+
 def traverse_pairs(positions, indices, other_positions=None, other_indices=None, thickness=0.0, fast_div=1, device=0,
                    timing=False):
     """BVH::Traverse (two meshes) / TraverseSelf (other_* = None), BVH.cu:1342-1400: face-face candidate rows
