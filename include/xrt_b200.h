@@ -151,6 +151,40 @@ int xrt_set_obstacle_target(xrt_solver* s, const float* xyz, size_t n_verts);
  * its pose sequence resident the same way (impl/smpl/ClothSolver.cpp:239-249). */
 int xrt_set_obstacle_sequence(xrt_solver* s, const float* xyz, size_t n_frames);
 
+/* Body-animation producer on the device.  Replaces, for a skinned obstacle, the reference's
+ * per-frame chain smplx::Body<>::Update (runtime/rag_doll/smpl/body.cpp:270-383, cuda/body.cu:212-313) ->
+ * Body::verts() device-to-host -> UpdateObstaclePredicted's cudaMalloc + host-to-device + kernel + cudaFree
+ * (physics/ClothSolverHelper.cu:81-97; call site impl/smpl/ClothSolver.cpp:244-249).  The rig stays resident; a
+ * frame uploads 12 floats per joint (or nothing, with a resident pose sequence) and one kernel writes Node::x of the
+ * obstacle: x = M * (sum_j w_vj (R_j v + t_j)), v = rest [+ pose_blend * (R - I)].  Call after xrt_finalize_setup.
+ *   rest_positions : 3*n_verts, the SHAPED rest mesh (shape blend shapes are static and applied by the caller)
+ *   weight_*       : skinning weights in CSR by vertex (outer n_verts+1, inner = joint index, values)
+ *   joints         : 3*n_joints shaped joint positions (joint regressor * rest); parent[j] < j, parent[0] ignored
+ *   model_matrix   : 16 floats row-major = model_matrix * align_matrix of UpdateObstaclePredicted, or NULL
+ *   pose_blend     : optional [3*n_verts][9*(n_joints-1)] row-major pose blend shapes (body.cu:243-249), or NULL */
+typedef struct xrt_rig_desc {
+  const float* rest_positions;
+  const uint32_t* weight_outer;
+  const uint32_t* weight_inner;
+  const float* weight_values;
+  const float* joints;
+  const int32_t* parent;
+  const float* model_matrix;
+  const float* pose_blend;
+  uint32_t n_verts, n_joints;
+} xrt_rig_desc;
+int xrt_set_obstacle_rig(xrt_solver* s, const xrt_rig_desc* rig);
+/* One frame: angle-axis pose (3*n_joints, joint 0 = root orientation) and root translation (3 or NULL), the
+ * arguments of Sequence::set_pose + Body::Update.  Same effect as xrt_set_obstacle_target with the skinned mesh. */
+int xrt_set_obstacle_pose(xrt_solver* s, const float* axis_angle, const float* trans);
+/* A whole pose sequence resident on the device (n_frames x 3*n_joints, trans n_frames x 3 or NULL): every frame
+ * without an explicit target or pose pending takes the next one (wrapping); no per-frame host-to-device traffic. */
+int xrt_set_obstacle_pose_sequence(xrt_solver* s, const float* axis_angle, const float* trans, size_t n_frames);
+/* n_joints x 12 joint transforms ([R | t] row-major) of the last xrt_set_obstacle_pose (Body::_local_to_global). */
+int xrt_get_obstacle_joint_transforms(xrt_solver* s, float* out);
+/* The obstacle's pending target positions Node::x (3*n_verts), whoever wrote them. */
+int xrt_get_obstacle_target(xrt_solver* s, float* xyz);
+
 /* ClothSolverBase::SimulateSwift (pipeline/base/ClothSolverBase.cpp:171-261).
  * solver_ms (may be NULL) receives the CUDA-event time of the frame, the
  * reference's "Solver_Total". */

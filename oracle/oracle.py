@@ -15,8 +15,8 @@ _SO = os.path.join(_HERE, "liboracle.so")
 
 
 def build(force=False):
-    src = os.path.join(_HERE, "xrt_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("xrt_oracle.c", "xrt_oracle_quality.c", "xrt_oracle_rig.c")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s", "liboracle.so"])
     return _SO
 
@@ -37,6 +37,11 @@ def _load():
     L.oracle_fem_solve.argtypes = [f32p, f32p, f32p, C.c_uint32, u32p, C.c_uint32, u32p, C.c_uint32, f32p, u32p, u32p,
                                    C.c_int, C.c_float]
     L.oracle_fem_solve.restype = None
+    L.oracle_rodrigues.argtypes = [f32p, f32p]; L.oracle_rodrigues.restype = None
+    L.oracle_local_to_global.argtypes = [f32p, f32p, f32p, i32p, C.c_uint32, f32p]; L.oracle_local_to_global.restype = None
+    L.oracle_pose_blend_params.argtypes = [f32p, C.c_uint32, f32p]; L.oracle_pose_blend_params.restype = None
+    L.oracle_lbs.argtypes = [f32p, C.c_uint32, u32p, u32p, f32p, f32p, f32p, f32p, f32p, C.c_uint32, f32p]
+    L.oracle_lbs.restype = None
     L.oracle_traverse_pairs.argtypes = [vp, vp, C.c_float, u32p, C.c_size_t]; L.oracle_traverse_pairs.restype = C.c_size_t
     L.oracle_nearest_point_f.argtypes = [f32p, f32p, f32p]; L.oracle_nearest_point_f.restype = C.c_float
     L.oracle_ray_intersect_f.argtypes = [f32p, f32p, C.c_float, f32p]; L.oracle_ray_intersect_f.restype = C.c_float
@@ -404,3 +409,34 @@ def fem_solve(rest, pos, inv_mass, tri, bend_idx, material, colors_strain, color
     L.oracle_fem_solve(_pf(rest), _pf(x), _pf(w), len(x), _pu(tri), len(tri), _pu(bend), len(bend), _pf(m), _pu(cs),
                        _pu(cb), int(iterations), float(dt))
     return x
+
+
+def rig_joint_transforms(pose, joints, parent, trans=None):
+    """Body<>::Update + _local_to_global (runtime/rag_doll/smpl/body.cpp:308-325,386-415): J x 12 joint transforms."""
+    pose, joints = _f(pose).reshape(-1, 3), _f(joints).reshape(-1, 3)
+    par = np.ascontiguousarray(parent, np.int32)
+    T = np.zeros((len(joints), 12), np.float32)
+    t = None if trans is None else _f(trans)
+    L.oracle_local_to_global(_pf(pose), None if t is None else _pf(t), _pf(joints), par.ctypes.data_as(C.POINTER(C.c_int32)),
+                              len(joints), _pf(T))
+    return T
+
+
+def rig_pose_blend_params(pose):
+    pose = _f(pose).reshape(-1, 3)
+    out = np.zeros(9 * (len(pose) - 1), np.float32)
+    L.oracle_pose_blend_params(_pf(pose), len(pose), _pf(out))
+    return out
+
+
+def rig_lbs(rest, w_outer, w_inner, w_val, T, model_matrix=None, pose_blend=None, blend_params=None):
+    """device::lbs (runtime/rag_doll/smpl/cuda/body.cu:39-63) + UpdateObstaclePredicted_Kernel (ClothSolverHelper.cu:70-79)."""
+    rest = _f(rest).reshape(-1, 3)
+    wo, wi, wv, T = _u(w_outer), _u(w_inner), _f(w_val), _f(T)
+    M = None if model_matrix is None else _f(model_matrix)
+    pb = None if pose_blend is None else _f(pose_blend)
+    bp = None if blend_params is None else _f(blend_params)
+    out = np.zeros_like(rest)
+    L.oracle_lbs(_pf(rest), len(rest), _pu(wo), _pu(wi), _pf(wv), _pf(T), None if M is None else _pf(M),
+                  None if pb is None else _pf(pb), None if bp is None else _pf(bp), 0 if bp is None else len(bp), _pf(out))
+    return out

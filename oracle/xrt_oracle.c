@@ -1298,3 +1298,4 @@ void oracle_scene_free(OScene* s) {
 }
 
 #include "xrt_oracle_quality.c"
+#include "xrt_oracle_rig.c"

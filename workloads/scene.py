@@ -290,6 +290,45 @@ class Body:
         return out
 
 
+def body_rig(body, blend=0.04):
+    """Skinning rig of the capsule body for the device-side animation producer: joint 0 = torso (root, at its centre),
+    1 = head, 2..5 = the shoulder / hip joints of the limbs, all children of the root.  Weights are one-hot on the
+    part except within `blend` metres below a limb's joint plane, where the limb blends linearly into the torso (what
+    a skinned body has around a shoulder); blend = 0 reproduces Body.pose exactly.
+    Returns dict(rest, w_outer, w_inner, w_val, joints, parent)."""
+    joints, parent = [], []
+    for name, r, h, c, joint, *_ in _BODY_PARTS:
+        joints.append(c if joint is None else joint)
+        parent.append(-1 if not parent else 0)
+    joints = np.asarray(joints, np.float32)
+    outer, inner, val = [0], [], []
+    for k, (name, lo, hi, joint) in enumerate(body.parts):
+        for v in range(lo, hi):
+            w = 1.0
+            if joint is not None and blend > 0.0:
+                w = float(np.clip((joint[1] - body.rest[v, 1]) / blend, 0.0, 1.0)) if body.rest[v, 1] < joint[1] else 0.0
+            if w >= 1.0 or k == 0:
+                inner.append(k); val.append(1.0)
+            elif w <= 0.0:
+                inner.append(0); val.append(1.0)
+            else:
+                inner += [0, k]; val += [1.0 - w, w]
+            outer.append(len(inner))
+    return dict(rest=body.rest.copy(), w_outer=np.asarray(outer, np.uint32), w_inner=np.asarray(inner, np.uint32),
+                w_val=np.asarray(val, np.float32), joints=joints, parent=np.asarray(parent, np.int32))
+
+
+def body_pose_params(body, frame, amp_deg=30.0, hz=1.0, fps=60.0, phase=0.0):
+    """Angle-axis pose (J x 3) of Body.pose's motion: limbs swing about the x axis, arms and legs in opposite phase."""
+    t = frame / fps
+    a = np.deg2rad(amp_deg) * np.sin(2 * np.pi * hz * t + phase)
+    pose = np.zeros((len(body.parts), 3), np.float32)
+    for k, (name, lo, hi, joint) in enumerate(body.parts):
+        if joint is not None:
+            pose[k, 0] = a if name in ("arm_l", "leg_r") else -a
+    return pose
+
+
 def body_scene(scale=1.0, seed=SEED, gap=0.012):
     """C2: shirt (~18k verts) around the torso and two trouser legs (~6k verts each) around the
     legs, `gap` metres off the body.  The top ring of each garment is tethered to the body with

@@ -15,6 +15,16 @@ class XrtError(RuntimeError):
         self.code = code
 
 
+class XrtRigDesc(C.Structure):
+    _fields_ = [
+        ("rest_positions", C.POINTER(C.c_float)), ("weight_outer", C.POINTER(C.c_uint32)),
+        ("weight_inner", C.POINTER(C.c_uint32)), ("weight_values", C.POINTER(C.c_float)),
+        ("joints", C.POINTER(C.c_float)), ("parent", C.POINTER(C.c_int32)),
+        ("model_matrix", C.POINTER(C.c_float)), ("pose_blend", C.POINTER(C.c_float)),
+        ("n_verts", C.c_uint32), ("n_joints", C.c_uint32),
+    ]
+
+
 class XrtParams(C.Structure):
     _fields_ = [
         ("num_substeps", C.c_int32), ("num_iterations", C.c_int32),
@@ -83,7 +93,8 @@ SYMBOLS = [
     "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
     "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
-    "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init", "xrt_morton_codes_noalloc",
+    "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init", "xrt_morton_codes_noalloc", "xrt_set_obstacle_rig", "xrt_set_obstacle_pose",
+    "xrt_set_obstacle_pose_sequence", "xrt_get_obstacle_joint_transforms", "xrt_get_obstacle_target",
     "xrt_default_quality_params", "xrt_set_quality", "xrt_quality_begin_frame", "xrt_quality_imminent_generate",
     "xrt_quality_imminent_solve", "xrt_quality_rep_update_pairs", "xrt_quality_rep_solve",
     "xrt_quality_obstacle_bvh_update", "xrt_quality_iteration", "xrt_quality_find_impacts",
@@ -134,6 +145,11 @@ def _load():
         "xrt_persist_info": [C.c_int, i32p, i32p],
         "xrt_bvh_build_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, C.c_int, C.c_int, u32p, u32p, u32p, f32p,
                                      i32p, i32p, f32p],
+        "xrt_set_obstacle_rig": [vp, C.POINTER(XrtRigDesc)],
+        "xrt_set_obstacle_pose": [vp, f32p, f32p],
+        "xrt_set_obstacle_pose_sequence": [vp, f32p, f32p, C.c_size_t],
+        "xrt_get_obstacle_joint_transforms": [vp, f32p],
+        "xrt_get_obstacle_target": [vp, f32p],
         "xrt_morton_codes_noalloc": [vp, C.c_uint32, vp, C.c_uint32, C.c_int, vp, vp, vp, C.c_char_p, C.c_size_t],
         "xrt_traverse_pairs_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, f32p, C.c_uint32, u32p, C.c_uint32,
                                           C.c_float, C.c_int, C.c_int, u32p, C.c_size_t, C.POINTER(C.c_size_t), f32p],

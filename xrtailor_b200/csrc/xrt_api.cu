@@ -728,6 +728,8 @@ extern "C" int xrt_set_obstacle_sequence(xrt_solver* s, const float* xyz, size_t
 
 // next frame of the resident sequence -> obstacle target (device to device)
 int xrt_take_sequence_frame(xrt_solver* s, cudaStream_t st) {
+  if (s->rig)  // a resident pose sequence skins the frame on the device (xrt_rig.cu)
+    if (int rc = xrt_rig_take_sequence_frame(s, st)) return rc;
   if (s->target_pending || !s->seq_frames) return XRT_OK;
   const float4* src = s->d_seq + (s->seq_cursor % s->seq_frames) * s->o.V;
   XRT_CUDA_OK(cudaMemcpyAsync(s->o.x, src, s->o.V * sizeof(float4), cudaMemcpyDeviceToDevice, st));
@@ -1257,6 +1259,7 @@ extern "C" void xrt_destroy(xrt_solver* s) {
   if (s->ev_side) cudaEventDestroy(s->ev_side);
   if (s->ev_gv) cudaEventDestroy(s->ev_gv);
   cudaFree(s->pred_alt);
+  xrt_rig_destroy(s);
   if (s->st) cudaStreamDestroy(s->st);
   delete s;
 }

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <vector>
 
+struct RigState;      // body-animation producer (xrt_rig.cu); null without xrt_set_obstacle_rig
 struct QualityState;  // Quality-mode state (xrt_quality.cu); null for a Swift-mode handle
 
 struct xrt_solver {
@@ -68,6 +69,7 @@ struct xrt_solver {
   unsigned long long* d_grid_bar = nullptr;  // grid-wide barrier counter (persist_cluster -2)
   unsigned long long* d_prof = nullptr;  // [16] per-phase-kind ns of the persistent kernel (XRT_PERSIST_PROF=1)
   QualityState* q = nullptr;             // set by xrt_set_quality: the handle runs SimulateQuality
+  RigState* rig = nullptr;               // set by xrt_set_obstacle_rig: the obstacle target is skinned on the device
 };
 
 static inline void xrt_set_error(xrt_solver* s, const char* fmt, ...) {
@@ -125,6 +127,9 @@ PersistArgs xrt_make_persist_args(const xrt_solver* s, int substep, bool moved, 
 int xrt_take_sequence_frame(xrt_solver* s, cudaStream_t st);
 double xrt_frame_bytes(const xrt_solver* s, bool moved);  // algorithmic bytes of one frame, SURVEY 8(d)
 double xrt_bvh_build_bytes(const xrt_solver* s);
+// body-animation producer (xrt_rig.cu)
+int xrt_rig_take_sequence_frame(xrt_solver* s, cudaStream_t st);
+void xrt_rig_destroy(xrt_solver* s);
 // Quality mode (xrt_quality.cu)
 int xrt_quality_finalize(xrt_solver* s);           // called by xrt_finalize_setup when xrt_set_quality was called
 int xrt_quality_step_frame(xrt_solver* s, float* solver_ms);  // ClothSolverBase::SimulateQuality

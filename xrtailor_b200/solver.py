@@ -11,7 +11,7 @@ import ctypes as C
 
 import numpy as np
 
-from ._abi import (XrtCollisionStats, XrtConstraints, XrtError, XrtMeshDesc, XrtParams, XrtQualityParams, XrtStats, default_params,
+from ._abi import (XrtRigDesc, XrtCollisionStats, XrtConstraints, XrtError, XrtMeshDesc, XrtParams, XrtQualityParams, XrtStats, default_params,
                    default_quality_params, lib)
 
 DBG = dict(MORTON=0, SORTED_OBJECT=1, NODES=2, AABBS=3, ESCAPE_INT=4, ESCAPE_EXT=5, VF_CONTACTS=6, RT_CONTACTS=7,
@@ -139,6 +139,42 @@ class ClothSolver:
     def SetObstacleSequence(self, frames_xyz):
         t = _f32(frames_xyz).reshape(-1, self.n_obstacle_verts, 3)
         self._ck(lib.xrt_set_obstacle_sequence(self._h, _pf(t), len(t)))
+
+    def SetObstacleRig(self, rest, w_outer, w_inner, w_val, joints, parent, model_matrix=None, pose_blend=None):
+        """Body animation on the device: the skinning rig of the obstacle (smplx::Body, runtime/rag_doll/smpl)."""
+        keep = dict(rest=_f32(rest).reshape(-1, 3), wo=_u32(w_outer), wi=_u32(w_inner), wv=_f32(w_val),
+                    j=_f32(joints).reshape(-1, 3), par=np.ascontiguousarray(parent, np.int32),
+                    M=None if model_matrix is None else _f32(model_matrix).reshape(16),
+                    pb=None if pose_blend is None else _f32(pose_blend))
+        d = XrtRigDesc()
+        d.rest_positions, d.weight_outer, d.weight_inner, d.weight_values = _pf(keep["rest"]), _pu(keep["wo"]), _pu(keep["wi"]), _pf(keep["wv"])
+        d.joints, d.parent = _pf(keep["j"]), keep["par"].ctypes.data_as(_i32p)
+        d.model_matrix = _pf(keep["M"]) if keep["M"] is not None else None
+        d.pose_blend = _pf(keep["pb"]) if keep["pb"] is not None else None
+        d.n_verts, d.n_joints = len(keep["rest"]), len(keep["j"])
+        self._n_joints = d.n_joints
+        self._ck(lib.xrt_set_obstacle_rig(self._h, C.byref(d)))
+
+    def SetObstaclePose(self, axis_angle, trans=None):
+        """Sequence::set_pose + Body::Update + UpdateObstaclePredicted for one frame (impl/smpl/ClothSolver.cpp:244-249)."""
+        a = _f32(axis_angle).reshape(self._n_joints, 3)
+        t = None if trans is None else _f32(trans).reshape(3)
+        self._ck(lib.xrt_set_obstacle_pose(self._h, _pf(a), None if t is None else _pf(t)))
+
+    def SetObstaclePoseSequence(self, axis_angle, trans=None):
+        a = _f32(axis_angle).reshape(-1, self._n_joints, 3)
+        t = None if trans is None else _f32(trans).reshape(len(a), 3)
+        self._ck(lib.xrt_set_obstacle_pose_sequence(self._h, _pf(a), None if t is None else _pf(t), len(a)))
+
+    def ObstacleJointTransforms(self):
+        out = np.zeros((self._n_joints, 12), np.float32)
+        self._ck(lib.xrt_get_obstacle_joint_transforms(self._h, _pf(out)))
+        return out
+
+    def ObstacleTarget(self):
+        out = np.zeros((self.n_obstacle_verts, 3), np.float32)
+        self._ck(lib.xrt_get_obstacle_target(self._h, _pf(out)))
+        return out
 
     def ProfileKernel(self, which, reps=20):
         ms, b = C.c_float(), C.c_double()
