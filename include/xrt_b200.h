@@ -367,6 +367,21 @@ int xrt_bvh_build_standalone(const float* positions, uint32_t n_verts,
                              uint32_t* nodes, float* aabbs,
                              int32_t* esc_int, int32_t* esc_ext, float* build_ms);
 
+/* Streaming OBJ-sequence writer, host threads only.  Replaces
+ * ObjSequenceExporter::ExportObjSequence (src/runtime/export/ObjSequenceExporter.cpp:155-250), which runs after the
+ * simulation over frames the solver kept in host memory (ClothSolver.cpp:107-144).  Frames are pushed as they come
+ * out of xrt_get_positions / xrt_batch_get_positions and written by `threads` workers (default 2) while the GPU
+ * computes the next ones; push copies the frame and returns, and blocks only when `queue_frames` (default 4) frames
+ * are waiting.  Files are <dir>/%06d.obj, byte for byte the reference's SaveObj output (:21-46 with normals,
+ * :83-103 without): header, "o mesh", "v" lines with 6 decimals, ["vn" lines], "s 1", 1-based faces.
+ * indices: 3*n_faces (each < n_verts, checked); xyz / nrm: 3*n_verts per frame (nrm required iff with_normals).
+ * close drains the queue, joins the workers and reports how many files and bytes were written. */
+typedef struct xrt_obj_writer xrt_obj_writer;
+int xrt_obj_writer_open(const char* dir, const uint32_t* indices, uint32_t n_faces, uint32_t n_verts,
+                        int with_normals, int queue_frames, int threads, xrt_obj_writer** out);
+int xrt_obj_writer_push(xrt_obj_writer* w, const float* xyz, const float* nrm);
+int xrt_obj_writer_close(xrt_obj_writer* w, uint64_t* frames_written, uint64_t* bytes_written);
+
 /* Morton codes of a triangle mesh (leaf boxes -> scene box -> 30-bit codes, the first stage of the tree build)
  * WITHOUT ANY ALLOCATION.  No counterpart in the reference: added for callers
  * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -8,6 +8,6 @@ tests and the bench.  There is no CPU fallback: importing works without a GPU,
 creating a solver does not.
 """
 from ._abi import lib, XrtParams, XrtQualityParams, XrtError, default_params, default_quality_params  # noqa: F401
-from .solver import (ClothSolver, Batch, build_constraints, batch_profile_substep, batch_run, bvh_build_standalone, morton_codes_noalloc, greedy_color, traverse_pairs, fem_solve,  # noqa: F401
+from .solver import (ClothSolver, Batch, build_constraints, batch_profile_substep, batch_run, bvh_build_standalone, morton_codes_noalloc, ObjSequenceWriter, greedy_color, traverse_pairs, fem_solve,  # noqa: F401
                      persist_info)  # noqa: F401
 from . import scene  # noqa: F401

@@ -93,7 +93,7 @@ SYMBOLS = [
     "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
     "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
-    "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init", "xrt_morton_codes_noalloc", "xrt_set_obstacle_rig", "xrt_set_obstacle_pose",
+    "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init", "xrt_morton_codes_noalloc", "xrt_obj_writer_open", "xrt_obj_writer_push", "xrt_obj_writer_close", "xrt_set_obstacle_rig", "xrt_set_obstacle_pose",
     "xrt_set_obstacle_pose_sequence", "xrt_get_obstacle_joint_transforms", "xrt_get_obstacle_target",
     "xrt_default_quality_params", "xrt_set_quality", "xrt_quality_begin_frame", "xrt_quality_imminent_generate",
     "xrt_quality_imminent_solve", "xrt_quality_rep_update_pairs", "xrt_quality_rep_solve",
@@ -150,6 +150,9 @@ def _load():
         "xrt_set_obstacle_pose_sequence": [vp, f32p, f32p, C.c_size_t],
         "xrt_get_obstacle_joint_transforms": [vp, f32p],
         "xrt_get_obstacle_target": [vp, f32p],
+        "xrt_obj_writer_open": [C.c_char_p, u32p, C.c_uint32, C.c_uint32, C.c_int, C.c_int, C.c_int, C.POINTER(vp)],
+        "xrt_obj_writer_push": [vp, f32p, f32p],
+        "xrt_obj_writer_close": [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)],
         "xrt_morton_codes_noalloc": [vp, C.c_uint32, vp, C.c_uint32, C.c_int, vp, vp, vp, C.c_char_p, C.c_size_t],
         "xrt_traverse_pairs_standalone": [f32p, C.c_uint32, u32p, C.c_uint32, f32p, C.c_uint32, u32p, C.c_uint32,
                                           C.c_float, C.c_int, C.c_int, u32p, C.c_size_t, C.POINTER(C.c_size_t), f32p],

@@ -522,6 +522,37 @@ def bvh_build_standalone(positions, indices, fast_div=1, device=0):
     return out
 
 
+class ObjSequenceWriter:
+    """xrt_obj_writer_*: frames are written as <dir>/%06d.obj by background threads while the solver runs
+    (ObjSequenceExporter, runtime/export/ObjSequenceExporter.cpp)."""
+
+    def __init__(self, directory, indices, n_verts, with_normals=False, queue_frames=4, threads=2):
+        tri = _u32(indices).reshape(-1, 3)
+        h = C.c_void_p()
+        rc = lib.xrt_obj_writer_open(str(directory).encode(), _pu(tri), len(tri), int(n_verts), int(with_normals),
+                                     int(queue_frames), int(threads), C.byref(h))
+        if rc:
+            raise XrtError(rc, "obj writer: bad directory or indices")
+        self._h, self._n, self._normals = h, int(n_verts), bool(with_normals)
+
+    def push(self, xyz, normals=None):
+        x = _f32(xyz).reshape(self._n, 3)
+        n = _f32(normals).reshape(self._n, 3) if self._normals else None
+        rc = lib.xrt_obj_writer_push(self._h, _pf(x), None if n is None else _pf(n))
+        if rc:
+            raise XrtError(rc, "obj writer: push failed (closed, or a file could not be written)")
+
+    def close(self):
+        if self._h is None:
+            return 0, 0
+        frames, nbytes = C.c_uint64(), C.c_uint64()
+        rc = lib.xrt_obj_writer_close(self._h, C.byref(frames), C.byref(nbytes))
+        self._h = None
+        if rc:
+            raise XrtError(rc, "obj writer: not every frame was written")
+        return frames.value, nbytes.value
+
+
 def morton_codes_noalloc(d_positions_xyzw, n_verts, d_indices, n_faces, d_morton, d_scene_box=0, fast_div=1, stream=0):
     """xrt_morton_codes_noalloc: Morton codes in face order through the library's static device scratch, no allocation.
     All d_* arguments are raw DEVICE addresses (ints) of the current CUDA device; the call only enqueues on `stream`."""
