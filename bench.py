@@ -619,6 +619,16 @@ def run_reference(args):
     except Exception:
         ref = None
     variants = {}
+    barrier = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        dist.init_process_group("gloo")
+
+        def barrier(flag=0):  # also carries a flag: the maximum over the ranks
+            t = torch.tensor([flag], dtype=torch.int64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return int(t.item())
     if ref is not None:
         os.environ.pop("XRT_REF_NO_TIMERS", None)
         res = _quiet_reference(lambda: ref.time_frames(sc, steps=args.steps, warmup=args.warmup, device=local_rank,
@@ -636,8 +646,8 @@ def run_reference(args):
             c = _ref_concurrent(args, P, local_rank)
             if c:
                 variants[f"concurrent_x{P}"] = c
-        if args.ref_mps and world == 1:
-            variants["mps"] = _ref_with_mps(args, local_rank)
+        if args.ref_mps:
+            variants["mps"] = _ref_with_mps(args, local_rank, rank, barrier)
             if "frames_per_s" not in variants["mps"] and not args.ref_procs:
                 c = _ref_concurrent(args, 4, local_rank)  # no daemon on this box: the time-sliced run instead
                 if c:
@@ -657,9 +667,6 @@ def run_reference(args):
         sample = f"{frames} frames on the CPU oracle port (the reference's CUDA harness is not built on this box)"
         ms_step = dt / frames * 1e3
     if world > 1:
-        import torch
-        import torch.distributed as dist
-        dist.init_process_group("gloo")
         t = torch.tensor([value], dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         value = float(t.item())
@@ -685,33 +692,48 @@ def _best_procs(variants, key):
     return max(best)[1] if best else 1
 
 
-def _ref_with_mps(args, device):
-    """Optional: the same concurrent run under the CUDA MPS daemon (kernels of different processes can then overlap).
-    The daemon is started for this measurement only and shut down again; any failure is reported, not raised."""
-    pipe = "/tmp/xrt_mps_pipe"
-    env = {"CUDA_MPS_PIPE_DIRECTORY": pipe, "CUDA_MPS_LOG_DIRECTORY": "/tmp/xrt_mps_log"}
-    os.makedirs(pipe, exist_ok=True)
-    os.makedirs(env["CUDA_MPS_LOG_DIRECTORY"], exist_ok=True)
+_MPS_ENV = {"CUDA_MPS_PIPE_DIRECTORY": "/tmp/xrt_mps_pipe", "CUDA_MPS_LOG_DIRECTORY": "/tmp/xrt_mps_log"}
+
+
+def _mps_start():
+    for d in _MPS_ENV.values():
+        os.makedirs(d, exist_ok=True)
     try:
-        r = subprocess.run(["nvidia-cuda-mps-control", "-d"], env=dict(os.environ, **env), capture_output=True, text=True, timeout=30)
-        if r.returncode != 0:
-            return {"error": f"daemon did not start: {r.stderr.strip()[:160]}"}
+        r = subprocess.run(["nvidia-cuda-mps-control", "-d"], env=dict(os.environ, **_MPS_ENV), capture_output=True, text=True, timeout=30)
+        return None if r.returncode == 0 else f"daemon did not start: {r.stderr.strip()[:160]}"
     except Exception as e:
-        return {"error": f"daemon did not start: {e}"}
-    out = {}
+        return f"daemon did not start: {e}"
+
+
+def _mps_stop():
     try:
-        old = dict(os.environ)
-        os.environ.update(env)
+        subprocess.run(["nvidia-cuda-mps-control"], input="quit\n", env=dict(os.environ, **_MPS_ENV), capture_output=True, text=True, timeout=30)
+    except Exception:
+        pass
+
+
+def _ref_with_mps(args, device, rank=0, barrier=None):
+    """Optional: the same concurrent run under the CUDA MPS daemon (kernels of different processes can then overlap).
+    The daemon is started for this measurement only and shut down again; any failure is reported, not raised.
+    With several ranks (one per GPU) rank 0 owns the daemon, which serves every GPU of the box; the ranks run their
+    processes side by side, as the repo's own arm runs its batches."""
+    barrier = barrier or (lambda flag=0: flag)
+    err = _mps_start() if rank == 0 else None
+    if barrier(1 if err else 0):  # every rank learns whether rank 0's daemon is up
+        return {"error": err or "daemon did not start on rank 0"}
+    out = {}
+    old = dict(os.environ)
+    try:
+        os.environ.update(_MPS_ENV)
         for P in [int(x) for x in args.ref_mps_procs.split(",") if x.strip()]:
             c = _ref_concurrent(args, P, device, mps=True)
             out[f"x{P}"] = c if c else {"error": "a process failed"}
+            barrier()
+    finally:
         os.environ.clear()
         os.environ.update(old)
-    finally:
-        try:
-            subprocess.run(["nvidia-cuda-mps-control"], input="quit\n", env=dict(os.environ, **env), capture_output=True, text=True, timeout=30)
-        except Exception:
-            pass
+        if rank == 0:
+            _mps_stop()
     best = [v["frames_per_s"] for v in out.values() if isinstance(v, dict) and "frames_per_s" in v]
     if best:
         out["frames_per_s"] = max(best)
@@ -750,7 +772,7 @@ def main():
                     "(comma list; measured slower than one process: 67 vs 90 frames/s at P = 4 and 8, profiles/r02d_bench_reference_arm.json)")
     ap.add_argument("--ref-mps", type=int, default=1, help="reference arm: time P concurrent reference processes under the CUDA MPS "
                     "daemon (the reference at its best per GPU); falls back to time-sliced processes when the daemon cannot start")
-    ap.add_argument("--ref-mps-procs", default="8,16,32", help="process counts of the MPS run")
+    ap.add_argument("--ref-mps-procs", default="8,16", help="process counts of the MPS run")
     ap.add_argument("--ref-child", default="", help=argparse.SUPPRESS)
     ap.add_argument("--ref-sync", default="", help=argparse.SUPPRESS)
     ap.add_argument("--ref-id", type=int, default=0, help=argparse.SUPPRESS)
