@@ -78,6 +78,25 @@ class ClothSolverB200 {
   void Start() { Check(xrt_finalize_setup(h_)); }  // ClothSolverUniversal::Start, ClothSolver.cpp:46-93
 
   // UpdateObstacleAnimationFrame: the posed body of the coming frame
+  // ClothSolverSMPL: the skinned body as a resident rig; per frame the pose replaces sequence_->set_pose + body_->Update +
+  // UpdateObstaclePredicted (impl/smpl/ClothSolver.cpp:244-249).  Call SetObstacleRig after Start().
+  void SetObstacleRig(const xrt_rig_desc& rig) { Check(xrt_set_obstacle_rig(h_, &rig)); }
+  void UpdateObstaclePose(const std::vector<float>& axis_angle, const float* trans = nullptr) {
+    Check(xrt_set_obstacle_pose(h_, axis_angle.data(), trans));
+  }
+  // ObjSequenceExporter (runtime/export/ObjSequenceExporter.cpp): frames stream to <dir>/%06d.obj while the run goes on
+  void OpenObjSequence(const char* dir, const std::vector<uint32_t>& indices, uint32_t n_verts, bool normals = true) {
+    if (xrt_obj_writer_open(dir, indices.data(), (uint32_t)(indices.size() / 3), n_verts, normals, 0, 0, &writer_))
+      throw std::runtime_error("xrt_b200: cannot open the OBJ sequence directory");
+  }
+  void ExportFrame() {  // after SaveCache(): hands the newest cached frame to the writer threads
+    if (writer_ && xrt_obj_writer_push(writer_, h_cloth_positions_cache.back().data(), h_cloth_normals_cache.back().data()))
+      throw std::runtime_error("xrt_b200: OBJ writer failed");
+  }
+  void CloseObjSequence() {
+    if (writer_) xrt_obj_writer_close(writer_, nullptr, nullptr);
+    writer_ = nullptr;
+  }
   void UpdateObstacleAnimationFrame(const std::vector<float>& xyz) { Check(xrt_set_obstacle_target(h_, xyz.data(), xyz.size() / 3)); }
 
   // ClothSolverBase::SimulateSwift / SimulateQuality (ClothSolverBase.cpp:171-362); solver_time = Solver_Total in ms
@@ -94,6 +113,7 @@ class ClothSolverB200 {
     Check(xrt_get_positions(h_, 0, h_cloth_positions_cache.back().data(), h_cloth_normals_cache.back().data()));
   }
   void OnDestroy() {
+    CloseObjSequence();
     if (h_) xrt_destroy(h_);
     h_ = nullptr;
   }
@@ -109,6 +129,7 @@ class ClothSolverB200 {
   }
   xrt_params params_;
   xrt_solver* h_ = nullptr;
+  xrt_obj_writer* writer_ = nullptr;
   size_t n_cloth_ = 0, n_obstacle_ = 0;
   bool quality_ = false;
 };

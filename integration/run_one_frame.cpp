@@ -63,6 +63,27 @@ static int run(bool quality) {
     solver.UpdateObstacleAnimationFrame(tgt);
     solver.Simulate();
   }
+  if (!quality) {
+    // the obstacle as a one-joint rig posed on the device, and the frames streamed to an OBJ sequence
+    const uint32_t nv = (uint32_t)(ob.size() / 3);
+    std::vector<uint32_t> outer(nv + 1), inner(nv, 0u);
+    std::vector<float> w(nv, 1.0f);
+    for (uint32_t i = 0; i <= nv; i++) outer[i] = i;
+    const float joint[3] = {0.f, 0.f, 0.f};
+    const int32_t parent[1] = {-1};
+    xrt_rig_desc rig{ob.data(), outer.data(), inner.data(), w.data(), joint, parent, nullptr, nullptr, nv, 1u};
+    solver.SetObstacleRig(rig);
+    std::vector<uint32_t> all = t0;
+    for (uint32_t v : t1) all.push_back(v + (uint32_t)off1);
+    solver.OpenObjSequence("integration/build/obj_sequence", all, (uint32_t)solver.NumClothVertices());
+    for (int f = 0; f < 2; f++) {
+      const float trans[3] = {0.f, 0.006f + 0.002f * f, 0.f};
+      solver.UpdateObstaclePose({0.f, 0.02f * (f + 1), 0.f}, trans);
+      solver.Simulate();
+      solver.ExportFrame();
+    }
+    solver.CloseObjSequence();
+  }
   const auto& x = solver.h_cloth_positions_cache.back();
   double sum = 0;
   bool finite = true;
