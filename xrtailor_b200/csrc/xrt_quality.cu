@@ -34,6 +34,7 @@
 #include <algorithm>
 #include <cstring>
 #include <set>
+#include <chrono>
 #include <vector>
 
 using namespace xrtq;
@@ -1224,14 +1225,21 @@ int collision_step(xrt_solver* s) {
   const float thickness = q->qp.impact_zone_thickness;
   q->stats = xrt_collision_stats{};
   bool success = false;
+  // XRT_QUALITY_PROF=2: host-clock split of the rounds (every stage ends in a stream sync here)
+  static const bool prof = [] { const char* e = getenv("XRT_QUALITY_PROF"); return e && atoi(e) >= 2; }();
+  double t_find = 0, t_ind = 0, t_iso = 0, t_host = 0, t_solve = 0;
+  auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+  double t0 = 0;
   std::vector<DImpact> ind, flat;
   std::vector<int> col, fcol;
   for (int deform = 0; deform < 2 && !success; deform++) {
     std::vector<HostZone> zones;
     q->stats.deform = deform;
     for (int round = 0; round < 100; round++) {
+      if (prof) { cudaStreamSynchronize(st); t0 = now(); }
       enqueue_find_impacts(s, thickness);
       if (int rc = read_counters(s)) return rc;
+      if (prof) { t_find += now() - t0; t0 = now(); }
       const uint32_t n_new = q->h_cnt[N_IMP];
       q->stats.n_pairs = (int32_t)q->h_cnt[N_PAIRS];
       q->stats.n_candidates = (int32_t)q->h_cnt[N_CAND];
@@ -1241,6 +1249,7 @@ int collision_step(xrt_solver* s) {
       XRT_CUDA_OK(cudaMemcpyAsync(q->h_cnt + N_IND, q->cnt + N_IND, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
       XRT_CUDA_OK(cudaStreamSynchronize(st));
       const uint32_t n_ind = q->h_cnt[N_IND];
+      if (prof) { t_ind += now() - t0; t0 = now(); }
       q->stats.total_impacts += (int32_t)n_ind;
       q->stats.rounds++;
       ind.resize(n_ind);
@@ -1254,6 +1263,7 @@ int collision_step(xrt_solver* s) {
         XRT_CUDA_OK(cudaStreamSynchronize(st));
         nc = (int)q->h_cnt[N_ZONES];
       }
+      if (prof) { t_iso += now() - t0; t0 = now(); }
       add_impacts(s->c.V, zones, ind, col, nc);
       // FlattenImpactZones (ImpactZoneHelper.cu:386-416): the impacts of the active zones back to back
       flat.clear();
@@ -1264,7 +1274,9 @@ int collision_step(xrt_solver* s) {
         for (auto& im : z.imp) { flat.push_back(im); fcol.push_back(nz); }
         nz++;
       }
+      if (prof) { t_host += now() - t0; t0 = now(); }
       if (int rc = solve_zones(s, flat, fcol, nz, deform, thickness, obstacle_mass, nullptr)) return rc;
+      if (prof) { cudaStreamSynchronize(st); t_solve += now() - t0; }
       bvh_update(q->ccd_c, q->ccd_cw, s->c.x0, s->c.x, s->c.tri, 1, st);
       if (deform == 1) {
         if (s->o.F) bvh_update(q->ccd_o, q->ccd_ow, s->o.x0, s->o.x, s->o.tri, 1, st);
@@ -1273,6 +1285,9 @@ int collision_step(xrt_solver* s) {
     }
   }
   q->stats.success = success ? 1 : 0;
+  if (prof)
+    fprintf(stderr, "[xrt quality] CollisionStep rounds %d: find_impacts %.2f | independent %.2f | isolate + copies %.2f | host zones %.2f | "
+            "zone optimiser %.2f ms\n", q->stats.rounds, t_find, t_ind, t_iso, t_host, t_solve);
   return XRT_OK;
 }
 
@@ -1545,10 +1560,19 @@ int xrt_quality_step_frame(xrt_solver* s, float* solver_ms) {
   if (q->qp.enable_imminent_repulsion) enqueue_imminent_generate(s);
   if (s->o.F) bvh_update(s->bvh, s->bw, s->o.x0, s->o.x, s->o.tri, 1, st);  // obstacle_bvh_->Update(faces, true)
   uint32_t launches = 0;
+  // XRT_QUALITY_PROF=1: where a Quality frame's time goes (setup | iterations | CollisionStep), one line per frame
+  static const bool prof = [] { const char* e = getenv("XRT_QUALITY_PROF"); return e && atoi(e) != 0; }();
+  cudaEvent_t pe[3] = {nullptr, nullptr, nullptr};
+  if (prof) {
+    for (auto& e : pe) cudaEventCreate(&e);
+    cudaEventRecord(pe[0], st);
+  }
   for (int substep = 0; substep < p.num_substeps; substep++) {
     launch_predict(s->c, s->k, st);
     for (int it = 0; it < p.num_iterations; it++) launches += (uint32_t)enqueue_iteration(s, it);
+    if (prof && substep == 0) cudaEventRecord(pe[1], st);
     if (int rc = collision_step(s)) return rc;
+    if (prof && substep == 0) cudaEventRecord(pe[2], st);
     launch_finalize(s->c, s->k, st);
   }
   if (s->o.V) {  // obstacle_->PredictedToPositions(); UpdateNormals
@@ -1562,6 +1586,17 @@ int xrt_quality_step_frame(xrt_solver* s, float* solver_ms) {
   if (int rc = read_counters(s)) return rc;
   XRT_CUDA_OK(cudaGetLastError());
   if (solver_ms) XRT_CUDA_OK(cudaEventElapsedTime(solver_ms, s->ev0, s->ev1));
+  if (prof) {
+    float a = 0, b = 0, c = 0, t = 0;
+    cudaEventElapsedTime(&a, s->ev0, pe[0]);
+    cudaEventElapsedTime(&b, pe[0], pe[1]);
+    cudaEventElapsedTime(&c, pe[1], pe[2]);
+    cudaEventElapsedTime(&t, s->ev0, s->ev1);
+    fprintf(stderr, "[xrt quality] frame %.2f ms: setup %.2f | %d iterations %.2f | CollisionStep %.2f (rounds %d, impacts %d, pairs %d, "
+            "candidates %d, deform %d) | quads %u rep items %u\n", t, a, p.num_iterations, b, c, q->stats.rounds, q->stats.total_impacts,
+            q->stats.n_pairs, q->stats.n_candidates, q->stats.deform, q->h_cnt[N_QUAD], q->h_cnt[N_REP]);
+    for (auto& e : pe) cudaEventDestroy(e);
+  }
   return XRT_OK;
 }
 
