@@ -21,9 +21,19 @@ frames = 10
 for M in Ms:
     b = X.Batch(solvers[:M], groups=min(4, M), workers=7)
     b.run(3)
-    p0 = solvers[0].debug("PERSIST_PROF", np.uint64).copy()
+    pa0 = np.stack([s.debug("PERSIST_PROF", np.uint64) for s in solvers[:M]])
+    p0 = pa0[0]
     ms = b.run(frames)
-    p = (solvers[0].debug("PERSIST_PROF", np.uint64) - p0).astype(np.float64) / frames / 1e3
+    pa = (np.stack([s.debug("PERSIST_PROF", np.uint64) for s in solvers[:M]]) - pa0).astype(np.float64) / frames / 1e3
+    p = pa[0]
+    inside, between = pa[:, 13], pa[:, 14]
+    print(f"  per garment, us/frame: inside shared launches min {inside.min():.0f} mean {inside.mean():.0f} max {inside.max():.0f}; "
+          f"between launches min {between.min():.0f} mean {between.mean():.0f} max {between.max():.0f}; "
+          f"inside + between mean {(inside + between).mean():.0f}")
+    per = max(1, M // min(4, M))
+    for gi in range(min(4, M)):
+        sl = inside[gi * per:(gi + 1) * per]
+        print(f"  group {gi}: slowest garment {sl.max():.0f}, fastest {sl.min():.0f} us/frame inside")
     print(f"cluster {cl} M={M}: {ms / frames:.3f} ms per round = {M * frames / ms * 1e3:.0f} f/s; "
           f"garment 0 per-phase-kind us/frame (sum {p[:13].sum():.0f}):")
     print("   " + "  ".join(f"{nm} {v:.0f}" for nm, v in zip(NAMES, p[:13])))

@@ -325,6 +325,17 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_batch_kernel(const Persis
   const uint32_t g = MODE == SYNC_CLUSTER ? blockIdx.x / cluster_nctarank() : blockIdx.x;
   static_assert(sizeof(PersistArgs) % 4 == 0, "argument block is copied word by word");
   const uint32_t mv = moved[g] ? 1u : 0u;
+  // XRT_PERSIST_PROF: [13] time inside shared launches, [14] time between them (stage kernels, launch latency, waiting
+  // for the slowest garment of the group), [15] end of this garment's previous launch
+  unsigned long long* span = nullptr;
+  unsigned long long t_in = 0;
+  if (threadIdx.x == 0 && (MODE != SYNC_CLUSTER || cluster_ctarank() == 0)) {
+    span = table[((size_t)sub_begin * 2u + mv) * n + g].prof;
+    if (span) {
+      t_in = gtimer();
+      if (span[15]) span[14] += t_in - span[15];
+    }
+  }
   // consecutive substeps that need nothing from outside (no hash, no build) run in one launch:
   // a garment does not wait for the slowest garment of the batch between them
   for (int sub = sub_begin; sub < sub_end; sub++) {
@@ -334,6 +345,11 @@ __global__ void __launch_bounds__(PT, 1) swift_substep_batch_kernel(const Persis
     __syncthreads();
     swift_substep_body<MODE>(sa);
     phase_sync<MODE>();  // the substep's last phase is complete (and sa is free) before the next one starts
+  }
+  if (span) {
+    const unsigned long long t_out = gtimer();
+    span[13] += t_out - t_in;
+    span[15] = t_out;
   }
 }
 
