@@ -305,8 +305,10 @@ def run_ours(args):
     done = np.zeros(M_all, np.int64)  # frames each garment has simulated (its cursor in its motion sequence)
     run(args.warmup)
     barrier()
+    counted0 = batch.launch_count() if shared else (0, 0)
     with ClockSampler(local_rank) as clk:
         ms = run(args.steps)
+    counted1 = batch.launch_count() if shared else (0, 0)
     barrier()
     done[:M] += args.warmup + args.steps
     t = torch.tensor([ms], dtype=torch.float64, device="cuda")
@@ -480,10 +482,16 @@ def run_ours(args):
                        "single_instance_ms_per_frame": round(ms_frame_single, 4),
                        "single_instance_ms_per_substep": round(ms_frame_single / 4, 4),
                        "persist_cluster": cluster, "shared_launch": shared, "groups": args.groups if shared else None,
-                       "e2e_instances_per_gpu": M_e2e, "colors": [st["n_stretch_colors"], st["n_bend_colors"]]},
+                       "e2e_instances_per_gpu": M_e2e, "colors": [st["n_stretch_colors"], st["n_bend_colors"]],
+                       "gpu_launches_source": ("counted by the library at its launch sites during the timed region "
+                                               f"(rank 0: {counted1[0] - counted0[0]} own kernels, {counted1[1] - counted0[1]} calls of "
+                                               f"cub's segmented sort; configuration formula: {launches_shared} per frame)")
+                       if shared else "launches per frame of a handle x garments x steps"},
             "e2e": {"value": round(e2e_value, 3), "unit": UNIT, "h2d_bytes_per_step": int(world * M_e2e * Vo * 12),
                     "d2h_bytes_per_step": int(world * M_e2e * V * 12 * 2)},
-            "gpu_launches": int((launches_shared if shared else st["launches_per_frame"] * M) * args.steps * world),
+            # shared launches: counted by the library at its launch sites over the timed region (its own kernels; the
+            # cub sort calls are in config); otherwise launches per frame of a handle x garments x steps
+            "gpu_launches": int(((counted1[0] - counted0[0]) if shared else st["launches_per_frame"] * M * args.steps) * world),
             "clocks": clk.summary(), "roofline": roofline,
         }
         if cpu:

@@ -259,6 +259,9 @@ int xrt_batch_set_obstacle_targets(xrt_batch* b, const float* xyz, size_t n_vert
 int xrt_batch_set_readback(xrt_batch* b, int on);
 /* Kernels one frame of the batch launches (moved: with a new obstacle target). */
 int xrt_batch_launches_per_frame(xrt_batch* b, int moved, uint32_t* out);
+/* Kernels of this library the batch has enqueued since xrt_batch_create, counted where they are launched (substep
+ * kernels, stage kernels, target unpack and read-back pack kernels), and the number of calls into cub's segmented sort. */
+int xrt_batch_launch_count(xrt_batch* b, uint64_t* own_kernels, uint64_t* sort_calls);
 void xrt_batch_destroy(xrt_batch* b);
 
 /* SaveCache (impl/universal/ClothSolver.cpp:107-144): which 0 = cloth,

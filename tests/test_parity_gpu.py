@@ -640,3 +640,23 @@ def test_hash_survives_a_blown_up_garment(small):
     s.HashParticles()          # returns (it used to spin forever in the cell loops)
     assert s.debug("NEIGHBORS", np.uint32).shape[0] > 0
     s.close()
+
+
+def test_batch_launch_count_counts_at_the_launch_sites(small):
+    """xrt_batch_launch_count: kernels of the library per frame of a uniform shared-launch batch = 2 substep launches
+    (substeps 0-2 share one: the hash is due at substeps 0 and 3) + 6 build + 2 x 4 hash + 2 end-of-frame stages per
+    group, whatever the number of garments; cub's segmented sort is counted as calls (1 build + 2 hashes)."""
+    ss = [scene.make_solver(small, persist_cluster=1) for _ in range(4)]
+    b = X.Batch(ss, groups=2)
+    for s in ss:
+        s.UpdateObstacleAnimationFrame(scene.sphere_motion(small.obs_pos, 1))
+    a0, c0 = b.launch_count()
+    b.run(1)
+    a1, c1 = b.launch_count()
+    assert (a1 - a0, c1 - c0) == (2 * (2 + 6 + 8 + 2), 2 * 3)
+    b.run(1)  # the obstacle did not move: no tree build
+    a2, c2 = b.launch_count()
+    assert (a2 - a1, c2 - c1) == (2 * (2 + 8 + 2), 2 * 2)
+    b.close()
+    for s in ss:
+        s.close()

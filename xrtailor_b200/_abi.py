@@ -92,7 +92,7 @@ SYMBOLS = [
     "xrt_debug_candidates", "xrt_greedy_color", "xrt_bvh_build_standalone", "xrt_persist_info", "xrt_batch_profile_substep", "xrt_add_binding",
     "xrt_traverse_pairs_standalone", "xrt_fem_solve_standalone", "xrt_batch_create", "xrt_batch_step_frame_async", "xrt_batch_sync",
     "xrt_batch_step_frames", "xrt_batch_profile", "xrt_batch_destroy", "xrt_batch_get_positions",
-    "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_set_readback",
+    "xrt_batch_set_obstacle_targets", "xrt_batch_launches_per_frame", "xrt_batch_launch_count", "xrt_batch_set_readback",
     "xrt_build_constraints", "xrt_free_constraints", "xrt_global_init", "xrt_morton_codes_noalloc", "xrt_obj_writer_open", "xrt_obj_writer_push", "xrt_obj_writer_close", "xrt_set_obstacle_rig", "xrt_set_obstacle_pose",
     "xrt_set_obstacle_pose_sequence", "xrt_get_obstacle_joint_transforms", "xrt_get_obstacle_target",
     "xrt_default_quality_params", "xrt_set_quality", "xrt_quality_begin_frame", "xrt_quality_imminent_generate",
@@ -165,6 +165,7 @@ def _load():
         "xrt_batch_profile": [vp, C.c_int, f32p, C.POINTER(C.c_double)],
         "xrt_batch_get_positions": [vp, C.c_int, f32p, f32p],
         "xrt_batch_set_obstacle_targets": [vp, f32p, C.c_size_t],
+        "xrt_batch_launch_count": [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)],
         "xrt_batch_launches_per_frame": [vp, C.c_int, u32p],
         "xrt_batch_set_readback": [vp, C.c_int],
         "xrt_build_constraints": [f32p, C.c_uint32, u32p, C.c_uint32, C.POINTER(XrtConstraints)],

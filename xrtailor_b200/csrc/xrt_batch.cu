@@ -50,6 +50,9 @@ struct xrt_batch {
   std::vector<float*> d_snap, h_snap[2];
   std::vector<cudaEvent_t> ev_dn[2];
   unsigned long long snap_written = 0, snap_read = 0;
+  // kernels of this library enqueued so far, counted where they are launched (xrt_batch_launch_count); cub's sort
+  // kernels are library code and counted as calls
+  unsigned long long own_launches = 0, sort_calls = 0;
 };
 
 extern "C" void xrt_batch_destroy(xrt_batch* b) {
@@ -313,6 +316,7 @@ static int batch_snapshot(xrt_batch* b, BatchGroup& g) {
     // the copy of the previous frame has left the device staging buffer
     XRT_CUDA_OK(cudaStreamWaitEvent(g.st, b->ev_dn[par ^ 1][g.first + i], 0));
     launch_pack_xyz(h->c.x0, h->c.n, b->d_snap[g.first + i], (uint32_t)h->c.V, g.st);
+    b->own_launches++;
   }
   XRT_CUDA_OK(cudaEventRecord(g.ev_snap, g.st));
   XRT_CUDA_OK(cudaStreamWaitEvent(g.st_copy, g.ev_snap, 0));
@@ -359,13 +363,24 @@ static int batch_enqueue_frame(xrt_batch* b) {
         if (sub == 0)
           for (int i = 0; i < g.n; i++) build = build || (g.h_moved[i] && b->h[g.first + i]->o.F);
         if (!(hash || build || sub == b->S)) continue;  // this substep joins the running segment
-        if (sub > g.seg_begin)
+        if (sub > g.seg_begin) {
           XRT_CUDA_OK(launch_swift_substep_batch(g.d_table, g.d_moved, (uint32_t)g.n, g.seg_begin, sub, b->cluster, g.st));
+          b->own_launches++;
+        }
         g.seg_begin = sub;
-        if (build) bvh_build_batched(g.bb, g.d_moved, h0->p.morton_fast_div, g.st);
-        if (hash) launch_predict_hash_batched(g.hb, g.st);
+        if (build) {
+          bvh_build_batched(g.bb, g.d_moved, h0->p.morton_fast_div, g.st);
+          b->own_launches += 6;  // stage0, leaf boxes, morton, karras, boxes, links
+          b->sort_calls++;
+        }
+        if (hash) {
+          launch_predict_hash_batched(g.hb, g.st);
+          b->own_launches += 4;  // predict + hash, cell clear, cell ranges, neighbour cache
+          b->sort_calls++;
+        }
         if (sub == b->S) {
           launch_post_batched(g.d_post, g.n_post, g.post_max_v, g.d_moved, g.st);
+          b->own_launches += 2;  // copy, normals
           if (b->readback)
             if (int rc = batch_snapshot(b, g)) return rc;
           XRT_CUDA_OK(cudaEventRecord(g.ev_done, g.st));
@@ -388,9 +403,18 @@ static int batch_enqueue_frame(xrt_batch* b) {
       }
       if (!any) continue;  // this substep joins the running segment
       // substeps [seg_begin, sub) need nothing from outside: one launch
-      if (sub > g.seg_begin)
+      if (sub > g.seg_begin) {
         XRT_CUDA_OK(launch_swift_substep_batch(g.d_table, g.d_moved, (uint32_t)g.n, g.seg_begin, sub, b->cluster, g.st));
+        b->own_launches++;
+      }
       g.seg_begin = sub;
+      for (int i = 0; i < g.n; i++)  // per-garment graphs of a non-uniform group: the kernels their capture recorded
+        if (gr[i]) {
+          const xrt_solver* h = b->h[g.first + i];
+          const bool hash_due = sub < b->S && h->p.enable_self_collision && sub % std::max(1, h->p.inter_leaved_hash) == 0;
+          b->own_launches += sub == b->S ? (h->o.V ? 2u : 1u)
+                                         : (hash_due ? 5u : 0u) + ((sub == 0 && g.h_moved[i] && h->o.F) ? 6u : 0u);
+        }
       if (int rc = batch_fan_out(b, g, gr)) return rc;
       if (sub == b->S) {
         if (b->readback)
@@ -521,6 +545,7 @@ extern "C" int xrt_batch_set_obstacle_targets(xrt_batch* b, const float* xyz, si
       XRT_CUDA_OK(cudaMemcpyAsync(h->d_up, h->h_up, n * 3 * sizeof(float), cudaMemcpyHostToDevice, g.st));
       XRT_CUDA_OK(cudaEventRecord(h->ev_up, g.st));
       launch_unpack_xyz(h->d_up, h->o.x, (uint32_t)n, g.st);
+      b->own_launches++;
       h->target_pending = true;
       row += n;
     }
@@ -530,7 +555,16 @@ extern "C" int xrt_batch_set_obstacle_targets(xrt_batch* b, const float* xyz, si
   return XRT_OK;
 }
 
-// kernels one frame of the batch launches (the count bench.py reports)
+// kernels of this library the batch has enqueued since it was created, counted at the launch sites, and calls into cub's
+// segmented sort (library kernels)
+extern "C" int xrt_batch_launch_count(xrt_batch* b, uint64_t* own_kernels, uint64_t* sort_calls) {
+  if (!b) return XRT_ERR_INVALID;
+  if (own_kernels) *own_kernels = b->own_launches;
+  if (sort_calls) *sort_calls = b->sort_calls;
+  return XRT_OK;
+}
+
+// kernels one frame of the batch launches, from the batch's configuration (xrt_batch_launch_count counts them)
 extern "C" int xrt_batch_launches_per_frame(xrt_batch* b, int moved, uint32_t* out) {
   if (!b || b->h.empty() || !out) return XRT_ERR_INVALID;
   uint32_t n = 0;

@@ -442,6 +442,12 @@ class Batch:
         then returns the oldest unread frame (at most two outstanding)."""
         self._ck(lib.xrt_batch_set_readback(self._h, int(bool(on))))
 
+    def launch_count(self):
+        """(kernels of this library enqueued so far, counted at the launch sites; calls into cub's segmented sort)"""
+        a, b = C.c_uint64(), C.c_uint64()
+        self._ck(lib.xrt_batch_launch_count(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     def launches_per_frame(self, moved=True):
         n = C.c_uint32()
         self._ck(lib.xrt_batch_launches_per_frame(self._h, int(bool(moved)), C.byref(n)))
