@@ -12,12 +12,18 @@ cl = int(sys.argv[1]) if len(sys.argv) > 1 else 1
 Ms = [int(a) for a in sys.argv[2:]] or [1, X.persist_info(cl)[1]]
 sc, body, bindings = scene.body_scene()
 seq = np.stack([body.pose(f + 1, amp_deg=30.0) for f in range(60)])
+varied = os.environ.get("VARIED") == "1"  # phase and amplitude of the motion differ per garment, as in bench.py
+rng = np.random.default_rng(20261104)
 solvers = []
 for i in range(max(Ms)):
     s = scene.make_solver(sc, persist_cluster=cl, bindings=bindings)
-    s.SetObstacleSequence(seq)
+    if varied:
+        ph, amp = float(rng.uniform(0, 2 * np.pi)), float(rng.uniform(20.0, 30.0))
+        s.SetObstacleSequence(np.stack([body.pose(f + 1, amp_deg=amp, phase=ph) for f in range(60)]))
+    else:
+        s.SetObstacleSequence(seq)
     solvers.append(s)
-frames = 10
+frames = 30
 for M in Ms:
     b = X.Batch(solvers[:M], groups=min(4, M), workers=7)
     b.run(3)
