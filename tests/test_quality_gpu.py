@@ -165,6 +165,61 @@ def test_ccd_impacts(n, layers, sphere):
     c.close()
 
 
+def impact_key_rows(nodes, twn):
+    """impact_keys as an int64 array [n, 5] (vectorised for lists of a million impacts)"""
+    nd = np.asarray(nodes, np.int64)
+    vf = np.asarray(twn)[:, 8] > 0.5
+    out = np.zeros((len(nd), 5), np.int64)
+    out[:, 0] = vf
+    f = np.sort(nd[:, 1:], axis=1)
+    out[vf, 1] = nd[vf, 0]
+    out[vf, 2:] = f[vf]
+    a, b = np.sort(nd[:, :2], axis=1), np.sort(nd[:, 2:], axis=1)
+    swap = (a[:, 0] > b[:, 0]) | ((a[:, 0] == b[:, 0]) & (a[:, 1] > b[:, 1]))
+    lo, hi = np.where(swap[:, None], b, a), np.where(swap[:, None], a, b)
+    ee = ~vf
+    out[ee, 1:3] = lo[ee]
+    out[ee, 3:5] = hi[ee]
+    return out
+
+
+def test_ccd_impacts_at_scale_against_the_reference():
+    """Rows a26 + a16 at the size of BASELINE config 4's quarter case (4 layers of 64 x 64 = 16 384 vertices, millions
+    of face pairs): the same impact set as the reference's own FindImpacts on the same state, times to 1e-6 in the
+    median.  The small cases above pin the rows against the oracle one by one; this one pins the compacted pipeline
+    (arena sizes, multi-wave grids, 64-bit offsets) where it is benchmarked."""
+    c = Case(64, 4, 4e-3, (24, 48))
+    if c.r is None:
+        c.close()
+        pytest.skip("reference harness not built")
+    x0, x1, v = falling(c)
+    c.load(x0, x1, v)
+    th = c.q.impact_zone_thickness
+    gn, gt, gp, gc = c.s.FindImpacts(th)
+    rn, rt, rp = c.r.find_impacts(th, float(c.dt))
+    print(f"V={len(x0)}: pairs {gp} (reference {rp}), candidates {gc}, impacts {len(gn)} (reference {len(rn)})")
+    assert gp == rp and len(gn) > 50000
+    gk, rk = impact_key_rows(gn, gt), impact_key_rows(rn, rt)
+    both = np.concatenate([gk, rk])
+    uniq, inv = np.unique(both, axis=0, return_inverse=True)
+    inv = inv.ravel()
+    in_g = np.zeros(len(uniq), bool)
+    in_r = np.zeros(len(uniq), bool)
+    in_g[inv[:len(gk)]] = True
+    in_r[inv[len(gk):]] = True
+    one_side = int((in_g ^ in_r).sum())
+    print(f"distinct impacts: {int(in_g.sum())} here, {int(in_r.sum())} in the reference, on one side only {one_side}")
+    assert one_side <= max(2, int(in_r.sum()) // 2000)
+    tg = np.full(len(uniq), 9.0)
+    tr = np.full(len(uniq), 9.0)
+    np.minimum.at(tg, inv[:len(gk)], gt[:, 0].astype(np.float64))
+    np.minimum.at(tr, inv[len(gk):], rt[:, 0].astype(np.float64))
+    d = np.abs(tg - tr)[in_g & in_r]
+    print(f"|t - t_ref|: median {np.median(d):.1e}, 99th percentile {np.percentile(d, 99):.1e}, max {d.max():.1e}")
+    assert np.median(d) <= 1e-6 and np.percentile(d, 99) <= 2e-5
+    c.close()
+
+
 def test_independent_impacts_and_zones():
     """Row a27: independentImpacts (earliest impact per movable node, rounds on the device) and IsolateImpacts (zone
     flood fill, frontier-parallel in one CTA): the oracle's selection and colours exactly; the reference's selection
