@@ -380,6 +380,47 @@ def test_repulsion_stages():
     c.close()
 
 
+def test_repulsion_stages_at_scale_against_the_reference():
+    """Rows a23 + a24 + a14 at 4 x 64 x 64 = 16 384 vertices against the reference's own CUDA on the same state:
+    imminent quadratures as a set, the PBD pair list after BVH::Update(ccd) pair for pair, and the positions after
+    one ImminentRepulsion::Solve and one SolveNoProximity to 1e-2 of the motion they cause (the quadrature sets differ in a few threshold cases, each one impulse)."""
+    c = Case(64, 4, 0.7e-3, (24, 48), q=qparams(pbd_thickness=2e-3), wave=1e-3, fast_div=1)
+    if c.r is None:
+        c.close()
+        pytest.skip("reference harness not built")
+    x0 = c.sc.cloth_pos.copy()
+    v = c.velocities(-0.2, -0.6)
+    c.s.SetClothState(x0, v); c.s.SetClothPredicted(x0); c.r.set_cloth_state(x0, x0, v)
+    c.s.QualityBeginFrame()
+    gqn, gqb = c.s.ImminentGenerate()
+    rqn, rqb = c.r.imminent_generate()
+    gs, rs = set(map(tuple, gqn.tolist())), set(map(tuple, rqn.tolist()))
+    print(f"V={len(x0)}: quadratures {len(gqn)} (reference {len(rqn)}), on one side only {len(gs ^ rs)}")
+    # the sheets' 1 mm wave takes some pairs across the 1 mm thickness: threshold cases under the reference's fast-math
+    assert len(gqn) > 2000 and len(gs ^ rs) <= max(2, len(rs) // 200)
+    x1 = (x0 + v * c.dt).astype(np.float32)
+    c.s.SetClothState(x0, v); c.s.SetClothPredicted(x1); c.r.set_cloth_state(x0, x1, v)
+    c.s.ImminentSolve()
+    c.r.imminent_solve(float(c.dt))
+    g, rx = c.predicted(), c.r.state(0)["x"]
+    moved = float(np.sqrt(((g - x1) ** 2).sum(1).mean()))
+    print(f"imminent solve: rms motion {moved:.2e}, vs reference {rms(g, rx):.2e}")
+    assert moved > 0 and rms(g, rx) <= max(1e-6, 1e-2 * moved)  # the threshold quadratures each carry one impulse
+    x2 = g.copy()
+    c.s.SetClothState(x0, v); c.s.SetClothPredicted(x2); c.r.set_cloth_state(x0, x2, v)
+    gp = c.s.RepUpdatePairs()
+    rp = c.r.rep_update_pairs()
+    print(f"pbd pairs: {len(gp)} (reference {len(rp)})")
+    assert len(gp) > 100000 and np.array_equal(gp, rp)
+    c.s.RepSolve()
+    c.r.rep_solve(float(c.dt))
+    g, rx = c.predicted(), c.r.state(0)["x"]
+    moved = float(np.sqrt(((g - x2) ** 2).sum(1).mean()))
+    print(f"pbd solve: rms motion {moved:.2e}, vs reference {rms(g, rx):.2e}")
+    assert moved > 0 and rms(g, rx) <= max(1e-6, 1e-2 * moved)  # the threshold quadratures each carry one impulse
+    c.close()
+
+
 @pytest.mark.parametrize("n,N,frames", [(16, 20, 5), (32, 20, 10)])
 def test_quality_frames(n, N, frames):
     """SimulateQuality (ClothSolverBase.cpp:263-362) end to end: two sheets falling on the sphere with repulsion, FEM
