@@ -530,108 +530,164 @@ __device__ __forceinline__ void st3f(float* a, uint32_t i, f3 v) { a[3 * i] = v.
 // ReduceBaselineLocal_Kernel + ReduceBaselineGlobal_Kernel (ParallelOptimizer.cu:330-420): blocks of 256 summed by
 // a stride-doubling tree, then the (at most 256) block sums by the same tree -- the same association order, so
 // the sums (and with them the line-search decisions) are the reference's.
+// The tree over 256 values is evaluated with warp shuffles for strides 1..16 (value t takes value t + stride, exactly
+// the additions s[t] += s[t + stride] of the reference's loop survive in lane t % (2 stride) == 0) and by warp 0 over
+// the eight warp sums for strides 32..128: the same binary tree, two block barriers instead of ten.
+__device__ __forceinline__ float block_tree_sum(float v, float* sbuf) {
+  const int t = threadIdx.x;
+#pragma unroll
+  for (int stride = 1; stride < 32; stride *= 2) v += __shfl_down_sync(0xFFFFFFFFu, v, stride);
+  if ((t & 31) == 0) sbuf[t >> 5] = v;
+  __syncthreads();
+  if (t < 32) {
+    float w = t < QB / 32 ? sbuf[t] : 0.0f;
+#pragma unroll
+    for (int stride = 1; stride < QB / 32; stride *= 2) w += __shfl_down_sync(0xFFFFFFFFu, w, stride);
+    if (t == 0) sbuf[QB / 32] = w;
+  }
+  __syncthreads();
+  const float r = sbuf[QB / 32];
+  __syncthreads();  // sbuf is free again
+  return r;
+}
 template <class Get>
 __device__ __forceinline__ float zone_reduce(float* sbuf, float* part, uint32_t n, Get get) {
   const int t = threadIdx.x;
   uint32_t nb = (n + QB - 1) / QB;
   if (nb > QB) nb = QB;
+  if (nb <= 1) {  // one block: its sum, then the tree over (sum, 0, 0, ...) which adds exact zeros
+    const float r = block_tree_sum((uint32_t)t < n ? get((uint32_t)t) : 0.0f, sbuf);
+    return r;
+  }
   for (uint32_t b = 0; b < nb; b++) {
     const uint32_t i = b * QB + t;
-    sbuf[t] = i < n ? get(i) : 0.0f;
-    __syncthreads();
-    for (int stride = 1; stride < QB; stride *= 2) {
-      if (t % (2 * stride) == 0 && t + stride < QB) sbuf[t] += sbuf[t + stride];
-      __syncthreads();
-    }
-    if (t == 0) part[b] = sbuf[0];
-    __syncthreads();
+    const float r = block_tree_sum(i < n ? get(i) : 0.0f, sbuf);
+    if (t == 0) part[b] = r;
   }
-  sbuf[t] = (uint32_t)t < nb ? part[t] : 0.0f;
   __syncthreads();
-  for (int stride = 1; stride < QB; stride *= 2) {
-    if (t % (2 * stride) == 0 && t + stride < QB) sbuf[t] += sbuf[t + stride];
-    __syncthreads();
-  }
-  const float r = sbuf[0];
-  __syncthreads();
-  return r;
+  return block_tree_sum((uint32_t)t < nb ? part[t] : 0.0f, sbuf);
 }
 
+// SM: the zone's working set -- variables, next variables, gradient, objective terms, constraint values, multipliers and
+// the per-variable / per-impact constants they are computed from -- lives in shared memory (the host picks this variant
+// when the largest zone of the launch fits, zone_smem_bytes).  The optimiser is ~5 000 tiny dependent phases per zone
+// (load a few values, a handful of flops, store, barrier), so its time is the latency of those loads and stores; the
+// arithmetic and its order are the same in both variants.
+struct ZoneImp {  // what the phases read of an impact, 48 bytes
+  float nrm[3];
+  float w[4];
+  int idx[4];
+  uint32_t pad;
+};
+__host__ __device__ inline size_t zone_smem_bytes(size_t nn, size_t ni) {
+  return (14 * nn + 2 * ni) * sizeof(float) + ni * sizeof(ZoneImp);
+}
+
+template <bool SM>
 __global__ void __launch_bounds__(QB) zone_optimize_kernel(OptArgs a) {
   __shared__ float sbuf[QB], part[QB];
+  extern __shared__ __align__(16) unsigned char zone_dyn[];
   const int4 z = a.zone[blockIdx.x];
   const uint32_t no = (uint32_t)z.x, nn = (uint32_t)z.y, io = (uint32_t)z.z, ni = (uint32_t)z.w;
   const int t = threadIdx.x;
   const QMesh& m = a.m;
   const float mu = a.mu, inv_mass = a.inv_mass;
-  auto mass = [&](uint32_t k) { const uint32_t g = a.node[k]; return is_cloth(m, g) ? (1.0f / invm_of(m, g)) : a.obstacle_mass; };
-  auto x1 = [&](uint32_t k) { const uint32_t g = a.node[k]; return mk3(is_cloth(m, g) ? a.cx1[g] : a.ox1[g - m.V]); };
+  // storage, indexed like the global arrays (k in [no, no + nn), i in [io, io + ni))
+  float* dyn = reinterpret_cast<float*>(zone_dyn);
+  float* X = SM ? dyn - 3 * (size_t)no : a.X;
+  float* Xn = SM ? dyn + 3 * (size_t)nn - 3 * (size_t)no : a.Xn;
+  float* G = SM ? dyn + 6 * (size_t)nn - 3 * (size_t)no : a.G;
+  float* X1 = dyn + 9 * (size_t)nn - 3 * (size_t)no;      // SM only: Node::x1 of the variable
+  float* obj = SM ? dyn + 12 * (size_t)nn - (size_t)no : a.obj;
+  float* M = dyn + 13 * (size_t)nn - (size_t)no;           // SM only: mass of the variable
+  float* con = SM ? dyn + 14 * (size_t)nn - (size_t)io : a.con;
+  float* lam = SM ? dyn + 14 * (size_t)nn + (size_t)ni - (size_t)io : a.lam;
+  ZoneImp* zi = reinterpret_cast<ZoneImp*>(dyn + 14 * (size_t)nn + 2 * (size_t)ni) - (size_t)io;  // SM only
+  auto mass_g = [&](uint32_t k) { const uint32_t g = a.node[k]; return is_cloth(m, g) ? (1.0f / invm_of(m, g)) : a.obstacle_mass; };
+  auto x1_g = [&](uint32_t k) { const uint32_t g = a.node[k]; return mk3(is_cloth(m, g) ? a.cx1[g] : a.ox1[g - m.V]); };
+  auto mass = [&](uint32_t k) { return SM ? M[k] : mass_g(k); };
+  auto x1 = [&](uint32_t k) { return SM ? ld3f(X1, k) : x1_g(k); };
+  auto imp_nrm = [&](uint32_t i) { return SM ? mk3(zi[i].nrm[0], zi[i].nrm[1], zi[i].nrm[2]) : mk3(a.imp[i].nrm[0], a.imp[i].nrm[1], a.imp[i].nrm[2]); };
+  auto imp_w = [&](uint32_t i, int j) { return SM ? zi[i].w[j] : a.imp[i].w[j]; };
+  auto imp_idx = [&](uint32_t i, int j) { return SM ? zi[i].idx[j] : a.idx[4 * i + j]; };
   // CollisionConstraint_Kernel (:77-93): c = -thickness + sum_j w_j n . x_j, variables from XX, the rest from the mesh
   auto constraint = [&](const float* XX) {
     for (uint32_t i = io + t; i < io + ni; i += QB) {
-      const DImpact& im = a.imp[i];
-      const f3 nrm = mk3(im.nrm[0], im.nrm[1], im.nrm[2]);
+      const f3 nrm = imp_nrm(i);
       float c = -a.thickness;
       for (int j = 0; j < 4; j++) {
-        const int k = a.idx[4 * i + j];
-        c += im.w[j] * dot3(nrm, k > -1 ? ld3f(XX, (uint32_t)k) : x_of(m, im.n[j]));
+        const int k = imp_idx(i, j);
+        c += imp_w(i, j) * dot3(nrm, k > -1 ? ld3f(XX, (uint32_t)k) : x_of(m, a.imp[i].n[j]));
       }
-      a.con[i] = c;
+      con[i] = c;
     }
     __syncthreads();
   };
   auto coeff = [&]() {  // ClampViolation
-    for (uint32_t i = io + t; i < io + ni; i += QB) a.con[i] = qmin(a.con[i] + a.lam[i] / mu, 0.0f);
+    for (uint32_t i = io + t; i < io + ni; i += QB) con[i] = qmin(con[i] + lam[i] / mu, 0.0f);
     __syncthreads();
   };
   auto objective = [&](const float* XX) {  // CollisionObjective_Kernel (:57-65)
     for (uint32_t k = no + t; k < no + nn; k += QB) {
       const f3 d = ld3f(XX, k) - x1(k);
-      a.obj[k] = mass(k) * dot3(d, d);
+      obj[k] = mass(k) * dot3(d, d);
     }
     __syncthreads();
   };
   for (uint32_t k = no + t; k < no + nn; k += QB) {  // Initialize_Kernel; next_X starts at zero
-    st3f(a.X, k, x_of(m, a.node[k]));
-    st3f(a.Xn, k, mk3(0.f, 0.f, 0.f));
+    st3f(X, k, x_of(m, a.node[k]));
+    st3f(Xn, k, mk3(0.f, 0.f, 0.f));
+    if (SM) {
+      st3f(X1, k, x1_g(k));
+      M[k] = mass_g(k);
+    }
   }
-  for (uint32_t i = io + t; i < io + ni; i += QB) a.lam[i] = 0.0f;
+  for (uint32_t i = io + t; i < io + ni; i += QB) {
+    lam[i] = 0.0f;
+    if (SM) {
+      const DImpact& im = a.imp[i];
+      ZoneImp q;
+      for (int j = 0; j < 3; j++) q.nrm[j] = im.nrm[j];
+      for (int j = 0; j < 4; j++) { q.w[j] = im.w[j]; q.idx[j] = a.idx[4 * i + j]; }
+      q.pad = 0;
+      zi[i] = q;
+    }
+  }
   __syncthreads();
   float s = 1e-3f * (float)nn;  // InitStepLength_Kernel
   bool converged = false;
   int iter, ls_total = 0;
   for (iter = 0; iter < 100; iter++) {
-    constraint(a.X);
+    constraint(X);
     // TotalGradient (:213-224)
-    for (uint32_t k = no + t; k < no + nn; k += QB) st3f(a.G, k, (ld3f(a.X, k) - x1(k)) * (inv_mass * mass(k)));
+    for (uint32_t k = no + t; k < no + nn; k += QB) st3f(G, k, (ld3f(X, k) - x1(k)) * (inv_mass * mass(k)));
     __syncthreads();
     coeff();
     for (uint32_t k = no + t; k < no + nn; k += QB) {  // a node gathers its impacts in slot order: no atomics
-      f3 g = ld3f(a.G, k);
+      f3 g = ld3f(G, k);
       for (uint32_t q = a.inc_off[k]; q < a.inc_off[k + 1]; q++) {
         const uint32_t slot = a.inc_slot[q], i = slot >> 2, j = slot & 3u;
-        const DImpact& im = a.imp[i];
-        g = g + mk3(im.nrm[0], im.nrm[1], im.nrm[2]) * (mu * a.con[i] * im.w[j]);
+        g = g + imp_nrm(i) * (mu * con[i] * imp_w(i, (int)j));
       }
-      st3f(a.G, k, g);
+      st3f(G, k, g);
     }
     __syncthreads();
-    const float G2 = zone_reduce(sbuf, part, nn, [&](uint32_t i) { const f3 g = ld3f(a.G, no + i); return dot3(g, g); });
-    objective(a.X);
-    const float C2 = zone_reduce(sbuf, part, ni, [&](uint32_t i) { return a.con[io + i] * a.con[io + i]; });
-    const float L2 = zone_reduce(sbuf, part, ni, [&](uint32_t i) { return a.lam[io + i] * a.lam[io + i]; });
-    const float O = zone_reduce(sbuf, part, nn, [&](uint32_t i) { return a.obj[no + i]; });
+    const float G2 = zone_reduce(sbuf, part, nn, [&](uint32_t i) { const f3 g = ld3f(G, no + i); return dot3(g, g); });
+    objective(X);
+    const float C2 = zone_reduce(sbuf, part, ni, [&](uint32_t i) { return con[io + i] * con[io + i]; });
+    const float L2 = zone_reduce(sbuf, part, ni, [&](uint32_t i) { return lam[io + i] * lam[io + i]; });
+    const float O = zone_reduce(sbuf, part, nn, [&](uint32_t i) { return obj[no + i]; });
     s /= 0.7f;  // PreconditionStepLength_Kernel
     bool wolfe = false;
     do {
       s *= 0.7f;  // AdjustStepLength_Kernel
-      for (uint32_t k = no + t; k < no + nn; k += QB) st3f(a.Xn, k, ld3f(a.X, k) - ld3f(a.G, k) * s);  // NextX_Kernel
+      for (uint32_t k = no + t; k < no + nn; k += QB) st3f(Xn, k, ld3f(X, k) - ld3f(G, k) * s);  // NextX_Kernel
       __syncthreads();
-      objective(a.Xn);
-      constraint(a.Xn);
+      objective(Xn);
+      constraint(Xn);
       coeff();
-      const float C2t = zone_reduce(sbuf, part, ni, [&](uint32_t i) { return a.con[io + i] * a.con[io + i]; });
-      const float Ot = zone_reduce(sbuf, part, nn, [&](uint32_t i) { return a.obj[no + i]; });
+      const float C2t = zone_reduce(sbuf, part, ni, [&](uint32_t i) { return con[io + i] * con[io + i]; });
+      const float Ot = zone_reduce(sbuf, part, nn, [&](uint32_t i) { return obj[no + i]; });
       // BacktrackingLineSearchAdvanced_Kernel (ParallelImpactZoneOptimizer.cu:383-468)
       const float f = 0.5f * inv_mass * O + 0.5f * mu * C2 - 0.5f * L2 / mu;
       const float ft = 0.5f * inv_mass * Ot + 0.5f * mu * C2t - 0.5f * L2 / mu;
@@ -640,10 +696,10 @@ __global__ void __launch_bounds__(QB) zone_optimize_kernel(OptArgs a) {
     } while (!wolfe);
     if (s < IZO_EPS_S) converged = true;  // UpdateConvergency_Kernel
     if (converged) break;
-    for (uint32_t k = no + t; k < no + nn; k += QB) st3f(a.X, k, ld3f(a.Xn, k));
+    for (uint32_t k = no + t; k < no + nn; k += QB) st3f(X, k, ld3f(Xn, k));
     __syncthreads();
-    constraint(a.X);  // UpdateMultiplier (:226-235)
-    for (uint32_t i = io + t; i < io + ni; i += QB) a.lam[i] = qmin(a.lam[i] + mu * a.con[i], 0.0f);
+    constraint(X);  // UpdateMultiplier (:226-235)
+    for (uint32_t i = io + t; i < io + ni; i += QB) lam[i] = qmin(lam[i] + mu * con[i], 0.0f);
     __syncthreads();
   }
   // Finalize_Kernel.  A node two zones list (an impact takes the zone of its FIRST zoned node, its other nodes may
@@ -652,7 +708,7 @@ __global__ void __launch_bounds__(QB) zone_optimize_kernel(OptArgs a) {
   for (uint32_t k = no + t; k < no + nn; k += QB) {
     if (a.skip[k]) continue;
     const uint32_t g = a.node[k];
-    const f3 p = ld3f(a.X, k);
+    const f3 p = ld3f(X, k);
     if (is_cloth(m, g)) { float4 q = a.out_cx[g]; q.x = p.x; q.y = p.y; q.z = p.z; a.out_cx[g] = q; }
     else { float4 q = a.out_ox[g - m.V]; q.x = p.x; q.y = p.y; q.z = p.z; a.out_ox[g - m.V] = q; }
   }
@@ -1145,7 +1201,28 @@ int solve_zones(xrt_solver* s, const std::vector<DImpact>& imp, const std::vecto
   a.out_cx = s->c.x; a.out_ox = s->o.x;
   a.thickness = thickness; a.obstacle_mass = obstacle_mass; a.inv_mass = inv_mass; a.mu = 1e3f;
   a.deform = deform;
-  zone_optimize_kernel<<<nz, QB, 0, st>>>(a);
+  {
+    // shared-memory variant when the largest zone of this launch fits (opt-in dynamic shared memory, once per device)
+    size_t need = 0;
+    for (int c = 0; c < nz; c++) need = std::max(need, zone_smem_bytes((size_t)zone[c].y, (size_t)zone[c].w));
+    static const size_t limit = [] {
+      const char* e = getenv("XRT_ZONE_SMEM");  // measurement switch: 0 keeps the optimiser's state in global memory
+      if (e && atoi(e) == 0) return (size_t)0;
+      return (size_t)200 * 1024;
+    }();
+    if (need <= limit) {
+      static thread_local int configured_dev = -1;
+      int dev = -1;
+      cudaGetDevice(&dev);
+      if (configured_dev != dev) {
+        XRT_CUDA_OK(cudaFuncSetAttribute(zone_optimize_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)limit));
+        configured_dev = dev;
+      }
+      zone_optimize_kernel<true><<<nz, QB, need, st>>>(a);
+    } else {
+      zone_optimize_kernel<false><<<nz, QB, 0, st>>>(a);
+    }
+  }
   XRT_CUDA_OK(cudaGetLastError());
   // the copies above read pageable host vectors: wait before they go out of scope; the stats ride along
   std::vector<int> hs(3 * (size_t)nz);
