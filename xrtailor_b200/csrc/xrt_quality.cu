@@ -56,6 +56,7 @@ struct HostZone {
   std::vector<DImpact> imp;
   std::vector<int> node_idx;  // 4 per impact: Node::index, LOCAL to its mesh (FlattenNode_Kernel)
   bool active = true, sorted = false, enabled = true;
+  bool prev_active = true;  // grew or was new in the previous round (its tests of that round may predate the growth)
 };
 
 struct QualityState {
@@ -1171,12 +1172,14 @@ int solve_zones(xrt_solver* s, const std::vector<DImpact>& imp, const std::vecto
   std::vector<int4> zone(nz);
   {
     size_t no = 0, io = 0;
+    std::vector<size_t> cn((size_t)nz, 0), ci((size_t)nz, 0);
+    for (size_t i = 0; i < nn; i++)
+      if (ncolor[i] >= 0 && ncolor[i] < nz) cn[(size_t)ncolor[i]]++;
+    for (size_t i = 0; i < n; i++)
+      if (color[i] >= 0 && color[i] < nz) ci[(size_t)color[i]]++;
     for (int c = 0; c < nz; c++) {
-      size_t cn = 0, ci = 0;
-      for (size_t i = 0; i < nn; i++) cn += ncolor[i] == c;
-      for (size_t i = 0; i < n; i++) ci += color[i] == c;
-      zone[c] = make_int4((int)no, (int)cn, (int)io, (int)ci);
-      no += cn; io += ci;
+      zone[c] = make_int4((int)no, (int)cn[c], (int)io, (int)ci[c]);
+      no += cn[c]; io += ci[c];
     }
   }
   // inv_mass = mean of the per-node inverse masses (thrust::reduce :237-243)
@@ -1254,8 +1257,10 @@ bool zone_merge(HostZone& a, HostZone& b) {
   if (!b.enabled) return false;
   if (!zone_intersects(a, b)) return false;
   a.imp.insert(a.imp.end(), b.imp.begin(), b.imp.end());
+  const size_t mid = a.node_idx.size();  // both lists are sorted (zone_intersects): merge instead of sorting again
   a.node_idx.insert(a.node_idx.end(), b.node_idx.begin(), b.node_idx.end());
-  a.active = true; a.sorted = false; a.enabled = true;
+  std::inplace_merge(a.node_idx.begin(), a.node_idx.begin() + (std::ptrdiff_t)mid, a.node_idx.end());
+  a.active = true; a.sorted = true; a.enabled = true;
   b.enabled = false;
   return true;
 }
@@ -1264,11 +1269,17 @@ void add_impacts(uint32_t V, std::vector<HostZone>& zones, const std::vector<DIm
   const size_t n = nimp.size();
   // stable_sort_by_key(colours) + ranges from the per-zone counts (:305-331): impacts left at -1 by the 100-zone
   // cap sort to the front and shift every range, as in the reference
-  std::vector<size_t> order;
+  std::vector<size_t> order(n);
   std::vector<size_t> cnt((size_t)nc + 1, 0);
-  for (int c = -1; c < nc; c++)
-    for (size_t i = 0; i < n; i++)
-      if (col[i] == c) { order.push_back(i); if (c >= 0) cnt[c]++; }
+  {
+    std::vector<size_t> at((size_t)nc + 2, 0);  // bucket c + 1 (colour -1 first), a stable counting sort
+    for (size_t i = 0; i < n; i++) at[(size_t)(col[i] + 1) + 1]++;
+    for (size_t c = 1; c < at.size(); c++) at[c] += at[c - 1];
+    for (size_t i = 0; i < n; i++) {
+      order[at[(size_t)(col[i] + 1)]++] = i;
+      if (col[i] >= 0) cnt[(size_t)col[i]]++;
+    }
+  }
   std::vector<HostZone> nz((size_t)nc);
   size_t lhs = 0;
   for (int c = 0; c < nc; c++) {
@@ -1280,13 +1291,18 @@ void add_impacts(uint32_t V, std::vector<HostZone>& zones, const std::vector<DIm
     lhs += cnt[c];
   }
   const size_t n_zone = zones.size();
-  for (size_t i = 0; i < n_zone; i++) zones[i].active = false;
+  for (size_t i = 0; i < n_zone; i++) { zones[i].prev_active = zones[i].active; zones[i].active = false; }
   for (size_t i = 0; i < n_zone; i++)
     for (size_t j = 0; j < nz.size(); j++) zone_merge(zones[i], nz[j]);
   for (size_t j = 0; j < nz.size(); j++)
     if (nz[j].enabled) zones.push_back(std::move(nz[j]));
+  // All pairs, in the reference's order.  A pair of zones that both stayed as they were through the whole previous
+  // round and this one so far has been tested with exactly these contents before and did not intersect (a zone that
+  // grew DURING the previous round's pass may have been tested against its earlier neighbours before it grew, hence
+  // prev_active), so that test is skipped: the zones and their order come out the same.
   for (size_t i = 0; i < zones.size(); i++)
-    for (size_t j = i + 1; j < zones.size(); j++) zone_merge(zones[i], zones[j]);
+    for (size_t j = i + 1; j < zones.size(); j++)
+      if (zones[i].active || zones[j].active || zones[i].prev_active || zones[j].prev_active) zone_merge(zones[i], zones[j]);
   std::vector<HostZone> kept;
   for (auto& z : zones)
     if (z.enabled) kept.push_back(std::move(z));
